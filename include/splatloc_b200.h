@@ -1,0 +1,132 @@
+/* include/splatloc_b200.h
+ *
+ * C ABI of libsplatloc_b200.so: the B200 (sm_100a) implementation of SplatLoc's
+ * differentiable Gaussian-splat rasterizer (diff_gauss) and simple-knn's
+ * distCUDA2.  Plain pointers and sizes only; every pointer is a DEVICE pointer
+ * unless stated otherwise; the caller owns all memory.  A null pointer means
+ * "optional input absent", exactly as the reference treats the data_ptr() of an
+ * empty tensor (rasterize_points.cu:100-107).
+ *
+ * Paths below are relative to the reference tree; DGR = submodules/
+ * diff-gaussian-rasterization, KNN = submodules/simple-knn.
+ *
+ * Return convention: >= 0 success (sl_forward returns the number of
+ * (tile, Gaussian) pairs R), < 0 failure with the text in sl_last_error():
+ *   -1 CUDA runtime error      -2 invalid argument
+ *   -3 capacity exceeded       -4 allocation callback returned NULL
+ */
+#ifndef SPLATLOC_B200_H_INCLUDED
+#define SPLATLOC_B200_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SL_ERR_CUDA     (-1)
+#define SL_ERR_ARGUMENT (-2)
+#define SL_ERR_CAPACITY (-3)
+#define SL_ERR_ALLOC    (-4)
+
+/* Growable scratch chunk: must return a device pointer to at least `bytes`
+ * bytes that stays valid until the matching sl_backward has run.  Replaces the
+ * std::function<char*(size_t)> of DGR/cuda_rasterizer/rasterizer.h:135-137 (in
+ * the reference it resizes a torch byte tensor, DGR/rasterize_points.cu:27-33). */
+typedef char* (*sl_alloc_fn)(void* ctx, size_t bytes);
+
+/* Library / build identification, e.g. "splatloc_b200 0.1 sm_100a". */
+const char* sl_version(void);
+
+/* Text of the last error raised on the calling thread ("" if none). */
+const char* sl_last_error(void);
+
+/* Bytes of the three scratch chunks for P Gaussians, R pairs, a W x H image.
+ * Replaces CudaRasterizer::required<GeometryState|BinningState|ImageState>
+ * (DGR/cuda_rasterizer/rasterizer_impl.h:66-81).  The leading fields of each
+ * chunk keep the reference layout (rasterizer_impl.cu:393-431), so
+ * diff_gauss.interpret_{geom,binning,img}Buffer read them unchanged. */
+size_t sl_geometry_bytes(int P);
+size_t sl_binning_bytes(int R);
+size_t sl_image_bytes(int width, int height);
+
+/* Forward rasterization.  Replaces CudaRasterizer::Rasterizer::forward
+ * (DGR/cuda_rasterizer/rasterizer.h:134-159, rasterizer_impl.cu:435-582), which
+ * RasterizeGaussiansCUDA binds (DGR/rasterize_points.cu:35-121).
+ *
+ *   C           number of feature channels, 3 or 4 (a compile-time constant,
+ *               NUM_CHANNELS, in the reference: cuda_rasterizer/config.h:15)
+ *   D, M        active SH degree, SH coefficients per Gaussian (0 without shs)
+ *   background  [C]
+ *   means3D [P,3]  shs [P,M,3]|NULL  colors_precomp [P,C]|NULL  opacities [P]
+ *   scales [P,3]|NULL  rotations [P,4] (w,x,y,z)|NULL  cov3D_precomp [P,6]|NULL
+ *   tile_mask   [ceil(H/16) * ceil(W/16)] bytes (0/1) | NULL
+ *   viewmatrix, projmatrix  [16] floats, element 4*c+r = mathematical M[r][c]
+ *   cam_pos [3]
+ *   out_color [C,H,W]  out_depth [H,W]  out_alpha [H,W]  radii [P] (may be NULL)
+ *   stream      cudaStream_t the work is enqueued on (the reference uses the
+ *               legacy default stream)
+ * Exactly one of shs / colors_precomp and one of (scales, rotations) /
+ * cov3D_precomp must be given; C != 3 requires colors_precomp (same rule and
+ * message as rasterizer_impl.cu:482-485).  Outputs are written for every pixel
+ * and every Gaussian; they need not be zeroed by the caller.  The call blocks
+ * the host once, to read R back after the prefix sum (as the reference does,
+ * rasterizer_impl.cu:522).  Returns R. */
+int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+               sl_alloc_fn binning_alloc, void* binning_ctx,
+               sl_alloc_fn image_alloc, void* image_ctx,
+               int P, int D, int M, int C,
+               const float* background, int width, int height,
+               const float* means3D, const float* shs, const float* colors_precomp,
+               const float* opacities, const float* scales, float scale_modifier,
+               const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+               const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+               float tan_fovx, float tan_fovy, int prefiltered,
+               float* out_color, float* out_depth, float* out_alpha, int* radii,
+               int debug, void* stream);
+
+/* Backward rasterization.  Replaces CudaRasterizer::Rasterizer::backward
+ * (DGR/cuda_rasterizer/rasterizer.h:161-195, rasterizer_impl.cu:586-692), bound
+ * by RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:123-213).
+ * The three scratch chunks are the ones sl_forward filled (same P, R, W, H).
+ * All dL_d* outputs must be ZERO on entry (the reference binding allocates them
+ * with torch::zeros, rasterize_points.cu:160-171):
+ *   dL_dmean2D [P,3]  dL_dabsmean2D [P,3]  dL_dconic [P,4]  dL_dopacity [P]
+ *   dL_dcolor [P,C]   dL_ddepth [P]        dL_dmean3D [P,3] dL_dcov3D [P,6]
+ *   dL_dsh [P,M,3]    dL_dscale [P,3]      dL_drot [P,4]
+ * Inputs: dL_dpix [C,H,W], dL_dpix_depth [H,W], dL_dpix_alpha [H,W],
+ * accum_alphas = sl_forward's out_alpha, radii = sl_forward's radii. */
+int sl_backward(int P, int D, int M, int R, int C,
+                const float* background, int width, int height,
+                const float* means3D, const float* shs, const float* colors_precomp,
+                const float* scales, float scale_modifier, const float* rotations,
+                const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                const float* dL_dpix_alpha,
+                float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                float* dL_dsh, float* dL_dscale, float* dL_drot,
+                int debug, void* stream);
+
+/* Frustum visibility, present[i] in {0,1}.  Replaces
+ * CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:71-76,
+ * rasterizer_impl.cu:379-391), bound by markVisible (DGR/rasterize_points.cu:215-234). */
+int sl_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                    const float* projmatrix, uint8_t* present, void* stream);
+
+/* distCUDA2: mean_dists[i] = mean of the squared distances from point i to its 3
+ * nearest other points.  Replaces SimpleKNN::knn (KNN/simple_knn.h:16-20,
+ * simple_knn.cu:186-221), bound by distCUDA2 (KNN/spatial.cu:15-25).  The
+ * reference allocates its temporaries itself (cudaMalloc / thrust); here the
+ * caller passes `scratch` of at least sl_knn_scratch_bytes(P) bytes. */
+size_t sl_knn_scratch_bytes(int P);
+int sl_knn(int P, const float* points, float* mean_dists,
+           char* scratch, size_t scratch_bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPLATLOC_B200_H_INCLUDED */

@@ -1,0 +1,225 @@
+"""Host-side operator layer: torch tensors in, C-ABI calls out.
+
+Mirrors the functions the reference registers in its pybind module `diff_gauss._C`
+for this path (submodules/diff-gaussian-rasterization/ext.cpp:15-27 and
+rasterize_points.h:18-67,105-108) and simple-knn's `simple_knn._C.distCUDA2`
+(submodules/simple-knn/ext.cpp:15-17, spatial.h:14): same names, positional
+argument order, return tuples and error behaviour.  PyTorch is used for device
+memory and the current stream only; all computation is in libsplatloc_b200.so.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _capi
+
+
+def _ptr(t: torch.Tensor | None):
+    """Device address, or NULL for an absent (None / empty) optional tensor."""
+    if t is None or t.numel() == 0:
+        return None
+    return t.data_ptr()
+
+
+def _f32(t: torch.Tensor, name: str) -> torch.Tensor:
+    if t.numel() == 0:
+        return t
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (the rasterizer has no CPU path)")
+    if t.dtype != torch.float32:
+        raise RuntimeError(f"{name} must be float32, got {t.dtype}")
+    return t.contiguous()
+
+
+def _stream(device) -> int:
+    return torch.cuda.current_stream(device).cuda_stream
+
+
+class _Chunk:
+    """A growable byte tensor handed to the library as an allocation callback
+    (the reference's resizeFunctional, rasterize_points.cu:27-33)."""
+
+    def __init__(self, device):
+        self.device = device
+        self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
+
+        def _alloc(_ctx, nbytes):
+            self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
+            return self.tensor.data_ptr()
+
+        self.callback = _capi.ALLOC_FN(_alloc)
+
+
+def _pad_bg(bg: torch.Tensor, n_ch: int) -> torch.Tensor:
+    """SplatLoc hands a 3-float background to its 4-channel build, which then reads
+    one float past the end (train_gaussians.py:70 vs forward.cu:960).  Here missing
+    channels are defined as 0 instead of out-of-bounds memory."""
+    bg = bg.reshape(-1)
+    if bg.numel() >= n_ch:
+        return bg
+    return torch.cat([bg, bg.new_zeros(n_ch - bg.numel())])
+
+
+def _channels(colors: torch.Tensor) -> int:
+    if colors.numel() == 0:
+        return 3  # SH colours are RGB
+    if colors.dim() != 2 or colors.shape[1] not in (3, 4):
+        raise RuntimeError(f"colors_precomp must have shape (num_points, 3 or 4), got {tuple(colors.shape)}")
+    return int(colors.shape[1])
+
+
+def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                        cov3D_precomp, tile_mask, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                        image_height, image_width, sh, degree, campos, prefiltered, debug):
+    """-> (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer)."""
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    lib = _capi.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (the rasterizer has no CPU path)")
+    dev = means3D.device
+    P, H, W = int(means3D.shape[0]), int(image_height), int(image_width)
+
+    means3D = _f32(means3D, "means3D")
+    colors = _f32(colors, "colors_precomp")
+    opacity = _f32(opacity, "opacities")
+    scales = _f32(scales, "scales")
+    rotations = _f32(rotations, "rotations")
+    cov3D_precomp = _f32(cov3D_precomp, "cov3D_precomp")
+    sh = _f32(sh, "shs")
+    background = _f32(background, "bg")
+    viewmatrix = _f32(viewmatrix, "viewmatrix")
+    projmatrix = _f32(projmatrix, "projmatrix")
+    campos = _f32(campos, "campos")
+    n_ch = _channels(colors)
+    background = _pad_bg(background, n_ch)
+    if tile_mask is not None and tile_mask.numel() != 0:
+        if not tile_mask.is_cuda:
+            raise RuntimeError("tile_mask must be a CUDA tensor")
+        tile_mask = tile_mask.to(torch.bool).contiguous()
+        tiles = ((H + 15) // 16) * ((W + 15) // 16)
+        if tile_mask.numel() != tiles:
+            raise RuntimeError(f"tile_mask must have {tiles} elements, got {tile_mask.numel()}")
+    M = int(sh.shape[1]) if sh.numel() != 0 else 0
+
+    with torch.cuda.device(dev):
+        f_opts = dict(dtype=torch.float32, device=dev)
+        out_color = torch.empty((n_ch, H, W), **f_opts)
+        out_depth = torch.empty((1, H, W), **f_opts)
+        out_alpha = torch.empty((1, H, W), **f_opts)
+        radii = torch.empty((P,), dtype=torch.int32, device=dev)
+        geom, binning, img = _Chunk(dev), _Chunk(dev), _Chunk(dev)
+        rendered = 0
+        rc = lib.sl_forward(
+            geom.callback, None, binning.callback, None, img.callback, None,
+            P, int(degree), M, n_ch,
+            _ptr(background), W, H,
+            _ptr(means3D), _ptr(sh), _ptr(colors),
+            _ptr(opacity), _ptr(scales), float(scale_modifier),
+            _ptr(rotations), _ptr(cov3D_precomp), _ptr(tile_mask),
+            _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos),
+            float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+            _ptr(out_color), _ptr(out_depth), _ptr(out_alpha), _ptr(radii),
+            int(bool(debug)), _stream(dev))
+        rendered = _capi.check(rc)
+    return rendered, out_color, out_depth, out_alpha, radii, geom.tensor, binning.tensor, img.tensor
+
+
+def _grad_block(P: int, widths: list[int], device) -> list[torch.Tensor]:
+    """One zero-filled allocation (one memset) carved into per-gradient blocks."""
+    sizes = [(P * w + 3) // 4 * 4 for w in widths]  # keep every block 16-byte aligned
+    flat = torch.zeros(sum(sizes), dtype=torch.float32, device=device)
+    out, off = [], 0
+    for w, s in zip(widths, sizes):
+        out.append(flat[off:off + P * w])
+        off += s
+    return out
+
+
+def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                 cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
+                                 dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
+                                 geomBuffer, R, binningBuffer, imageBuffer, out_alpha, debug):
+    """-> (dL_dabsmeans2D, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
+           dL_dsh, dL_dscales, dL_drotations)."""
+    lib = _capi.load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    H, W = int(dL_dout_color.shape[1]), int(dL_dout_color.shape[2])
+    n_ch = int(dL_dout_color.shape[0])
+    M = int(sh.shape[1]) if sh.numel() != 0 else 0
+
+    means3D = _f32(means3D, "means3D")
+    colors = _f32(colors, "colors_precomp")
+    scales = _f32(scales, "scales")
+    rotations = _f32(rotations, "rotations")
+    cov3D_precomp = _f32(cov3D_precomp, "cov3D_precomp")
+    sh = _f32(sh, "shs")
+    dL_dout_color = _f32(dL_dout_color, "dL_dout_color")
+    dL_dout_depth = _f32(dL_dout_depth, "dL_dout_depth")
+    dL_dout_alpha = _f32(dL_dout_alpha, "dL_dout_alpha")
+    out_alpha = _f32(out_alpha, "out_alpha")
+    background = _pad_bg(_f32(background, "bg"), n_ch)
+    viewmatrix = _f32(viewmatrix, "viewmatrix")
+    projmatrix = _f32(projmatrix, "projmatrix")
+    campos = _f32(campos, "campos")
+    radii = radii.contiguous()
+
+    with torch.cuda.device(dev):
+        (g_mean3D, g_mean2D, g_abs2D, g_color, g_depth, g_conic, g_opac, g_cov3D, g_sh, g_scale,
+         g_rot) = _grad_block(P, [3, 3, 3, n_ch, 1, 4, 1, 6, 3 * M, 3, 4], dev)
+        if P != 0:
+            rc = lib.sl_backward(
+                P, int(degree), M, int(R), n_ch,
+                _ptr(background), W, H,
+                _ptr(means3D), _ptr(sh), _ptr(colors),
+                _ptr(scales), float(scale_modifier), _ptr(rotations),
+                _ptr(cov3D_precomp), _ptr(viewmatrix), _ptr(projmatrix),
+                _ptr(campos), float(tan_fovx), float(tan_fovy), _ptr(radii),
+                _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
+                _ptr(out_alpha), _ptr(dL_dout_color), _ptr(dL_dout_depth), _ptr(dL_dout_alpha),
+                g_mean2D.data_ptr(), g_abs2D.data_ptr(), g_conic.data_ptr(), g_opac.data_ptr(),
+                g_color.data_ptr(), g_depth.data_ptr(), g_mean3D.data_ptr(), g_cov3D.data_ptr(),
+                _ptr(g_sh), g_scale.data_ptr(), g_rot.data_ptr(),
+                int(bool(debug)), _stream(dev))
+            _capi.check(rc)
+    return (g_abs2D.view(P, 3), g_mean2D.view(P, 3), g_color.view(P, n_ch), g_opac.view(P, 1),
+            g_mean3D.view(P, 3), g_cov3D.view(P, 6), g_sh.view(P, M, 3), g_scale.view(P, 3),
+            g_rot.view(P, 4))
+
+
+def mark_visible(means3D, viewmatrix, projmatrix):
+    """-> bool tensor (P,): inside the padded view frustum."""
+    lib = _capi.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (the rasterizer has no CPU path)")
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    present = torch.empty((P,), dtype=torch.bool, device=dev)
+    if P != 0:
+        means3D = _f32(means3D, "means3D")
+        viewmatrix = _f32(viewmatrix, "viewmatrix")
+        projmatrix = _f32(projmatrix, "projmatrix")
+        with torch.cuda.device(dev):
+            _capi.check(lib.sl_mark_visible(P, _ptr(means3D), _ptr(viewmatrix), _ptr(projmatrix),
+                                            present.data_ptr(), _stream(dev)))
+    return present
+
+
+def distCUDA2(points):
+    """-> float tensor (P,): mean squared distance to the 3 nearest neighbours."""
+    lib = _capi.load()
+    if not points.is_cuda:
+        raise RuntimeError("points must be a CUDA tensor (distCUDA2 has no CPU path)")
+    dev = points.device
+    P = int(points.shape[0])
+    means = torch.zeros((P,), dtype=torch.float32, device=dev)
+    if P != 0:
+        points = _f32(points, "points")
+        with torch.cuda.device(dev):
+            nbytes = int(lib.sl_knn_scratch_bytes(P))
+            scratch = torch.empty(nbytes, dtype=torch.uint8, device=dev)
+            _capi.check(lib.sl_knn(P, _ptr(points), means.data_ptr(), scratch.data_ptr(), nbytes, _stream(dev)))
+    return means

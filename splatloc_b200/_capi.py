@@ -1,0 +1,85 @@
+"""ctypes binding of libsplatloc_b200.so (the C ABI in include/splatloc_b200.h).
+
+This is the only place the shared library is loaded.  There is no fallback: if
+the library is missing or a CUDA device is absent, the product path raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libsplatloc_b200.so")
+
+ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
+
+_F = C.c_void_p  # every device pointer travels as an integer address
+
+# name -> (restype, argtypes); kept in sync with include/splatloc_b200.h and
+# checked against the header's declarations by tests/test_capi_symbols.py.
+SIGNATURES = {
+    "sl_version": (C.c_char_p, []),
+    "sl_last_error": (C.c_char_p, []),
+    "sl_geometry_bytes": (C.c_size_t, [C.c_int]),
+    "sl_binning_bytes": (C.c_size_t, [C.c_int]),
+    "sl_image_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "sl_forward": (C.c_int, [
+        ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p,
+        C.c_int, C.c_int, C.c_int, C.c_int,          # P, D, M, C
+        _F, C.c_int, C.c_int,                        # background, width, height
+        _F, _F, _F,                                  # means3D, shs, colors_precomp
+        _F, _F, C.c_float,                           # opacities, scales, scale_modifier
+        _F, _F, _F,                                  # rotations, cov3D_precomp, tile_mask
+        _F, _F, _F,                                  # viewmatrix, projmatrix, cam_pos
+        C.c_float, C.c_float, C.c_int,               # tan_fovx, tan_fovy, prefiltered
+        _F, _F, _F, _F,                              # out_color, out_depth, out_alpha, radii
+        C.c_int, C.c_void_p,                         # debug, stream
+    ]),
+    "sl_backward": (C.c_int, [
+        C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # P, D, M, R, C
+        _F, C.c_int, C.c_int,                        # background, width, height
+        _F, _F, _F,                                  # means3D, shs, colors_precomp
+        _F, C.c_float, _F,                           # scales, scale_modifier, rotations
+        _F, _F, _F,                                  # cov3D_precomp, viewmatrix, projmatrix
+        _F, C.c_float, C.c_float, _F,                # campos, tan_fovx, tan_fovy, radii
+        _F, _F, _F,                                  # geometry, binning, image chunks
+        _F, _F, _F, _F,                              # accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha
+        _F, _F, _F, _F,                              # dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity
+        _F, _F, _F, _F,                              # dL_dcolor, dL_ddepth, dL_dmean3D, dL_dcov3D
+        _F, _F, _F,                                  # dL_dsh, dL_dscale, dL_drot
+        C.c_int, C.c_void_p,                         # debug, stream
+    ]),
+    "sl_mark_visible": (C.c_int, [C.c_int, _F, _F, _F, _F, C.c_void_p]),
+    "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
+    "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),
+}
+
+_lib = None
+
+
+def load() -> C.CDLL:
+    """Load the library once; raise (never fall back) when it is not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m splatloc_b200.build` "
+                "(there is no CPU or PyTorch fallback for the rasterizer)")
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = lib
+    return _lib
+
+
+def last_error() -> str:
+    return load().sl_last_error().decode("utf-8", "replace")
+
+
+def check(rc: int) -> int:
+    """Raise RuntimeError with the library's message on a negative return code."""
+    if rc < 0:
+        raise RuntimeError(last_error() or f"libsplatloc_b200 error {rc}")
+    return rc

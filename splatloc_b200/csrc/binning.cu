@@ -1,0 +1,79 @@
+// splatloc_b200/csrc/binning.cu
+//
+// K3  emit one (tile | depth) key and Gaussian id per overlapped tile
+//     (reference: duplicateWithKeys, cuda_rasterizer/rasterizer_impl.cu:70-132).
+//     Pairs are written at the Gaussian's prefix-sum offset in row-major tile
+//     order, so the emission order -- and with it the tie-break of the stable
+//     sort -- is the reference's.
+// K5  per-tile [first, last+1) ranges in the sorted list
+//     (reference: identifyTileRanges, rasterizer_impl.cu:137-159).
+#include "kernels.h"
+
+namespace sl {
+
+__global__ void __launch_bounds__(256)
+emit_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                  const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
+                  const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y,
+                  uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    const int r = radii[idx];
+    if (r <= 0) return;
+
+    uint32_t off = (idx == 0) ? 0 : offsets[idx - 1];
+    const uint32_t end = offsets[idx];
+    if (off == end) return;  // visible radius but nothing to emit (masked out)
+    const float2 xy = means2D[idx];
+    uint2 rmin, rmax;
+    tile_rect(xy.x, xy.y, r, grid_x, grid_y, rmin, rmax);
+    const uint64_t depth_bits = __float_as_uint(depths[idx]);
+
+    for (uint32_t y = rmin.y; y < rmax.y; y++) {
+        for (uint32_t x = rmin.x; x < rmax.x; x++) {
+            uint64_t key = y * grid_x + x;
+            if (tile_mask != nullptr && !tile_mask[key]) continue;
+            key <<= 32;
+            key |= depth_bits;
+            keys[off] = key;
+            vals[off] = idx;
+            off++;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+tile_ranges_kernel(int L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= L) return;
+    const uint32_t cur = (uint32_t)(keys[idx] >> 32);
+    if (idx == 0) {
+        ranges[cur].x = 0;
+    } else {
+        const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
+        if (cur != prev) {
+            ranges[prev].y = idx;
+            ranges[cur].x = idx;
+        }
+    }
+    if (idx == L - 1) ranges[cur].y = L;
+}
+
+int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
+                      int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream)
+{
+    emit_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
+                                                            tile_mask, grid_x, grid_y, keys, vals);
+    return 0;
+}
+
+int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_tiles, cudaStream_t stream)
+{
+    SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream), "ranges memset");
+    if (R > 0) tile_ranges_kernel<<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, ranges);
+    return 0;
+}
+
+}  // namespace sl

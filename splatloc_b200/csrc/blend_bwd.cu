@@ -1,0 +1,282 @@
+// splatloc_b200/csrc/blend_bwd.cu
+//
+// K7  backward alpha blending (reference: renderCUDA in
+//     cuda_rasterizer/backward.cu:1018-1209).  Same per-pixel recurrences and
+//     per-term arithmetic as the reference, walked back to front over the first
+//     n_contrib entries of the tile's list; what changes is how the 9 + C
+//     per-Gaussian partial gradients leave the CTA.
+//
+//     The reference issues 9 + C global float atomics per blended
+//     (pixel, Gaussian) pair.  Here a warp owns an 8x4 pixel patch; for every
+//     Gaussian that at least one of its 32 pixels blends, the partials are
+//     reduced across the warp with a 16-shuffle transpose-reduction (16 values,
+//     halving the live set at each of the 5 butterfly levels) and the 9 + C sums
+//     leave the warp as one `red.global.add.f32` per value, issued by 9 + C
+//     different lanes.  Warps none of whose pixels blend the Gaussian skip it on
+//     a ballot.  Global atomic traffic drops from (9+C) per blended pixel pair
+//     to at most 8 x (9+C) per (tile, Gaussian) pair.
+//
+//     Channel rule kept from the fork: channels >= 3 do not feed dL/dalpha
+//     (backward.cu:1153-1154) but do receive colour gradients.
+#include "kernels.h"
+
+namespace sl {
+
+namespace {
+
+constexpr unsigned FULL = 0xffffffffu;
+
+// Sum 16 per-lane values across the warp.  On return lane L holds in the result the
+// warp-wide total of value (L >> 1).
+__device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lane)
+{
+    {
+        const bool up = lane & 16;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+            const float send = up ? v[k] : v[k + 8];
+            const float keep = up ? v[k + 8] : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 16);
+        }
+    }
+    {
+        const bool up = lane & 8;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const float send = up ? v[k] : v[k + 4];
+            const float keep = up ? v[k + 4] : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 8);
+        }
+    }
+    {
+        const bool up = lane & 4;
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const float send = up ? v[k] : v[k + 2];
+            const float keep = up ? v[k + 2] : v[k];
+            v[k] = keep + __shfl_xor_sync(FULL, send, 4);
+        }
+    }
+    {
+        const bool up = lane & 2;
+        const float send = up ? v[0] : v[1];
+        const float keep = up ? v[1] : v[0];
+        v[0] = keep + __shfl_xor_sync(FULL, send, 2);
+    }
+    return v[0] + __shfl_xor_sync(FULL, v[0], 1);
+}
+
+}  // namespace
+
+template <int C>
+__global__ void __launch_bounds__(SL_TILE_PIX)
+blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                      int W, int H, int grid_x, const float* __restrict__ bg,
+                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
+                      const float* __restrict__ colors, const float* __restrict__ depths,
+                      const float* __restrict__ out_alpha, const uint32_t* __restrict__ n_contrib,
+                      const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
+                      const float* __restrict__ dL_dpix_alpha,
+                      float* __restrict__ dL_dmean2D,     // (P,3)
+                      float* __restrict__ dL_dabsmean2D,  // (P,3)
+                      float* __restrict__ dL_dconic,      // (P,4)
+                      float* __restrict__ dL_dopacity,    // (P,1)
+                      float* __restrict__ dL_dcolor,      // (P,C)
+                      float* __restrict__ dL_ddepth)      // (P,1)
+{
+    __shared__ int s_id[SL_TILE_PIX];
+    __shared__ float4 s_xyd[SL_TILE_PIX];
+    __shared__ float4 s_co[SL_TILE_PIX];
+    __shared__ float4 s_col[SL_TILE_PIX];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    const int px = tile_x * SL_TILE_X + (warp & 1) * 8 + (lane & 7);
+    const int py = tile_y * SL_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const uint32_t pix_id = (uint32_t)W * py + px;
+    const float pixf_x = (float)px, pixf_y = (float)py;
+
+    const uint2 range = ranges[tile];
+    const int total = range.y - range.x;
+    const int rounds = (total + SL_TILE_PIX - 1) / SL_TILE_PIX;
+    int todo = total;
+
+    const float T_final = inside ? (1 - out_alpha[pix_id]) : 0;
+    float T = T_final;
+    uint32_t contributor = todo;
+    const int last_contributor = inside ? n_contrib[pix_id] : 0;
+
+    float accum_rec[C];
+    float last_color[C];
+    float dL_dpixel[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) {
+        accum_rec[ch] = 0.f;
+        last_color[ch] = 0.f;
+        dL_dpixel[ch] = inside ? dL_dpix[(size_t)ch * H * W + pix_id] : 0.f;
+    }
+    float accum_red = 0.f, accum_rea = 0.f;
+    const float dL_dpixel_depth = inside ? dL_dpix_depth[pix_id] : 0.f;
+    const float dL_dpixel_alpha = inside ? dL_dpix_alpha[pix_id] : 0.f;
+    float last_alpha = 0.f, last_depth = 0.f;
+
+    float bg_dot_dpixel = 0.f;
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) bg_dot_dpixel += bg[ch] * dL_dpixel[ch];
+
+    const float ddelx_dx = 0.5 * W;
+    const float ddely_dy = 0.5 * H;
+
+    // Which output this lane flushes after a warp reduction: value index lane >> 1.
+    //   0..C-1 colour | C depth | C+1,C+2 mean2D x,y | C+3,C+4 |mean2D| x,y |
+    //   C+5..C+7 conic xx,xy,yy | C+8 opacity
+    float* flush_base = nullptr;
+    int flush_stride = 0;
+    {
+        const int v = lane >> 1;
+        if ((lane & 1) == 0) {
+            if (v < C) { flush_base = dL_dcolor + v; flush_stride = C; }
+            else if (v == C) { flush_base = dL_ddepth; flush_stride = 1; }
+            else if (v == C + 1) { flush_base = dL_dmean2D; flush_stride = 3; }
+            else if (v == C + 2) { flush_base = dL_dmean2D + 1; flush_stride = 3; }
+            else if (v == C + 3) { flush_base = dL_dabsmean2D; flush_stride = 3; }
+            else if (v == C + 4) { flush_base = dL_dabsmean2D + 1; flush_stride = 3; }
+            else if (v == C + 5) { flush_base = dL_dconic; flush_stride = 4; }
+            else if (v == C + 6) { flush_base = dL_dconic + 1; flush_stride = 4; }
+            else if (v == C + 7) { flush_base = dL_dconic + 3; flush_stride = 4; }
+            else if (v == C + 8) { flush_base = dL_dopacity; flush_stride = 1; }
+        }
+    }
+
+    // Entries at list positions >= the warp's largest n_contrib are never blended by it.
+    int warp_last = last_contributor;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(FULL, warp_last, o));
+
+    for (int i = 0; i < rounds; ++i, todo -= SL_TILE_PIX) {
+        __syncthreads();
+        const int progress = i * SL_TILE_PIX + tid;
+        if (range.x + progress < range.y) {
+            const int id = point_list[range.y - progress - 1];
+            s_id[tid] = id;
+            const float2 xy = means2D[id];
+            s_xyd[tid] = make_float4(xy.x, xy.y, depths[id], 0.f);
+            s_co[tid] = conic_opacity[id];
+            if (C == 4) {
+                s_col[tid] = reinterpret_cast<const float4*>(colors)[id];
+            } else {
+                float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+                f.x = colors[id * C + 0];
+                if (C > 1) f.y = colors[id * C + 1];
+                if (C > 2) f.z = colors[id * C + 2];
+                s_col[tid] = f;
+            }
+        }
+        __syncthreads();
+
+        const int n = min(SL_TILE_PIX, todo);
+        // list position of batch entry j is (contributor_at_batch_start - 1 - j)
+        for (int j = 0; j < n; ++j) {
+            contributor--;
+            if ((int)contributor >= warp_last) continue;  // warp-uniform
+
+            const float4 xyd = s_xyd[j];
+            const float4 co = s_co[j];
+            const float dx = __fsub_rn(xyd.x, pixf_x);
+            const float dy = __fsub_rn(xyd.y, pixf_y);
+            const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
+            const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
+            const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
+            const float power = __fmaf_rn(s, -0.5f, -t3);
+            const float G = __expf(power);
+            const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
+            const bool blend = ((int)contributor < last_contributor) && !(power > 0.0f) &&
+                               !(alpha < 1.0f / 255.0f);
+            if (!__any_sync(FULL, blend)) continue;
+
+            float v[16];
+#pragma unroll
+            for (int k = 0; k < 16; ++k) v[k] = 0.f;
+
+            if (blend) {
+                T = T / (1.f - alpha);
+                const float w = alpha * T;
+                float dL_dalpha = 0.0f;
+                const float4 f = s_col[j];
+                const float c4[4] = {f.x, f.y, f.z, f.w};
+#pragma unroll
+                for (int ch = 0; ch < C; ++ch) {
+                    const float c = c4[ch];
+                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
+                    last_color[ch] = c;
+                    const float dL_dchannel = dL_dpixel[ch];
+                    const float weight = (ch > 2) ? 0.0f : 1.0f;
+                    dL_dalpha += (c - accum_rec[ch]) * dL_dchannel * weight;
+                    v[ch] = w * dL_dchannel;
+                }
+                const float dep = xyd.z;
+                accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
+                last_depth = dep;
+                dL_dalpha += (dep - accum_red) * dL_dpixel_depth;
+                v[C] = w * dL_dpixel_depth;
+
+                accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
+                dL_dalpha += (1 - accum_rea) * dL_dpixel_alpha;
+
+                dL_dalpha *= T;
+                last_alpha = alpha;
+                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+
+                const float dL_dG = co.w * dL_dalpha;
+                const float gdx = G * dx;
+                const float gdy = G * dy;
+                const float dG_ddelx = -gdx * co.x - gdy * co.y;
+                const float dG_ddely = -gdy * co.z - gdx * co.y;
+                const float gx = dL_dG * dG_ddelx * ddelx_dx;
+                const float gy = dL_dG * dG_ddely * ddely_dy;
+                v[C + 1] = gx;
+                v[C + 2] = gy;
+                v[C + 3] = fabsf(gx);
+                v[C + 4] = fabsf(gy);
+                v[C + 5] = -0.5f * gdx * dx * dL_dG;
+                v[C + 6] = -0.5f * gdx * dy * dL_dG;
+                v[C + 7] = -0.5f * gdy * dy * dL_dG;
+                v[C + 8] = G * dL_dalpha;
+            }
+
+            const float total_v = warp_transpose_reduce16(v, lane);
+            if (flush_base != nullptr) {
+                const int gid = s_id[j];
+                atomicAdd(flush_base + (size_t)gid * flush_stride, total_v);
+            }
+        }
+    }
+}
+
+int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+                          const float* bg, const float2* means2D, const float4* conic_opacity,
+                          const float* colors, const float* depths, const float* out_alpha,
+                          const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,
+                          const float* dL_dpix_alpha, float* dL_dmean2D, float* dL_dabsmean2D,
+                          float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_ddepth,
+                          cudaStream_t stream)
+{
+    const int tiles = vp.grid_x * vp.grid_y;
+    if (C == 4)
+        blend_backward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x, bg,
+            means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
+            dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
+    else if (C == 3)
+        blend_backward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x, bg,
+            means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
+            dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
+    else {
+        set_error("blend_backward: unsupported channel count %d (3 or 4)", C);
+        return -2;
+    }
+    return 0;
+}
+
+}  // namespace sl

@@ -1,0 +1,140 @@
+// splatloc_b200/csrc/blend_fwd.cu
+//
+// K6  forward alpha blending, one CTA per 16x16 tile, one thread per pixel
+//     (reference: renderCUDA, cuda_rasterizer/forward.cu:844-963).
+//
+// Per (pixel, Gaussian) arithmetic is pinned with explicit round-to-nearest
+// intrinsics to the operation sequence the reference compiles to, because the
+// alpha / transmittance thresholds decide the integer output n_contrib:
+//     power = fma(fma(dx, dx*A, (dy*C)*dy), -0.5, -((dx*B)*dy))
+//     alpha = min(0.99, o * __expf(power));   T' = T * (1 - alpha)
+//     acc  += T * (alpha * f)                 (fma)
+// The Gaussian that drives T below 1e-4 is still blended, then the pixel stops
+// (forward.cu:932-949).
+//
+// Layout: a warp owns an 8x4 pixel patch (not two 16-pixel rows) so that whole
+// warps finish -- and skip the inner loop -- earlier; every batch of 256
+// Gaussians stages position, depth, conic/opacity *and* features in shared
+// memory, so the inner loop touches no global memory.
+#include "kernels.h"
+
+namespace sl {
+
+template <int C>
+__global__ void __launch_bounds__(SL_TILE_PIX)
+blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+                     int W, int H, int grid_x,
+                     const float2* __restrict__ means2D, const float* __restrict__ features,
+                     const float* __restrict__ depths, const float4* __restrict__ conic_opacity,
+                     const float* __restrict__ bg, float* __restrict__ out_color,
+                     float* __restrict__ out_depth, float* __restrict__ out_alpha,
+                     uint32_t* __restrict__ n_contrib)
+{
+    __shared__ float4 s_xyd[SL_TILE_PIX];   // x, y, depth, -
+    __shared__ float4 s_co[SL_TILE_PIX];    // conic xx, xy, yy, opacity
+    __shared__ float4 s_col[SL_TILE_PIX];   // up to 4 feature channels
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tile = blockIdx.x;
+    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
+    const int px = tile_x * SL_TILE_X + (warp & 1) * 8 + (lane & 7);
+    const int py = tile_y * SL_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const bool inside = px < W && py < H;
+    const uint32_t pix_id = (uint32_t)W * py + px;
+    const float pixf_x = (float)px, pixf_y = (float)py;
+
+    const uint2 range = ranges[tile];
+    const int rounds = ((int)(range.y - range.x) + SL_TILE_PIX - 1) / SL_TILE_PIX;
+    int todo = range.y - range.x;
+
+    bool done = !inside;
+    float T = 1.0f;
+    uint32_t contributor = 0, last_contributor = 0;
+    float acc[C];
+#pragma unroll
+    for (int ch = 0; ch < C; ++ch) acc[ch] = 0.f;
+    float D = 0.f;
+
+    for (int i = 0; i < rounds; ++i, todo -= SL_TILE_PIX) {
+        if (__syncthreads_count(done) == SL_TILE_PIX) break;
+
+        const int progress = i * SL_TILE_PIX + tid;
+        if (range.x + progress < range.y) {
+            const int id = point_list[range.x + progress];
+            const float2 xy = means2D[id];
+            s_xyd[tid] = make_float4(xy.x, xy.y, depths[id], 0.f);
+            s_co[tid] = conic_opacity[id];
+            if (C == 4) {
+                s_col[tid] = reinterpret_cast<const float4*>(features)[id];
+            } else {
+                float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+                f.x = features[id * C + 0];
+                if (C > 1) f.y = features[id * C + 1];
+                if (C > 2) f.z = features[id * C + 2];
+                s_col[tid] = f;
+            }
+        }
+        __syncthreads();
+
+        // A warp whose 32 pixels are all finished only helps with staging.
+        if (__all_sync(0xffffffffu, done)) continue;
+
+        const int n = min(SL_TILE_PIX, todo);
+        for (int j = 0; !done && j < n; ++j) {
+            contributor++;
+            const float4 xyd = s_xyd[j];
+            const float4 co = s_co[j];
+            const float dx = __fsub_rn(xyd.x, pixf_x);
+            const float dy = __fsub_rn(xyd.y, pixf_y);
+            const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
+            const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
+            const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
+            const float power = __fmaf_rn(s, -0.5f, -t3);
+            if (power > 0.0f) continue;
+
+            const float alpha = fminf(0.99f, __fmul_rn(co.w, __expf(power)));
+            if (alpha < 1.0f / 255.0f) continue;
+            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+
+            const float4 f = s_col[j];
+            acc[0] = __fmaf_rn(T, __fmul_rn(alpha, f.x), acc[0]);
+            if (C > 1) acc[1] = __fmaf_rn(T, __fmul_rn(alpha, f.y), acc[1]);
+            if (C > 2) acc[2] = __fmaf_rn(T, __fmul_rn(alpha, f.z), acc[2]);
+            if (C > 3) acc[3] = __fmaf_rn(T, __fmul_rn(alpha, f.w), acc[3]);
+            D = __fmaf_rn(T, __fmul_rn(alpha, xyd.z), D);
+            T = test_T;
+            last_contributor = contributor;
+            if (test_T < 0.0001f) done = true;
+        }
+    }
+
+    if (inside) {
+        out_alpha[pix_id] = __fsub_rn(1.0f, T);
+        n_contrib[pix_id] = last_contributor;
+#pragma unroll
+        for (int ch = 0; ch < C; ++ch)
+            out_color[(size_t)ch * H * W + pix_id] = __fmaf_rn(bg[ch], T, acc[ch]);
+        out_depth[pix_id] = D;
+    }
+}
+
+int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+                         const float2* means2D, const float* features, const float* depths,
+                         const float4* conic_opacity, const float* bg, float* out_color,
+                         float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream)
+{
+    const int tiles = vp.grid_x * vp.grid_y;
+    if (C == 4)
+        blend_forward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x,
+            means2D, features, depths, conic_opacity, bg, out_color, out_depth, out_alpha, n_contrib);
+    else if (C == 3)
+        blend_forward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x,
+            means2D, features, depths, conic_opacity, bg, out_color, out_depth, out_alpha, n_contrib);
+    else {
+        set_error("blend_forward: unsupported channel count %d (3 or 4)", C);
+        return -2;
+    }
+    return 0;
+}
+
+}  // namespace sl

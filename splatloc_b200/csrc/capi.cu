@@ -1,0 +1,295 @@
+// splatloc_b200/csrc/capi.cu -- the extern "C" surface declared in
+// include/splatloc_b200.h: argument checks, scratch carve-up, stage order.
+//
+// Stage order of the forward follows CudaRasterizer::Rasterizer::forward
+// (cuda_rasterizer/rasterizer_impl.cu:435-582): preprocess -> prefix sum ->
+// read R -> emit pairs -> sort -> tile ranges -> blend; the backward follows
+// Rasterizer::backward (:586-692): blend backward -> per-Gaussian backward.
+// Everything is enqueued on the caller's stream.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include "kernels.h"
+#include "../../include/splatloc_b200.h"
+
+namespace sl {
+
+static thread_local char g_error[512] = "";
+
+void set_error(const char* fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_error, sizeof(g_error), fmt, ap);
+    va_end(ap);
+}
+
+const char* last_error() { return g_error; }
+
+int check_cuda(cudaError_t e, const char* what)
+{
+    if (e == cudaSuccess) return 0;
+    set_error("CUDA error in %s: %s", what, cudaGetErrorString(e));
+    return SL_ERR_CUDA;
+}
+
+int check_stage(bool debug, cudaStream_t stream, const char* what)
+{
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess && debug) e = cudaStreamSynchronize(stream);
+    return check_cuda(e, what);
+}
+
+// Number of bits needed for tile ids: same value as the reference's getHigherMsb
+// (rasterizer_impl.cu:35-50) -- the position of the highest set bit, plus one.
+static int tile_id_bits(uint32_t n)
+{
+    int bits = 0;
+    while (n >> bits) ++bits;
+    return bits;
+}
+
+static ViewParams make_view(int width, int height, float tan_fovx, float tan_fovy, float scale_modifier)
+{
+    ViewParams vp;
+    vp.W = width;
+    vp.H = height;
+    vp.grid_x = (width + SL_TILE_X - 1) / SL_TILE_X;
+    vp.grid_y = (height + SL_TILE_Y - 1) / SL_TILE_Y;
+    vp.tan_fovx = tan_fovx;
+    vp.tan_fovy = tan_fovy;
+    vp.focal_y = height / (2.0f * tan_fovy);
+    vp.focal_x = width / (2.0f * tan_fovx);
+    vp.scale_modifier = scale_modifier;
+    return vp;
+}
+
+}  // namespace sl
+
+using namespace sl;
+
+extern "C" {
+
+const char* sl_version(void) { return "splatloc_b200 0.1 sm_100a"; }
+
+const char* sl_last_error(void) { return last_error(); }
+
+size_t sl_geometry_bytes(int P) { return required_bytes<GeomState>((size_t)(P > 0 ? P : 0)); }
+size_t sl_binning_bytes(int R) { return required_bytes<BinningState>((size_t)(R > 0 ? R : 0)); }
+size_t sl_image_bytes(int width, int height)
+{
+    const size_t gx = (width + SL_TILE_X - 1) / SL_TILE_X, gy = (height + SL_TILE_Y - 1) / SL_TILE_Y;
+    return required_bytes<ImageState>((size_t)width * height, gx * gy);
+}
+
+int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+               sl_alloc_fn binning_alloc, void* binning_ctx,
+               sl_alloc_fn image_alloc, void* image_ctx,
+               int P, int D, int M, int C,
+               const float* background, int width, int height,
+               const float* means3D, const float* shs, const float* colors_precomp,
+               const float* opacities, const float* scales, float scale_modifier,
+               const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+               const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+               float tan_fovx, float tan_fovy, int prefiltered,
+               float* out_color, float* out_depth, float* out_alpha, int* radii,
+               int debug, void* stream_)
+{
+    g_error[0] = 0;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const bool dbg = debug != 0;
+    if (P < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4)) {
+        set_error("sl_forward: bad sizes (P=%d, W=%d, H=%d, C=%d; C must be 3 or 4)", P, width, height, C);
+        return SL_ERR_ARGUMENT;
+    }
+    if (!geometry_alloc || !binning_alloc || !image_alloc || !out_color || !out_depth || !out_alpha ||
+        !background || !viewmatrix || !projmatrix) {
+        set_error("sl_forward: a required pointer is NULL");
+        return SL_ERR_ARGUMENT;
+    }
+    const size_t N = (size_t)width * height;
+    if (P == 0) {
+        // Nothing to draw: all-zero outputs, as the reference binding returns
+        // (rasterize_points.cu:69-72,84).
+        SL_CUDA(cudaMemsetAsync(out_color, 0, N * C * sizeof(float), stream), "forward memset");
+        SL_CUDA(cudaMemsetAsync(out_depth, 0, N * sizeof(float), stream), "forward memset");
+        SL_CUDA(cudaMemsetAsync(out_alpha, 0, N * sizeof(float), stream), "forward memset");
+        return 0;
+    }
+    if (!means3D || !opacities || (!cov3D_precomp && (!scales || !rotations))) {
+        set_error("sl_forward: means3D, opacities and either cov3D_precomp or scales+rotations are required");
+        return SL_ERR_ARGUMENT;
+    }
+    if (C != 3 && colors_precomp == nullptr) {
+        set_error("For non-RGB, provide precomputed Gaussian colors!");
+        return SL_ERR_ARGUMENT;
+    }
+    if (colors_precomp == nullptr && (shs == nullptr || cam_pos == nullptr || M <= 0)) {
+        set_error("sl_forward: without colors_precomp, shs (M > 0) and cam_pos are required");
+        return SL_ERR_ARGUMENT;
+    }
+    if (colors_precomp == nullptr && (D + 1) * (D + 1) > M) {
+        set_error("sl_forward: SH degree %d needs %d coefficients, got M=%d", D, (D + 1) * (D + 1), M);
+        return SL_ERR_ARGUMENT;
+    }
+
+    const ViewParams vp = make_view(width, height, tan_fovx, tan_fovy, scale_modifier);
+    const int n_tiles = vp.grid_x * vp.grid_y;
+
+    char* chunk = geometry_alloc(geometry_ctx, sl_geometry_bytes(P));
+    if (!chunk) { set_error("sl_forward: geometry allocation failed"); return SL_ERR_ALLOC; }
+    GeomState geom = GeomState::from_chunk(chunk, P);
+    if (radii == nullptr) radii = geom.internal_radii;
+
+    char* img_chunk = image_alloc(image_ctx, sl_image_bytes(width, height));
+    if (!img_chunk) { set_error("sl_forward: image allocation failed"); return SL_ERR_ALLOC; }
+    ImageState img = ImageState::from_chunk(img_chunk, N, n_tiles);
+
+    int rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
+                               colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered != 0, radii,
+                               geom, stream);
+    if (rc) return rc;
+    SL_STAGE(dbg, stream, "preprocess");
+
+    rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_desc, geom.counters, stream);
+    if (rc) return rc;
+    SL_STAGE(dbg, stream, "prefix sum");
+
+    // The binning chunk is sized by R, which only the device knows: one blocking read.
+    uint32_t num_rendered = 0;
+    SL_CUDA(cudaMemcpyAsync(&num_rendered, geom.point_offsets + P - 1, sizeof(uint32_t),
+                            cudaMemcpyDeviceToHost, stream), "read R");
+    SL_CUDA(cudaStreamSynchronize(stream), "read R");
+    if (num_rendered >= (1u << 30)) {
+        set_error("sl_forward: %u (tile, Gaussian) pairs exceed the 2^30 limit", num_rendered);
+        return SL_ERR_CAPACITY;
+    }
+    const int R = (int)num_rendered;
+
+    char* bin_chunk = binning_alloc(binning_ctx, sl_binning_bytes(R));
+    if (!bin_chunk) { set_error("sl_forward: binning allocation failed"); return SL_ERR_ALLOC; }
+    BinningState bin = BinningState::from_chunk(bin_chunk, R);
+
+    if (R > 0) {
+        rc = launch_emit_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, bin.point_list_keys_unsorted,
+                               bin.point_list_unsorted, stream);
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "emit pairs");
+
+        rc = launch_sort_pairs(bin.point_list_keys_unsorted, bin.point_list_unsorted, bin.point_list_keys,
+                               bin.point_list, bin.sort, R, 32 + tile_id_bits(n_tiles), stream);
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "sort");
+    }
+
+    rc = launch_tile_ranges(R, bin.point_list_keys, img.ranges, n_tiles, stream);
+    if (rc) return rc;
+    SL_STAGE(dbg, stream, "tile ranges");
+
+    const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
+    rc = launch_blend_forward(C, vp, img.ranges, bin.point_list, geom.means2D, features, geom.depths,
+                              geom.conic_opacity, background, out_color, out_depth, out_alpha, img.n_contrib,
+                              stream);
+    if (rc) return rc;
+    SL_STAGE(dbg, stream, "blend forward");
+    return R;
+}
+
+int sl_backward(int P, int D, int M, int R, int C,
+                const float* background, int width, int height,
+                const float* means3D, const float* shs, const float* colors_precomp,
+                const float* scales, float scale_modifier, const float* rotations,
+                const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                const float* dL_dpix_alpha,
+                float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                float* dL_dsh, float* dL_dscale, float* dL_drot,
+                int debug, void* stream_)
+{
+    g_error[0] = 0;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const bool dbg = debug != 0;
+    if (P < 0 || R < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4)) {
+        set_error("sl_backward: bad sizes (P=%d, R=%d, W=%d, H=%d, C=%d)", P, R, width, height, C);
+        return SL_ERR_ARGUMENT;
+    }
+    if (P == 0) return 0;
+    if (!geometry_chunk || !binning_chunk || !image_chunk || !accum_alphas || !dL_dpix || !dL_dpix_depth ||
+        !dL_dpix_alpha || !dL_dmean2D || !dL_dabsmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
+        !dL_ddepth || !dL_dmean3D || !dL_dcov3D || !means3D || !background || !viewmatrix || !projmatrix) {
+        set_error("sl_backward: a required pointer is NULL");
+        return SL_ERR_ARGUMENT;
+    }
+    if (scales != nullptr && (!rotations || !dL_dscale || !dL_drot)) {
+        set_error("sl_backward: scales given without rotations / dL_dscale / dL_drot");
+        return SL_ERR_ARGUMENT;
+    }
+    if (shs != nullptr && (!dL_dsh || !campos || C != 3)) {
+        set_error("sl_backward: SH gradients need dL_dsh, campos and C == 3");
+        return SL_ERR_ARGUMENT;
+    }
+    const ViewParams vp = make_view(width, height, tan_fovx, tan_fovy, scale_modifier);
+    const int n_tiles = vp.grid_x * vp.grid_y;
+
+    GeomState geom = GeomState::from_chunk(geometry_chunk, P);
+    BinningState bin = BinningState::from_chunk(binning_chunk, R);
+    ImageState img = ImageState::from_chunk(image_chunk, (size_t)width * height, n_tiles);
+    if (radii == nullptr) radii = geom.internal_radii;
+
+    const float* color_ptr = (colors_precomp != nullptr) ? colors_precomp : geom.rgb;
+    int rc = launch_blend_backward(C, vp, img.ranges, bin.point_list, background, geom.means2D,
+                                   geom.conic_opacity, color_ptr, geom.depths, accum_alphas, img.n_contrib,
+                                   dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic,
+                                   dL_dopacity, dL_dcolor, dL_ddepth, stream);
+    if (rc) return rc;
+    SL_STAGE(dbg, stream, "blend backward");
+
+    const float* cov3D_ptr = (cov3D_precomp != nullptr) ? cov3D_precomp : geom.cov3D;
+    rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, scales, rotations, cov3D_ptr,
+                                    viewmatrix, projmatrix, campos, vp, dL_dmean2D, dL_dconic, dL_dmean3D,
+                                    dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream);
+    if (rc) return rc;
+    SL_STAGE(dbg, stream, "preprocess backward");
+    return 0;
+}
+
+int sl_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                    uint8_t* present, void* stream_)
+{
+    g_error[0] = 0;
+    if (P < 0) { set_error("sl_mark_visible: P < 0"); return SL_ERR_ARGUMENT; }
+    if (P == 0) return 0;
+    if (!means3D || !viewmatrix || !projmatrix || !present) {
+        set_error("sl_mark_visible: a required pointer is NULL");
+        return SL_ERR_ARGUMENT;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = launch_mark_visible(P, means3D, viewmatrix, projmatrix, present, stream);
+    if (rc) return rc;
+    SL_STAGE(false, stream, "mark visible");
+    return 0;
+}
+
+size_t sl_knn_scratch_bytes(int P) { return knn_scratch_bytes(P); }
+
+int sl_knn(int P, const float* points, float* mean_dists, char* scratch, size_t scratch_bytes, void* stream_)
+{
+    g_error[0] = 0;
+    if (P < 0) { set_error("sl_knn: P < 0"); return SL_ERR_ARGUMENT; }
+    if (P == 0) return 0;
+    if (!points || !mean_dists || !scratch) { set_error("sl_knn: a required pointer is NULL"); return SL_ERR_ARGUMENT; }
+    if (scratch_bytes < knn_scratch_bytes(P)) {
+        set_error("sl_knn: scratch of %zu bytes is smaller than the %zu required", scratch_bytes, knn_scratch_bytes(P));
+        return SL_ERR_CAPACITY;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = launch_knn(P, points, mean_dists, scratch, stream);
+    if (rc) return rc;
+    SL_STAGE(false, stream, "knn");
+    return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,74 @@
+// splatloc_b200/csrc/kernels.h -- host-side launchers of every stage.
+// Each returns 0 or a negative C-ABI error code (see include/splatloc_b200.h).
+#pragma once
+#include "common.cuh"
+#include "state.cuh"
+
+namespace sl {
+
+struct ViewParams {
+    int W, H;
+    int grid_x, grid_y;
+    float tan_fovx, tan_fovy;
+    float focal_x, focal_y;
+    float scale_modifier;
+};
+
+// K1: per-Gaussian forward preprocess (reference: FORWARD::preprocess, forward.cu:995-1050).
+int launch_preprocess(int P, int D, int M, int C, const float* means3D, const float* scales,
+                      const float* rotations, const float* opacities, const float* shs,
+                      const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
+                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                      const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
+                      cudaStream_t stream);
+
+// K10: frustum visibility (reference: checkFrustum, rasterizer_impl.cu:54-66).
+int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                        uint8_t* present, cudaStream_t stream);
+
+// K2: inclusive prefix sum, single pass with decoupled look-back.
+int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned long long* desc,
+                          uint32_t* ticket, cudaStream_t stream);
+
+// K3: emit (tile | depth) keys and Gaussian ids (reference: duplicateWithKeys, rasterizer_impl.cu:70-132).
+int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
+                      int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
+
+// K4: stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit);
+// result in (keys_out, vals_out); the inputs are preserved.
+int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream);
+
+// K5: per-tile [first, last+1) ranges (reference: identifyTileRanges, rasterizer_impl.cu:137-159).
+int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_tiles, cudaStream_t stream);
+
+// K6: forward alpha blending per 16x16 tile (reference: renderCUDA, forward.cu:844-963).
+int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+                         const float2* means2D, const float* features, const float* depths,
+                         const float4* conic_opacity, const float* bg, float* out_color,
+                         float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream);
+
+// K7: backward blending (reference: BACKWARD::render, backward.cu:1018-1209).
+int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+                          const float* bg, const float2* means2D, const float4* conic_opacity,
+                          const float* colors, const float* depths, const float* out_alpha,
+                          const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,
+                          const float* dL_dpix_alpha, float* dL_dmean2D, float* dL_dabsmean2D,
+                          float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_ddepth,
+                          cudaStream_t stream);
+
+// K8+K9 fused: per-Gaussian backward (reference: BACKWARD::preprocess, backward.cu:1810-1876).
+int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
+                               const float* shs, const uint8_t* clamped, const float* scales,
+                               const float* rotations, const float* cov3D, const float* viewmatrix,
+                               const float* projmatrix, const float* campos, const ViewParams& vp,
+                               const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
+                               float* dL_dcolor, const float* dL_ddepth, float* dL_dcov3D, float* dL_dsh,
+                               float* dL_dscale, float* dL_drot, cudaStream_t stream);
+
+// K11-K15: mean squared distance to the 3 nearest neighbours (reference: SimpleKNN::knn,
+// simple_knn.cu:186-221).  `scratch` must hold knn_scratch_bytes(P) bytes.
+size_t knn_scratch_bytes(int P);
+int launch_knn(int P, const float* points, float* mean_dists, char* scratch, cudaStream_t stream);
+
+}  // namespace sl

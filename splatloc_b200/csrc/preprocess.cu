@@ -1,0 +1,209 @@
+// splatloc_b200/csrc/preprocess.cu
+//
+// K1  forward per-Gaussian preprocess: frustum cull, EWA projection of the 3D
+//     covariance, conic, screen radius, tile rectangle, optional SH -> RGB.
+//     Follows the arithmetic specified by the reference's preprocessCUDA
+//     (cuda_rasterizer/forward.cu:694-839) with computeCov3D (:394-428),
+//     computeCov2D (:347-389) and computeColorFromSH (:20-71).
+// K10 frustum visibility (rasterizer_impl.cu:54-66).
+//
+// One thread per Gaussian, 256 threads per block; the kernel is HBM-bound
+// (44 B in, 8 B + 52 B per visible Gaussian out) and carries no shared state.
+#include "kernels.h"
+#include "sh.cuh"
+
+namespace sl {
+
+// World covariance from scale and (un-normalised, as in the reference) quaternion.
+__device__ __forceinline__ void cov3d_from_scale_rot(const f3 s, float mod, const float4 q, float* cov3D)
+{
+    mat3 S = mat3_cols(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+    S.c[0][0] = mod * s.x;
+    S.c[1][1] = mod * s.y;
+    S.c[2][2] = mod * s.z;
+
+    float r = q.x, x = q.y, y = q.z, z = q.w;
+    mat3 R = mat3_cols(
+        1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+        2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+        2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+
+    mat3 Mx = mul(S, R);
+    mat3 Sigma = mul(transpose(Mx), Mx);
+
+    cov3D[0] = Sigma.c[0][0];
+    cov3D[1] = Sigma.c[0][1];
+    cov3D[2] = Sigma.c[0][2];
+    cov3D[3] = Sigma.c[1][1];
+    cov3D[4] = Sigma.c[1][2];
+    cov3D[5] = Sigma.c[2][2];
+}
+
+// Screen-space covariance (EWA, Zwicker et al. 2002, eq. 29/31) + 0.3 px low-pass.
+__device__ __forceinline__ f3 cov2d_ewa(const f3& mean, float focal_x, float focal_y, float tan_fovx,
+                                        float tan_fovy, const float* cov3D, const float* __restrict__ view)
+{
+    f3 t = xform_4x3(mean, view);
+
+    const float limx = 1.3f * tan_fovx;
+    const float limy = 1.3f * tan_fovy;
+    const float txtz = t.x / t.z;
+    const float tytz = t.y / t.z;
+    t.x = min(limx, max(-limx, txtz)) * t.z;
+    t.y = min(limy, max(-limy, tytz)) * t.z;
+
+    mat3 J = mat3_cols(
+        focal_x / t.z, 0.0f, -(focal_x * t.x) / (t.z * t.z),
+        0.0f, focal_y / t.z, -(focal_y * t.y) / (t.z * t.z),
+        0, 0, 0);
+
+    mat3 Wm = mat3_cols(
+        view[0], view[4], view[8],
+        view[1], view[5], view[9],
+        view[2], view[6], view[10]);
+
+    mat3 T = mul(Wm, J);
+
+    mat3 Vrk = mat3_cols(
+        cov3D[0], cov3D[1], cov3D[2],
+        cov3D[1], cov3D[3], cov3D[4],
+        cov3D[2], cov3D[4], cov3D[5]);
+
+    mat3 cov = mul(mul(transpose(T), transpose(Vrk)), T);
+
+    cov.c[0][0] += 0.3f;
+    cov.c[1][1] += 0.3f;
+    return {cov.c[0][0], cov.c[0][1], cov.c[1][1]};
+}
+
+__global__ void __launch_bounds__(256)
+preprocess_kernel(int P, int D, int M, int C,
+                  const float* __restrict__ means3D,
+                  const float* __restrict__ scales,
+                  const float* __restrict__ rotations,
+                  const float* __restrict__ opacities,
+                  const float* __restrict__ shs,
+                  const float* __restrict__ cov3D_precomp,
+                  const uint8_t* __restrict__ tile_mask,
+                  const float* __restrict__ colors_precomp,
+                  const float* __restrict__ viewmatrix,
+                  const float* __restrict__ projmatrix,
+                  const float* __restrict__ cam_pos,
+                  ViewParams vp, bool prefiltered,
+                  int* __restrict__ radii,
+                  float2* __restrict__ means2D,
+                  float* __restrict__ depths,
+                  float* __restrict__ cov3Ds,
+                  float* __restrict__ rgb,
+                  uint8_t* __restrict__ clamped,
+                  float4* __restrict__ conic_opacity,
+                  uint32_t* __restrict__ tiles_touched)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+
+    // A Gaussian that leaves early keeps radius 0 / 0 tiles and is ignored downstream.
+    radii[idx] = 0;
+    tiles_touched[idx] = 0;
+
+    f3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    f3 p_view = xform_4x3(p_orig, viewmatrix);
+    if (!prefiltered && !in_frustum_ndc(p_orig, projmatrix)) return;
+    if (opacities[idx] < 0.0001f) return;
+
+    float4 p_hom = xform_4x4(p_orig, projmatrix);
+    float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    f3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+
+    const float* cov3D;
+    if (cov3D_precomp != nullptr) {
+        cov3D = cov3D_precomp + idx * 6;
+    } else {
+        f3 s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+        float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        cov3d_from_scale_rot(s, vp.scale_modifier, q, cov3Ds + idx * 6);
+        cov3D = cov3Ds + idx * 6;
+    }
+
+    f3 cov = cov2d_ewa(p_orig, vp.focal_x, vp.focal_y, vp.tan_fovx, vp.tan_fovy, cov3D, viewmatrix);
+
+    float det = (cov.x * cov.z - cov.y * cov.y);
+    if (det <= 0.0f || cov.x <= 0.0f || cov.z <= 0.0f) {
+        radii[idx] = -1;  // degenerate footprint: pruned with zero gradients
+        return;
+    }
+    float det_inv = 1.f / det;
+    f3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+
+    float mid = 0.5f * (cov.x + cov.z);
+    float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
+    float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
+    if (lambda1 <= 0.01 || lambda2 <= 0.01 || lambda1 < lambda2 || (lambda1 / lambda2) > 10000.0) {
+        radii[idx] = -1;
+        return;
+    }
+    float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+
+    float2 point_image = {ndc_to_pix(p_proj.x, vp.W), ndc_to_pix(p_proj.y, vp.H)};
+    uint2 rmin, rmax;
+    tile_rect(point_image.x, point_image.y, (int)my_radius, vp.grid_x, vp.grid_y, rmin, rmax);
+
+    uint32_t touched = (rmax.y - rmin.y) * (rmax.x - rmin.x);
+    if (touched == 0) return;  // off-screen: tiles_touched stays 0, radius stays 0
+
+    if (tile_mask != nullptr) {
+        touched = 0;
+        for (uint32_t y = rmin.y; y < rmax.y; y++)
+            for (uint32_t x = rmin.x; x < rmax.x; x++)
+                if (tile_mask[y * vp.grid_x + x]) touched += 1;
+        if (touched == 0) return;
+    }
+    tiles_touched[idx] = touched;
+
+    conic_opacity[idx] = {conic.x, conic.y, conic.z, opacities[idx]};
+
+    if (colors_precomp == nullptr) {
+        f3 campos = {cam_pos[0], cam_pos[1], cam_pos[2]};
+        f3 result = sh_to_rgb(idx, D, M, p_orig, campos, shs, clamped);
+        rgb[idx * C + 0] = result.x;
+        rgb[idx * C + 1] = result.y;
+        rgb[idx * C + 2] = result.z;
+    }
+
+    depths[idx] = p_view.z;
+    radii[idx] = my_radius;
+    means2D[idx] = point_image;
+}
+
+__global__ void __launch_bounds__(256)
+mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __restrict__ viewmatrix,
+                    const float* __restrict__ projmatrix, uint8_t* __restrict__ present)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P) return;
+    f3 p = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    present[idx] = in_frustum_ndc(p, projmatrix) ? 1 : 0;
+}
+
+int launch_preprocess(int P, int D, int M, int C, const float* means3D, const float* scales,
+                      const float* rotations, const float* opacities, const float* shs,
+                      const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
+                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                      const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
+                      cudaStream_t stream)
+{
+    preprocess_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
+        P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
+        colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, g.means2D, g.depths,
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched);
+    return 0;
+}
+
+int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
+                        uint8_t* present, cudaStream_t stream)
+{
+    mark_visible_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, means3D, viewmatrix, projmatrix, present);
+    return 0;
+}
+
+}  // namespace sl

@@ -1,0 +1,241 @@
+// splatloc_b200/csrc/preprocess_bwd.cu
+//
+// K8+K9 fused per-Gaussian backward.  The reference runs two kernels
+// (computeCov2DCUDA, cuda_rasterizer/backward.cu:534-664, then preprocessCUDA,
+// :949-1015), the second re-reading and += -ing what the first stored; here one
+// thread carries a Gaussian through both and stores each gradient once:
+//   conic grads -> 2D covariance -> 3D covariance (6) and camera-space mean,
+//   + screen-space mean grads through the projection,
+//   + depth grads through the view matrix (row 2),
+//   + optional SH backward (colour -> SH coefficients and view direction),
+//   + optional 3D covariance -> scale / raw quaternion (no normalisation
+//     Jacobian, as in the reference, backward.cu:730).
+// Only Gaussians with radii > 0 are touched; all other rows keep the caller's
+// zeros.  HBM-bound: ~100 B in, 36..64 B out per visible Gaussian.
+#include "kernels.h"
+#include "sh.cuh"
+
+namespace sl {
+
+__global__ void __launch_bounds__(256)
+preprocess_backward_kernel(int P, int D, int M, int C,
+                           const float* __restrict__ means3D, const int* __restrict__ radii,
+                           const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                           const float* __restrict__ scales, const float* __restrict__ rotations,
+                           const float* __restrict__ cov3Ds, const float* __restrict__ view,
+                           const float* __restrict__ proj, const float* __restrict__ campos,
+                           ViewParams vp,
+                           const float* __restrict__ dL_dmean2D,  // (P,3)
+                           const float* __restrict__ dL_dconics,  // (P,4)
+                           float* __restrict__ dL_dmeans,         // (P,3)
+                           const float* __restrict__ dL_dcolor,   // (P,C)
+                           const float* __restrict__ dL_ddepth,   // (P,1)
+                           float* __restrict__ dL_dcov,           // (P,6)
+                           float* __restrict__ dL_dsh,            // (P,M,3)
+                           float* __restrict__ dL_dscale,         // (P,3)
+                           float* __restrict__ dL_drot)           // (P,4)
+{
+    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= P || !(radii[idx] > 0)) return;
+
+    const float* cov3D = cov3Ds + 6 * idx;
+    const f3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    const float h_x = vp.focal_x, h_y = vp.focal_y;
+
+    // ---------------------------------------------------------------- conic -> cov2D -> cov3D, t
+    const f3 dL_dconic = {dL_dconics[4 * idx], dL_dconics[4 * idx + 1], dL_dconics[4 * idx + 3]};
+    f3 t = xform_4x3(mean, view);
+
+    const float limx = 1.3f * vp.tan_fovx;
+    const float limy = 1.3f * vp.tan_fovy;
+    const float txtz = t.x / t.z;
+    const float tytz = t.y / t.z;
+    t.x = min(limx, max(-limx, txtz)) * t.z;
+    t.y = min(limy, max(-limy, tytz)) * t.z;
+
+    const float x_grad_mul = txtz < -limx || txtz > limx ? 0 : 1;
+    const float y_grad_mul = tytz < -limy || tytz > limy ? 0 : 1;
+
+    mat3 J = mat3_cols(h_x / t.z, 0.0f, -(h_x * t.x) / (t.z * t.z),
+                       0.0f, h_y / t.z, -(h_y * t.y) / (t.z * t.z),
+                       0, 0, 0);
+    mat3 Wm = mat3_cols(view[0], view[4], view[8],
+                        view[1], view[5], view[9],
+                        view[2], view[6], view[10]);
+    mat3 Vrk = mat3_cols(cov3D[0], cov3D[1], cov3D[2],
+                         cov3D[1], cov3D[3], cov3D[4],
+                         cov3D[2], cov3D[4], cov3D[5]);
+    mat3 T = mul(Wm, J);
+    mat3 cov2D = mul(mul(transpose(T), transpose(Vrk)), T);
+
+    const float a = cov2D.c[0][0] + 0.3f;
+    const float b = cov2D.c[0][1];
+    const float c = cov2D.c[1][1] + 0.3f;
+
+    const float denom = a * c - b * b;
+    float dL_da = 0, dL_db = 0, dL_dc = 0;
+    const float denom2inv = 1.0f / ((denom * denom) + 0.0000001f);
+
+    float g_cov[6];
+    if (denom2inv != 0) {
+        dL_da = denom2inv * (-c * c * dL_dconic.x + 2 * b * c * dL_dconic.y + (denom - a * c) * dL_dconic.z);
+        dL_dc = denom2inv * (-a * a * dL_dconic.z + 2 * a * b * dL_dconic.y + (denom - a * c) * dL_dconic.x);
+        dL_db = denom2inv * 2 * (b * c * dL_dconic.x - (denom + 2 * b * b) * dL_dconic.y + a * b * dL_dconic.z);
+
+        g_cov[0] = (T.c[0][0] * T.c[0][0] * dL_da + T.c[0][0] * T.c[1][0] * dL_db + T.c[1][0] * T.c[1][0] * dL_dc);
+        g_cov[3] = (T.c[0][1] * T.c[0][1] * dL_da + T.c[0][1] * T.c[1][1] * dL_db + T.c[1][1] * T.c[1][1] * dL_dc);
+        g_cov[5] = (T.c[0][2] * T.c[0][2] * dL_da + T.c[0][2] * T.c[1][2] * dL_db + T.c[1][2] * T.c[1][2] * dL_dc);
+        g_cov[1] = 2 * T.c[0][0] * T.c[0][1] * dL_da + (T.c[0][0] * T.c[1][1] + T.c[0][1] * T.c[1][0]) * dL_db + 2 * T.c[1][0] * T.c[1][1] * dL_dc;
+        g_cov[2] = 2 * T.c[0][0] * T.c[0][2] * dL_da + (T.c[0][0] * T.c[1][2] + T.c[0][2] * T.c[1][0]) * dL_db + 2 * T.c[1][0] * T.c[1][2] * dL_dc;
+        g_cov[4] = 2 * T.c[0][2] * T.c[0][1] * dL_da + (T.c[0][1] * T.c[1][2] + T.c[0][2] * T.c[1][1]) * dL_db + 2 * T.c[1][1] * T.c[1][2] * dL_dc;
+    } else {
+#pragma unroll
+        for (int i = 0; i < 6; i++) g_cov[i] = 0;
+    }
+#pragma unroll
+    for (int i = 0; i < 6; i++) dL_dcov[6 * idx + i] = g_cov[i];
+
+    // gradients w.r.t. the upper 2x3 of T (cov2D = T^T Vrk^T T)
+    const float dL_dT00 = 2 * (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_da +
+                          (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_db;
+    const float dL_dT01 = 2 * (T.c[0][0] * Vrk.c[1][0] + T.c[0][1] * Vrk.c[1][1] + T.c[0][2] * Vrk.c[1][2]) * dL_da +
+                          (T.c[1][0] * Vrk.c[1][0] + T.c[1][1] * Vrk.c[1][1] + T.c[1][2] * Vrk.c[1][2]) * dL_db;
+    const float dL_dT02 = 2 * (T.c[0][0] * Vrk.c[2][0] + T.c[0][1] * Vrk.c[2][1] + T.c[0][2] * Vrk.c[2][2]) * dL_da +
+                          (T.c[1][0] * Vrk.c[2][0] + T.c[1][1] * Vrk.c[2][1] + T.c[1][2] * Vrk.c[2][2]) * dL_db;
+    const float dL_dT10 = 2 * (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_dc +
+                          (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_db;
+    const float dL_dT11 = 2 * (T.c[1][0] * Vrk.c[1][0] + T.c[1][1] * Vrk.c[1][1] + T.c[1][2] * Vrk.c[1][2]) * dL_dc +
+                          (T.c[0][0] * Vrk.c[1][0] + T.c[0][1] * Vrk.c[1][1] + T.c[0][2] * Vrk.c[1][2]) * dL_db;
+    const float dL_dT12 = 2 * (T.c[1][0] * Vrk.c[2][0] + T.c[1][1] * Vrk.c[2][1] + T.c[1][2] * Vrk.c[2][2]) * dL_dc +
+                          (T.c[0][0] * Vrk.c[2][0] + T.c[0][1] * Vrk.c[2][1] + T.c[0][2] * Vrk.c[2][2]) * dL_db;
+
+    // T = W * J
+    const float dL_dJ00 = Wm.c[0][0] * dL_dT00 + Wm.c[0][1] * dL_dT01 + Wm.c[0][2] * dL_dT02;
+    const float dL_dJ02 = Wm.c[2][0] * dL_dT00 + Wm.c[2][1] * dL_dT01 + Wm.c[2][2] * dL_dT02;
+    const float dL_dJ11 = Wm.c[1][0] * dL_dT10 + Wm.c[1][1] * dL_dT11 + Wm.c[1][2] * dL_dT12;
+    const float dL_dJ12 = Wm.c[2][0] * dL_dT10 + Wm.c[2][1] * dL_dT11 + Wm.c[2][2] * dL_dT12;
+
+    const float tz = 1.f / t.z;
+    const float tz2 = tz * tz;
+    const float tz3 = tz2 * tz;
+
+    const float dL_dtx = x_grad_mul * -h_x * tz2 * dL_dJ02;
+    const float dL_dty = y_grad_mul * -h_y * tz2 * dL_dJ12;
+    const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+                         (2 * h_y * t.y) * tz3 * dL_dJ12;
+
+    // back through t = view * mean (rotation part, transposed)
+    f3 g_mean;
+    g_mean.x = view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz;
+    g_mean.y = view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz;
+    g_mean.z = view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz;
+
+    // ---------------------------------------------------------------- screen-space mean -> mean
+    {
+        float4 m_hom = xform_4x4(mean, proj);
+        float m_w = 1.0f / (m_hom.w + 0.0000001f);
+        const float gx = dL_dmean2D[3 * idx], gy = dL_dmean2D[3 * idx + 1];
+        float mul1 = (proj[0] * mean.x + proj[4] * mean.y + proj[8] * mean.z + proj[12]) * m_w * m_w;
+        float mul2 = (proj[1] * mean.x + proj[5] * mean.y + proj[9] * mean.z + proj[13]) * m_w * m_w;
+        f3 g;
+        g.x = (proj[0] * m_w - proj[3] * mul1) * gx + (proj[1] * m_w - proj[3] * mul2) * gy;
+        g.y = (proj[4] * m_w - proj[7] * mul1) * gx + (proj[5] * m_w - proj[7] * mul2) * gy;
+        g.z = (proj[8] * m_w - proj[11] * mul1) * gx + (proj[9] * m_w - proj[11] * mul2) * gy;
+        g_mean.x += g.x;
+        g_mean.y += g.y;
+        g_mean.z += g.z;
+    }
+
+    // ---------------------------------------------------------------- depth -> mean (view row 2)
+    {
+        const float gd = dL_ddepth[idx];
+        float mul3 = view[2] * mean.x + view[6] * mean.y + view[10] * mean.z + view[14];
+        f3 g;
+        g.x = (view[2] - view[3] * mul3) * gd;
+        g.y = (view[6] - view[7] * mul3) * gd;
+        g.z = (view[10] - view[11] * mul3) * gd;
+        g_mean.x += g.x;
+        g_mean.y += g.y;
+        g_mean.z += g.z;
+    }
+
+    // ---------------------------------------------------------------- colour -> SH (+ view direction)
+    if (shs != nullptr) {
+        f3 cp = {campos[0], campos[1], campos[2]};
+        f3 dL_dRGB = {dL_dcolor[idx * C + 0], dL_dcolor[idx * C + 1], dL_dcolor[idx * C + 2]};
+        f3 g = sh_to_rgb_backward(idx, D, M, mean, cp, shs, clamped, dL_dRGB, dL_dsh);
+        g_mean.x += g.x;
+        g_mean.y += g.y;
+        g_mean.z += g.z;
+    }
+    dL_dmeans[3 * idx + 0] = g_mean.x;
+    dL_dmeans[3 * idx + 1] = g_mean.y;
+    dL_dmeans[3 * idx + 2] = g_mean.z;
+
+    // ---------------------------------------------------------------- cov3D -> scale, rotation
+    if (scales != nullptr) {
+        const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        const float r = q.x, x = q.y, y = q.z, z = q.w;
+        mat3 R = mat3_cols(
+            1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
+            2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
+            2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
+        const f3 s = {vp.scale_modifier * scales[3 * idx], vp.scale_modifier * scales[3 * idx + 1],
+                      vp.scale_modifier * scales[3 * idx + 2]};
+        mat3 S = mat3_cols(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
+        S.c[0][0] = s.x;
+        S.c[1][1] = s.y;
+        S.c[2][2] = s.z;
+        mat3 Mx = mul(S, R);
+
+        mat3 dL_dSigma = mat3_cols(
+            g_cov[0], 0.5f * g_cov[1], 0.5f * g_cov[2],
+            0.5f * g_cov[1], g_cov[3], 0.5f * g_cov[4],
+            0.5f * g_cov[2], 0.5f * g_cov[4], g_cov[5]);
+
+        // dSigma/dM = 2 M
+        mat3 M2;
+#pragma unroll
+        for (int cc = 0; cc < 3; ++cc)
+#pragma unroll
+            for (int rr = 0; rr < 3; ++rr) M2.c[cc][rr] = 2.0f * Mx.c[cc][rr];
+        mat3 dL_dM = mul(M2, dL_dSigma);
+
+        mat3 Rt = transpose(R);
+        mat3 dL_dMt = transpose(dL_dM);
+
+        dL_dscale[3 * idx + 0] = Rt.c[0][0] * dL_dMt.c[0][0] + Rt.c[0][1] * dL_dMt.c[0][1] + Rt.c[0][2] * dL_dMt.c[0][2];
+        dL_dscale[3 * idx + 1] = Rt.c[1][0] * dL_dMt.c[1][0] + Rt.c[1][1] * dL_dMt.c[1][1] + Rt.c[1][2] * dL_dMt.c[1][2];
+        dL_dscale[3 * idx + 2] = Rt.c[2][0] * dL_dMt.c[2][0] + Rt.c[2][1] * dL_dMt.c[2][1] + Rt.c[2][2] * dL_dMt.c[2][2];
+
+#pragma unroll
+        for (int rr = 0; rr < 3; ++rr) {
+            dL_dMt.c[0][rr] *= s.x;
+            dL_dMt.c[1][rr] *= s.y;
+            dL_dMt.c[2][rr] *= s.z;
+        }
+
+        float4 dq;
+        dq.x = 2 * z * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * y * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) + 2 * x * (dL_dMt.c[1][2] - dL_dMt.c[2][1]);
+        dq.y = 2 * y * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * z * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * r * (dL_dMt.c[1][2] - dL_dMt.c[2][1]) - 4 * x * (dL_dMt.c[2][2] + dL_dMt.c[1][1]);
+        dq.z = 2 * x * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * r * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) + 2 * z * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * y * (dL_dMt.c[2][2] + dL_dMt.c[0][0]);
+        dq.w = 2 * r * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * x * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * y * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * z * (dL_dMt.c[1][1] + dL_dMt.c[0][0]);
+        reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+    }
+}
+
+int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
+                               const float* shs, const uint8_t* clamped, const float* scales,
+                               const float* rotations, const float* cov3D, const float* viewmatrix,
+                               const float* projmatrix, const float* campos, const ViewParams& vp,
+                               const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
+                               float* dL_dcolor, const float* dL_ddepth, float* dL_dcov3D, float* dL_dsh,
+                               float* dL_dscale, float* dL_drot, cudaStream_t stream)
+{
+    preprocess_backward_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
+        P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrix, projmatrix, campos,
+        vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+    return 0;
+}
+
+}  // namespace sl

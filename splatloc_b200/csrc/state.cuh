@@ -1,0 +1,133 @@
+// splatloc_b200/csrc/state.cuh
+//
+// Carve-up of the three caller-owned scratch chunks (geometry / binning /
+// image).  The leading fields keep the order, element types and 128-byte
+// alignment of the reference's GeometryState / BinningState / ImageState
+// (cuda_rasterizer/rasterizer_impl.h:33-66, rasterizer_impl.cu:393-431) so
+// that the reference's Python buffer interpreters
+// (diff_gauss/__init__.py:399-502) read this library's chunks unchanged; the
+// space the reference gives to CUB temp storage holds this library's own
+// scratch (scan descriptors, radix-sort histograms and ping-pong buffers).
+#pragma once
+#include "common.cuh"
+
+namespace sl {
+
+constexpr int SCAN_ITEMS_PER_BLOCK = 4096;   // 256 threads x 16 items
+constexpr int SORT_ITEMS_PER_BLOCK = 4096;   // 256 threads x 16 keys
+constexpr int SORT_RADIX_BITS = 8;
+constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
+constexpr int SORT_MAX_PASSES = 8;
+
+template <typename T>
+__host__ __device__ inline void carve(char*& chunk, T*& ptr, size_t count, size_t alignment = 128)
+{
+    size_t off = (reinterpret_cast<uintptr_t>(chunk) + alignment - 1) & ~(alignment - 1);
+    ptr = reinterpret_cast<T*>(off);
+    chunk = reinterpret_cast<char*>(ptr + count);
+}
+
+struct GeomState {
+    // --- reference-compatible prefix ---
+    float* depths;            // [P]   view-space z (sort-key low word)
+    uint8_t* clamped;         // [3P]  SH colour clamp flags
+    int* internal_radii;      // [P]   used when the caller passes radii == nullptr
+    float2* means2D;          // [P]   pixel-space centre
+    float* cov3D;             // [6P]  upper triangle of the world covariance
+    float4* conic_opacity;    // [P]   (conic xx, xy, yy, opacity)
+    float* rgb;               // [3P]  SH -> RGB result (C == 3 only)
+    uint32_t* tiles_touched;  // [P]
+    uint32_t* point_offsets;  // [P]   inclusive prefix sum of tiles_touched
+    // --- own scratch ---
+    unsigned long long* scan_desc;  // [scan_blocks] decoupled look-back descriptors
+    uint32_t* counters;             // [8] dynamic block tickets etc.
+    size_t scan_blocks;
+
+    static GeomState from_chunk(char*& chunk, size_t P)
+    {
+        GeomState g;
+        carve(chunk, g.depths, P);
+        carve(chunk, g.clamped, P * 3);
+        carve(chunk, g.internal_radii, P);
+        carve(chunk, g.means2D, P);
+        carve(chunk, g.cov3D, P * 6);
+        carve(chunk, g.conic_opacity, P);
+        carve(chunk, g.rgb, P * 3);
+        carve(chunk, g.tiles_touched, P);
+        carve(chunk, g.point_offsets, P);
+        g.scan_blocks = (P + SCAN_ITEMS_PER_BLOCK - 1) / SCAN_ITEMS_PER_BLOCK;
+        carve(chunk, g.scan_desc, g.scan_blocks + 1);
+        carve(chunk, g.counters, 8);
+        return g;
+    }
+};
+
+struct ImageState {
+    uint32_t* n_contrib;  // [N] last contributing list position per pixel
+    uint2* ranges;        // [Tn] [first, last+1) in the sorted pair list
+
+    static ImageState from_chunk(char*& chunk, size_t N, size_t Tn)
+    {
+        ImageState s;
+        carve(chunk, s.n_contrib, N);
+        carve(chunk, s.ranges, Tn);
+        return s;
+    }
+};
+
+// Scratch of one radix sort of n (u64 key, u32 value) pairs.
+struct SortScratch {
+    uint64_t* keys_tmp;      // [n] ping-pong
+    uint32_t* vals_tmp;      // [n]
+    uint32_t* histograms;    // [SORT_MAX_PASSES * 256] global digit histograms
+    uint32_t* lookback;      // [SORT_MAX_PASSES * sort_blocks * 256]
+    uint32_t* tickets;       // [SORT_MAX_PASSES] dynamic block ids
+    size_t sort_blocks;
+    size_t zero_bytes;       // bytes from `histograms` that must be zeroed per sort
+
+    static SortScratch from_chunk(char*& chunk, size_t n)
+    {
+        SortScratch b;
+        carve(chunk, b.keys_tmp, n);
+        carve(chunk, b.vals_tmp, n);
+        b.sort_blocks = (n + SORT_ITEMS_PER_BLOCK - 1) / SORT_ITEMS_PER_BLOCK;
+        carve(chunk, b.histograms, (size_t)SORT_MAX_PASSES * SORT_RADIX);
+        char* zero_begin = reinterpret_cast<char*>(b.histograms);
+        carve(chunk, b.lookback, (size_t)SORT_MAX_PASSES * b.sort_blocks * SORT_RADIX, 4);
+        carve(chunk, b.tickets, SORT_MAX_PASSES, 4);
+        b.zero_bytes = (size_t)(chunk - zero_begin);
+        return b;
+    }
+    static size_t bytes(size_t n);
+};
+
+struct BinningState {
+    // --- reference-compatible prefix ---
+    uint32_t* point_list;             // [R] sorted Gaussian ids
+    uint32_t* point_list_unsorted;    // [R]
+    uint64_t* point_list_keys;        // [R] sorted (tile << 32 | depth bits)
+    uint64_t* point_list_keys_unsorted;  // [R]
+    // --- own scratch ---
+    SortScratch sort;
+
+    static BinningState from_chunk(char*& chunk, size_t R)
+    {
+        BinningState b;
+        carve(chunk, b.point_list, R);
+        carve(chunk, b.point_list_unsorted, R);
+        carve(chunk, b.point_list_keys, R);
+        carve(chunk, b.point_list_keys_unsorted, R);
+        b.sort = SortScratch::from_chunk(chunk, R);
+        return b;
+    }
+};
+
+template <typename S, typename... A>
+inline size_t required_bytes(A... a)
+{
+    char* p = nullptr;
+    S::from_chunk(p, a...);
+    return reinterpret_cast<size_t>(p) + 128;
+}
+
+}  // namespace sl

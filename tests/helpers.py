@@ -1,0 +1,135 @@
+"""Shared helpers of the parity tests: run a rasterizer back end on a seeded scene and
+collect every output, gradient and integer intermediate in one dict."""
+from __future__ import annotations
+
+import torch
+
+from splatloc_b200 import scenes
+from splatloc_b200.diff_gauss import interpret_binningBuffer, interpret_geomBuffer, interpret_imgBuffer
+
+EMPTY = torch.Tensor([])
+
+
+def scene_inputs(P, seed, cam_seed=None, channels=4, sh_degree=None, intrinsics=None, size=None,
+                 device="cuda", use_cov3d=False, tile_mask_seed=None, bg=None):
+    sc = scenes.make_scene(P, seed, channels=channels, sh_degree=sh_degree)
+    cam = scenes.make_camera(seed if cam_seed is None else cam_seed, intrinsics=intrinsics, size=size)
+    C = 3 if sh_degree is not None else channels
+    d = {k: v.to(device) for k, v in sc.items()}
+    d["cam"] = cam.to(device)
+    d["C"] = C
+    d["sh_degree"] = 0 if sh_degree is None else sh_degree
+    d["bg"] = (torch.zeros(C) if bg is None else torch.tensor(bg, dtype=torch.float32)).to(device)
+    if use_cov3d:
+        d["cov3D_precomp"] = cov3d_from(sc["scales"], sc["rotations"]).to(device)
+    if tile_mask_seed is not None:
+        g = torch.Generator().manual_seed(tile_mask_seed)
+        ty, tx = (cam.H + 15) // 16, (cam.W + 15) // 16
+        d["tile_mask"] = (torch.rand((ty, tx), generator=g) < 0.6).to(device)
+    gc, gd, ga = scenes.make_pixel_grads(seed, C, cam.H, cam.W, normalised=False)
+    d["grads"] = (gc.to(device), gd.to(device), ga.to(device))
+    return d
+
+
+def cov3d_from(scales, rotations):
+    """(P,6) upper triangle of R S S^T R^T in float32 torch (input generator for cov3D_precomp runs)."""
+    r, x, y, z = rotations.unbind(1)
+    R = torch.stack([
+        1 - 2 * (y * y + z * z), 2 * (x * y - r * z), 2 * (x * z + r * y),
+        2 * (x * y + r * z), 1 - 2 * (x * x + z * z), 2 * (y * z - r * x),
+        2 * (x * z - r * y), 2 * (y * z + r * x), 1 - 2 * (x * x + y * y)], dim=1).view(-1, 3, 3)
+    L = R * scales[:, None, :]
+    S = L @ L.transpose(1, 2)
+    return torch.stack([S[:, 0, 0], S[:, 0, 1], S[:, 0, 2], S[:, 1, 1], S[:, 1, 2], S[:, 2, 2]], dim=1).contiguous()
+
+
+def run_backend(be, d, debug=False, backward=True):
+    """`be` exposes rasterize_gaussians / rasterize_gaussians_backward with the reference's
+    pybind signatures (splatloc_b200._C or oracle.ref_cuda).  Returns a dict of CPU tensors."""
+    cam = d["cam"]
+    colors = d.get("colors_precomp", EMPTY)
+    shs = d.get("shs", EMPTY)
+    use_cov = "cov3D_precomp" in d
+    scales = EMPTY if use_cov else d["scales"]
+    rots = EMPTY if use_cov else d["rotations"]
+    cov = d["cov3D_precomp"] if use_cov else EMPTY
+    tm = d.get("tile_mask", EMPTY.bool())
+    P = d["means3D"].shape[0]
+    R, color, depth, alpha, radii, geom, binning, img = be.rasterize_gaussians(
+        d["bg"], d["means3D"], colors, d["opacities"], scales, rots, 1.0, cov, tm, cam.viewmatrix,
+        cam.projmatrix, cam.tanfovx, cam.tanfovy, cam.H, cam.W, shs, d["sh_degree"], cam.campos, False, debug)
+    out = dict(R=R, color=color, depth=depth, alpha=alpha, radii=radii)
+    if P > 0:
+        g = interpret_geomBuffer(geom, P)
+        vis = radii > 0
+        out["tiles_touched"] = g["tiles_touched"]
+        out["point_offsets"] = g["point_offsets"]
+        # per-Gaussian intermediates are only defined where the Gaussian survived preprocess
+        out["depths_vis"] = g["depths"][vis].view(torch.int32)
+        out["means2D_vis"] = g["means2D"][vis].view(torch.int32)
+        out["conic_opacity_vis"] = g["conic_opacity"][vis]
+        if not use_cov:
+            out["cov3D_vis"] = g["cov3D"][vis]
+        if shs.numel():
+            out["rgb_vis"] = g["rgb"][vis]
+            out["clamped_vis"] = g["clamped"][vis]
+        n_tiles = ((cam.H + 15) // 16) * ((cam.W + 15) // 16)
+        im = interpret_imgBuffer(img, cam.H * cam.W, n_tiles)
+        out["n_contrib"] = im["n_contrib"]
+        out["ranges"] = im["ranges"]
+        if R > 0:
+            b = interpret_binningBuffer(binning, R)
+            out["keys_unsorted"] = b["point_list_keys_unsorted"]
+            out["vals_unsorted"] = b["point_list_unsorted"]
+            out["keys_sorted"] = b["point_list_keys"]
+            out["point_list"] = b["point_list"]
+    if backward:
+        gc, gd, ga = d["grads"]
+        names = ("g_abs2D", "g_means2D", "g_colors", "g_opacity", "g_means3D", "g_cov3D", "g_sh", "g_scales", "g_rot")
+        res = be.rasterize_gaussians_backward(
+            d["bg"], d["means3D"], radii, colors, scales, rots, 1.0, cov, cam.viewmatrix, cam.projmatrix,
+            cam.tanfovx, cam.tanfovy, gc, gd, ga, shs, d["sh_degree"], cam.campos, geom, R, binning, img,
+            alpha, debug)
+        out.update(dict(zip(names, res)))
+    torch.cuda.synchronize()
+    return {k: (v.detach().cpu().clone() if isinstance(v, torch.Tensor) else v) for k, v in out.items()}
+
+
+INT_KEYS = ("radii", "tiles_touched", "point_offsets", "depths_vis", "means2D_vis", "n_contrib", "ranges",
+            "keys_unsorted", "vals_unsorted", "keys_sorted", "point_list", "clamped_vis")
+FLOAT_KEYS = ("color", "depth", "alpha", "conic_opacity_vis", "cov3D_vis", "rgb_vis")
+GRAD_KEYS = ("g_abs2D", "g_means2D", "g_colors", "g_opacity", "g_means3D", "g_cov3D", "g_sh", "g_scales", "g_rot")
+
+# north_star tolerance for fp32 outputs and gradients
+RTOL, ATOL = 1e-4, 1e-5
+
+
+def compare(a, b, rtol=RTOL, atol=ATOL, grad_scale_aware=True):
+    """Return a list of mismatch descriptions between two run_backend() dicts (a = ours, b = golden)."""
+    bad = []
+    if a["R"] != b["R"]:
+        bad.append(f"R {a['R']} != {b['R']}")
+    for k in INT_KEYS:
+        if k in b:
+            if k not in a or a[k].shape != b[k].shape:
+                bad.append(f"{k}: shape {None if k not in a else tuple(a[k].shape)} vs {tuple(b[k].shape)}")
+            elif not torch.equal(a[k], b[k]):
+                n = int((a[k] != b[k]).sum())
+                bad.append(f"{k}: {n}/{b[k].numel()} integer mismatches")
+    for k in FLOAT_KEYS + GRAD_KEYS:
+        if k in b:
+            if k not in a or a[k].shape != b[k].shape:
+                bad.append(f"{k}: shape mismatch")
+                continue
+            x, y = a[k].double(), b[k].double()
+            if x.numel() == 0:
+                continue
+            # gradients are sums of many atomically-added terms: scale atol with the tensor's magnitude
+            at = atol * max(1.0, float(y.abs().max())) if (grad_scale_aware and k in GRAD_KEYS) else atol
+            err = (x - y).abs()
+            tol = at + rtol * y.abs()
+            nbad = int((err > tol).sum())
+            if nbad or not torch.isfinite(x).all():
+                bad.append(f"{k}: {nbad}/{y.numel()} outside tol, max err {float(err.max()):.3e}, "
+                           f"max ref {float(y.abs().max()):.3e}")
+    return bad

@@ -1,0 +1,116 @@
+"""GPU parity: libsplatloc_b200 (through the C ABI) against the unmodified reference CUDA
+rasterizer compiled into oracle/_ref (same inputs, same GPU).  Integer outputs and the
+floats that feed them must be bit-identical; fp32 images and gradients within
+rtol 1e-4 / atol 1e-5 (north_star)."""
+import pytest
+import torch
+
+from tests import helpers as H
+
+pytestmark = pytest.mark.gpu
+
+
+def _ref():
+    from oracle import ref_cuda
+    if not ref_cuda.available():
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    return ref_cuda
+
+
+def _ours():
+    from splatloc_b200 import _C
+    return _C
+
+
+CASES = [
+    dict(P=3000, seed=1, size=(160, 120)),
+    dict(P=20000, seed=2, size=(320, 240)),
+    dict(P=20000, seed=3, size=(300, 200)),            # image sizes that are not tile multiples
+    dict(P=20000, seed=4, size=(320, 240), use_cov3d=True),
+    dict(P=20000, seed=5, size=(320, 240), tile_mask_seed=7),
+    dict(P=20000, seed=6, size=(320, 240), bg=[0.3, 0.5, 0.7, 0.2]),
+    dict(P=60000, seed=7, channels=3, size=(320, 240), bg=[1.0, 1.0, 1.0]),
+    dict(P=20000, seed=8, sh_degree=3, size=(320, 240)),
+    dict(P=20000, seed=9, sh_degree=1, size=(320, 240), bg=[0.1, 0.2, 0.3]),
+    dict(P=200000, seed=0),                            # config-1-sized, C=4
+]
+
+
+@pytest.mark.parametrize("case", CASES, ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items() if k != "bg"))
+def test_matches_reference_cuda(case):
+    ref, ours = _ref(), _ours()
+    d = H.scene_inputs(**case)
+    b = H.run_backend(ref, d)
+    a = H.run_backend(ours, d)
+    assert b["R"] > 0
+    bad = H.compare(a, b)
+    assert not bad, "\n".join(bad)
+
+
+def test_empty_and_invisible():
+    ours = _ours()
+    # P == 0 -> zero outputs, R == 0
+    d = H.scene_inputs(10, 0, size=(64, 48))
+    for k in ("means3D", "scales", "rotations", "opacities", "colors_precomp"):
+        d[k] = d[k][:0]
+    a = H.run_backend(ours, d)
+    assert a["R"] == 0 and float(a["color"].abs().max()) == 0.0
+    # every Gaussian behind the camera -> R == 0, background everywhere, zero gradients
+    d = H.scene_inputs(500, 0, size=(64, 48), bg=[0.25, 0.5, 0.75, 1.0])
+    cam = d["cam"]
+    fwd = cam.viewmatrix[:3, 2]
+    d["means3D"] = (cam.campos[None, :] - 5.0 * fwd[None, :] + 0.01 * torch.randn_like(d["means3D"])).contiguous()
+    a = H.run_backend(ours, d)
+    assert a["R"] == 0
+    assert torch.equal(a["color"], torch.tensor([0.25, 0.5, 0.75, 1.0]).view(4, 1, 1).expand(4, 48, 64))
+    assert float(a["g_means3D"].abs().max()) == 0.0
+    ref = _ref()
+    b = H.run_backend(ref, d)
+    assert not H.compare(a, b)
+
+
+def test_mark_visible_matches_reference():
+    ref, ours = _ref(), _ours()
+    d = H.scene_inputs(50000, 11)
+    cam = d["cam"]
+    a = ours.mark_visible(d["means3D"], cam.viewmatrix, cam.projmatrix)
+    b = ref.mark_visible(d["means3D"], cam.viewmatrix, cam.projmatrix)
+    assert a.dtype == torch.bool and torch.equal(a, b)
+    assert 0 < int(a.sum()) < a.numel()
+
+
+@pytest.mark.parametrize("P", [1, 2, 3, 5, 1000, 100000, 1000000])
+def test_knn_bit_exact(P):
+    from splatloc_b200 import scenes
+    ref, ours = _ref(), _ours()
+    pts = scenes.make_knn_points(P, seed=P % 7).cuda()
+    a = ours.distCUDA2(pts)
+    b = ref.distCUDA2(pts)
+    torch.cuda.synchronize()
+    assert torch.equal(a.view(torch.int32), b.view(torch.int32)), \
+        f"{int((a.view(torch.int32) != b.view(torch.int32)).sum())}/{P} differ"
+
+
+def test_autograd_front_end():
+    """The diff_gauss-compatible module: 4-tuple, gradients on the leaf tensors, absgrad side channel."""
+    from splatloc_b200.diff_gauss import GaussianRasterizationSettings, GaussianRasterizer
+    d = H.scene_inputs(20000, 12, size=(320, 240))
+    cam = d["cam"]
+    leaves = {k: d[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "colors_precomp", "scales", "rotations")}
+    means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    rs = GaussianRasterizationSettings(cam.H, cam.W, cam.tanfovx, cam.tanfovy, d["bg"], 1.0, cam.viewmatrix,
+                                       cam.projmatrix, 0, cam.campos, False, False)
+    out = GaussianRasterizer(rs)(means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
+                                 colors_precomp=leaves["colors_precomp"], scales=leaves["scales"],
+                                 rotations=leaves["rotations"])
+    assert len(out) == 4
+    color, depth, alpha, radii = out
+    assert color.shape == (4, cam.H, cam.W) and depth.shape == (1, cam.H, cam.W) and radii.dtype == torch.int32
+    gc, gd, ga = d["grads"]
+    ((color * gc).sum() + (depth * gd).sum() + (alpha * ga).sum()).backward()
+    b = H.run_backend(_ours(), d)
+    assert torch.allclose(leaves["means3D"].grad.cpu(), b["g_means3D"], rtol=1e-4, atol=1e-5 * float(b["g_means3D"].abs().max()))
+    assert torch.allclose(means2D.grad.cpu(), b["g_means2D"], rtol=1e-4, atol=1e-5 * float(b["g_means2D"].abs().max()))
+    assert hasattr(means2D, "absgrad") and means2D.absgrad.shape == (20000, 3)
+    with pytest.raises(Exception):
+        GaussianRasterizer(rs)(means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"])
