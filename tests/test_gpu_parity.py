@@ -55,17 +55,22 @@ def test_empty_and_invisible():
         d[k] = d[k][:0]
     a = H.run_backend(ours, d)
     assert a["R"] == 0 and float(a["color"].abs().max()) == 0.0
-    # every Gaussian behind the camera -> R == 0, background everywhere, zero gradients
+    # Gaussians behind the camera are NOT culled by the reference's NDC test (z_ndc ~ 1.002 for any
+    # z_cam < 0 with getProjectionMatrix2): whatever it renders, we must render the same.
+    ref = _ref()
     d = H.scene_inputs(500, 0, size=(64, 48), bg=[0.25, 0.5, 0.75, 1.0])
     cam = d["cam"]
-    fwd = cam.viewmatrix[:3, 2]
-    d["means3D"] = (cam.campos[None, :] - 5.0 * fwd[None, :] + 0.01 * torch.randn_like(d["means3D"])).contiguous()
-    a = H.run_backend(ours, d)
-    assert a["R"] == 0
+    fwd, right = cam.viewmatrix[:3, 2], cam.viewmatrix[:3, 0]
+    base = d["means3D"].clone()
+    d["means3D"] = (cam.campos[None, :] - 5.0 * fwd[None, :] + 0.3 * torch.randn_like(base)).contiguous()
+    a, b = H.run_backend(ours, d), H.run_backend(ref, d)
+    assert not H.compare(a, b)
+    # every Gaussian far outside the frustum sideways -> R == 0, background everywhere, zero gradients
+    d["means3D"] = (cam.campos[None, :] + 1.0 * fwd[None, :] + 50.0 * right[None, :] + 0.01 * torch.randn_like(base)).contiguous()
+    a, b = H.run_backend(ours, d), H.run_backend(ref, d)
+    assert a["R"] == 0 and b["R"] == 0
     assert torch.equal(a["color"], torch.tensor([0.25, 0.5, 0.75, 1.0]).view(4, 1, 1).expand(4, 48, 64))
     assert float(a["g_means3D"].abs().max()) == 0.0
-    ref = _ref()
-    b = H.run_backend(ref, d)
     assert not H.compare(a, b)
 
 
