@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the rasterizer hot path (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Metric: fwd+bwd Mpix/s at 640x480.  One "step" = one forward + backward pass of
+one 640x480 view per GPU over the config-2 scene (500 k Gaussians, C=4
+precomputed colours [rgb, kp_score], depth and alpha outputs and gradients):
+SplatLoc's `train_gaussians.py` mapping step as seen by the rasterizer.  With
+N > 1 every rank renders its own views of the replicated map and the packed
+per-Gaussian gradient block is all-reduced over NCCL inside the step (weak
+scaling).  `value` is device-resident (inputs in HBM when the timer starts);
+`e2e` goes through the public `GaussianRasterizer` autograd API with the
+per-view inputs (camera, upstream pixel gradients) copied from pinned host
+memory and the rendered images copied back inside the timed region.
+
+--impl reference runs the UNMODIFIED reference CUDA rasterizer
+(oracle/_ref/libref_raster_c4.so, compiled from /root/reference for sm_100a)
+on the same scene, cameras and protocol; the reference has no CPU
+implementation of this path, so when that library or a GPU is missing the arm
+falls back to the float64 CPU port under oracle/ on a bounded sample.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+from splatloc_b200 import scenes  # noqa: E402
+
+WORKLOAD = "replica_train_step_500k_640x480_c4"
+P_DEFAULT, C_DEFAULT = 500_000, 4
+N_CAMERAS = 8          # views cycled per rank, so consecutive steps see different inputs
+L2_FLUSH_BYTES = 256 << 20
+
+
+def env_int(name, default):
+    return int(os.environ.get(name, default))
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.gpu = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100",
+                 "-i", str(self.gpu)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 8:
+                continue
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def algorithmic_bytes(P, V, R, N, Tn, C, M_sh=0):
+    """Compulsory HBM bytes per stage: every stage reads its inputs and writes
+    its outputs exactly once."""
+    return {
+        "preprocess": P * (44 + 12 * M_sh) + 8 * P + 52 * V,
+        "scan": 8 * P,
+        "emit_pairs": 16 * V + 8 * P + 12 * R,
+        "sort_pairs": 24 * R,
+        "tile_ranges": 8 * R + 8 * Tn,
+        "blend_forward": (32 + 4 * C) * R + (12 + 4 * C) * N,
+        "blend_backward": (32 + 4 * C) * R + (16 + 4 * C) * N + (36 + 4 * C) * R,
+        "preprocess_backward": 4 * P + 164 * V + (92 + 4 * C + 12 * M_sh) * P,
+    }
+
+
+def measured_peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+# ------------------------------------------------------------------------------------ back ends
+def load_backend(impl):
+    if impl == "ours":
+        from splatloc_b200 import _C
+        from splatloc_b200.diff_gauss import GaussianRasterizationSettings, GaussianRasterizer
+        return _C, GaussianRasterizationSettings, GaussianRasterizer
+    from oracle import ref_cuda, ref_module
+    return ref_cuda, ref_module.GaussianRasterizationSettings, ref_module.GaussianRasterizer
+
+
+def run_gpu(args, impl):
+    rank, world = env_int("RANK", 0), env_int("WORLD_SIZE", 1)
+    local = env_int("LOCAL_RANK", 0)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if impl == "reference":
+        if rank != 0:
+            return None  # rank 0 alone times the reference arm; no process group is formed
+        world = 1
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+
+    be, Settings, Rasterizer = load_backend(impl)
+    P, C = args.points, C_DEFAULT
+    W, H = scenes.REPLICA_INTRINSICS["W"], scenes.REPLICA_INTRINSICS["H"]
+    N, Tn = W * H, ((W + 15) // 16) * ((H + 15) // 16)
+    sc = {k: v.to(dev) for k, v in scenes.make_scene(P, seed=0, channels=C).items()}
+    bg = torch.zeros(C, device=dev)
+    cams_host = [scenes.make_camera(seed=100 * rank + i) for i in range(N_CAMERAS)]
+    cams = [c.to(dev) for c in cams_host]
+    grads_host = [tuple(t.pin_memory() for t in scenes.make_pixel_grads(100 * rank + i, C, H, W)) for i in range(N_CAMERAS)]
+    grads = [tuple(t.to(dev) for t in g) for g in grads_host]
+    EMPTY = torch.Tensor([])
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+    use_dist = world > 1 and impl == "ours"
+
+    def step_resident(i):
+        cam, (gc, gd, ga) = cams[i % N_CAMERAS], grads[i % N_CAMERAS]
+        R, color, depth, alpha, radii, geom, binning, img = be.rasterize_gaussians(
+            bg, sc["means3D"], sc["colors_precomp"], sc["opacities"], sc["scales"], sc["rotations"], 1.0, EMPTY,
+            EMPTY.bool(), cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, H, W, EMPTY, 0, cam.campos,
+            False, False)
+        out = be.rasterize_gaussians_backward(
+            bg, sc["means3D"], radii, sc["colors_precomp"], sc["scales"], sc["rotations"], 1.0, EMPTY,
+            cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, gc, gd, ga, EMPTY, 0, cam.campos, geom, R,
+            binning, img, alpha, False)
+        if use_dist:
+            flat = out[0]._base if out[0]._base is not None else out[0]
+            dist.all_reduce(flat)   # multi-view step: sum of per-Gaussian gradients over the views
+        return R, radii
+
+    # ---- e2e: public autograd API, per-view inputs from pinned host memory, images read back
+    leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "colors_precomp", "scales", "rotations")}
+    means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
+    cam_host = [(c.viewmatrix.pin_memory(), c.projmatrix.pin_memory(), c.campos.pin_memory()) for c in cams_host]
+    cam_dev = (torch.empty(4, 4, device=dev), torch.empty(4, 4, device=dev), torch.empty(3, device=dev))
+    g_dev = (torch.empty(C, H, W, device=dev), torch.empty(1, H, W, device=dev), torch.empty(1, H, W, device=dev))
+    img_host = (torch.empty(C, H, W).pin_memory(), torch.empty(1, H, W).pin_memory(), torch.empty(1, H, W).pin_memory())
+    h2d = sum(t.numel() * 4 for t in cam_dev) + sum(t.numel() * 4 for t in g_dev)
+    d2h = sum(t.numel() * 4 for t in img_host)
+
+    def step_e2e(i):
+        k = i % N_CAMERAS
+        for dst, src in zip(cam_dev, cam_host[k]):
+            dst.copy_(src, non_blocking=True)
+        for dst, src in zip(g_dev, grads_host[k]):
+            dst.copy_(src, non_blocking=True)
+        c = cams_host[k]
+        rs = Settings(H, W, c.tanfovx, c.tanfovy, bg, 1.0, cam_dev[0], cam_dev[1], 0, cam_dev[2], False, False)
+        for t in leaves.values():
+            t.grad = None
+        means2D.grad = None
+        color, depth, alpha, radii = Rasterizer(rs)(
+            means3D=leaves["means3D"], means2D=means2D, opacities=leaves["opacities"],
+            colors_precomp=leaves["colors_precomp"], scales=leaves["scales"], rotations=leaves["rotations"])
+        torch.autograd.backward([color, depth, alpha], list(g_dev))
+        if use_dist:
+            for t in leaves.values():
+                dist.all_reduce(t.grad)
+        for dst, src in zip(img_host, (color, depth, alpha)):
+            dst.copy_(src.detach(), non_blocking=True)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1 and impl == "ours":
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup, profile=False):
+        for i in range(warmup):
+            fn(i)
+            flush.zero_()
+        barrier()
+        if profile and impl == "ours":
+            from splatloc_b200 import _capi
+            _capi.load().sl_profile_enable(1)
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(steps)]
+        t0 = time.perf_counter()
+        for i in range(steps):
+            flush.zero_()             # L2 flush between timed iterations (outside the event pair)
+            ev[i][0].record()
+            fn(warmup + i)
+            ev[i][1].record()
+        barrier()
+        wall = time.perf_counter() - t0
+        ms = sum(a.elapsed_time(b) for a, b in ev)
+        prof = None
+        if profile and impl == "ours":
+            prof = _capi.profile_read()
+            _capi.load().sl_profile_enable(0)
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        if world > 1 and impl == "ours":
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), wall, prof
+
+    # bring the GPU out of its idle clocks before anything is timed (a 10-step run lasts ~20 ms)
+    t_spin = time.perf_counter()
+    while time.perf_counter() - t_spin < 0.5:
+        step_resident(0)
+        torch.cuda.synchronize()
+
+    n_ranks = world if impl == "ours" else 1
+    launches0 = 0
+    if impl == "ours":
+        from splatloc_b200 import _capi
+        launches0 = _capi.load().sl_launch_count()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ms_total, wall, _ = timed(step_resident, args.steps, args.warmup)
+    clocks = sampler.stop()
+    launches = (_capi.load().sl_launch_count() - launches0) if impl == "ours" else 0
+    # the warm-up steps launched too; count only the timed ones
+    if impl == "ours":
+        launches = launches * args.steps // (args.steps + args.warmup)
+    e2e_ms, _, _ = timed(step_e2e, args.steps, args.warmup)
+    # per-stage device times: same steps again with the library's event timers on (kept apart from
+    # the headline loop because reading the events back blocks the host between stages)
+    _, _, prof = timed(step_resident, max(5, args.steps // 2), 1, profile=True)
+
+    R, radii = step_resident(0)
+    V = int((radii > 0).sum())
+    torch.cuda.synchronize()
+    ms_step = ms_total / args.steps
+    value = N * n_ranks / (ms_step * 1e-3) / 1e6
+    e2e_value = N * n_ranks / (e2e_ms / args.steps * 1e-3) / 1e6
+
+    out = {
+        "metric": "fwd+bwd Mpix/s at 640x480", "value": round(value, 3), "unit": "Mpix/s",
+        "n_gpus": n_ranks, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "impl": impl,
+        "config": {"workload": WORKLOAD, "gaussians": P, "channels": C, "image": [W, H], "views_per_gpu_per_step": 1,
+                   "visible": V, "pairs": R, "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
+                   "parallelism": f"views sharded over {n_ranks} GPU(s)" + (", NCCL all-reduce of the packed gradient block" if use_dist else "")},
+        "e2e": {"value": round(e2e_value, 3), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "api": "GaussianRasterizer autograd fwd+bwd; camera + upstream pixel gradients from pinned host memory, "
+                       "images read back; the Gaussian map is resident state"},
+        "gpu_launches": int(launches),
+        "clocks": clocks,
+        "wall_s": round(wall, 3),
+    }
+    if impl == "ours":
+        peak, how = measured_peaks()
+        alg = algorithmic_bytes(P, V, R, N, Tn, C)
+        stages = {}
+        for name, (tot, calls) in prof.items():
+            if calls:
+                ms = tot / calls
+                stages[name] = {"ms": round(ms, 4), "alg_MB": round(alg[name] / 1e6, 2),
+                                "GBps": round(alg[name] / (ms * 1e-3) / 1e9, 1)}
+        top = max(stages, key=lambda k: stages[k]["ms"])
+        ach = stages[top]["GBps"]
+        out["roofline"] = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
+                           "frac": round(ach / peak, 4), "traffic": None, "peak_source": how,
+                           "note": "blend kernels are FP32/SFU/atomic-bound; see profiles/ for pipe utilisation",
+                           "step_alg_MB": round(sum(alg.values()) / 1e6, 1),
+                           "step_frac": round(sum(alg.values()) / (ms_step * 1e-3) / 1e9 / peak, 4)}
+        out["stages"] = stages
+        if rank == 0 and not args.no_cpu_baseline:
+            out["cpu_baseline"] = cpu_baseline(budget_s=args.cpu_budget)
+    else:
+        out["cpu_baseline"] = {"value": out["value"], "unit": "Mpix/s", "cores": 0, "kind": "reference",
+                               "sample": "full workload; the reference path is CUDA-only, so this arm is the reference's own "
+                                         "CUDA rasterizer (oracle/_ref, sm_100a) on the GPU, not host cores"}
+    if world > 1:
+        dist.destroy_process_group()
+    return out if rank == 0 else None
+
+
+def cpu_baseline(budget_s=20.0):
+    """Float64 CPU port (oracle/) on a bounded sample of the same workload: a centred crop of the
+    config-2 view, chosen so that the run takes ~10-30 s on the host cores."""
+    from oracle import raster_oracle
+    torch.set_num_threads(os.cpu_count() or 1)
+    return raster_oracle.timed_sample(budget_s=budget_s)
+
+
+def run_cpu_reference(args):
+    cb = cpu_baseline(budget_s=args.cpu_budget)
+    cb["kind"] = "port"
+    return {"metric": "fwd+bwd Mpix/s at 640x480", "value": cb["value"], "unit": "Mpix/s", "n_gpus": 0,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": None, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "impl": "reference",
+            "config": {"workload": WORKLOAD, "note": "reference CUDA library or GPU unavailable: float64 CPU port"},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--points", type=int, default=P_DEFAULT)
+    ap.add_argument("--cpu-budget", type=float, default=20.0)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+
+    if args.impl == "reference":
+        from oracle import ref_cuda
+        if not (torch.cuda.is_available() and ref_cuda.available()):
+            if env_int("RANK", 0) == 0:
+                print(json.dumps(run_cpu_reference(args)))
+            return
+    elif not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    out = run_gpu(args, args.impl)
+    if out is not None:
+        print(json.dumps(out))
+
+
+if __name__ == "__main__":
+    main()

@@ -126,6 +126,23 @@ size_t sl_knn_scratch_bytes(int P);
 int sl_knn(int P, const float* points, float* mean_dists,
            char* scratch, size_t scratch_bytes, void* stream);
 
+/* ---- instrumentation (no counterpart in the reference, which has no tracing,
+ * SURVEY.md section 5) ------------------------------------------------------ */
+
+/* Number of this library's kernels launched by the process so far. */
+long long sl_launch_count(void);
+
+/* Per-stage device timing with CUDA events recorded on the caller's stream
+ * around each stage of sl_forward / sl_backward.  sl_profile_enable(1) resets
+ * and starts accumulation, sl_profile_enable(0) stops it.  sl_profile_read
+ * synchronises on the last recorded events and fills, for stage i <
+ * sl_profile_stage_count(), the accumulated milliseconds and number of timed
+ * calls.  Host-blocking; not for use inside latency-critical loops. */
+void sl_profile_enable(int on);
+int sl_profile_stage_count(void);
+const char* sl_profile_stage_name(int stage);
+int sl_profile_read(double* total_ms, long long* calls, int n);
+
 #ifdef __cplusplus
 }
 #endif

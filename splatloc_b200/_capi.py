@@ -52,6 +52,11 @@ SIGNATURES = {
     "sl_mark_visible": (C.c_int, [C.c_int, _F, _F, _F, _F, C.c_void_p]),
     "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),
+    "sl_launch_count": (C.c_longlong, []),
+    "sl_profile_enable": (None, [C.c_int]),
+    "sl_profile_stage_count": (C.c_int, []),
+    "sl_profile_stage_name": (C.c_char_p, [C.c_int]),
+    "sl_profile_read": (C.c_int, [C.POINTER(C.c_double), C.POINTER(C.c_longlong), C.c_int]),
 }
 
 _lib = None
@@ -83,3 +88,13 @@ def check(rc: int) -> int:
     if rc < 0:
         raise RuntimeError(last_error() or f"libsplatloc_b200 error {rc}")
     return rc
+
+
+def profile_read() -> dict:
+    """{stage name: (total ms, timed calls)} accumulated since sl_profile_enable(1)."""
+    lib = load()
+    n = lib.sl_profile_stage_count()
+    ms = (C.c_double * n)()
+    calls = (C.c_longlong * n)()
+    lib.sl_profile_read(ms, calls, n)
+    return {lib.sl_profile_stage_name(i).decode(): (ms[i], calls[i]) for i in range(n)}

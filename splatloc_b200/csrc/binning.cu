@@ -65,14 +65,17 @@ int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t
                       int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream)
 {
     emit_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                            tile_mask, grid_x, grid_y, keys, vals);
+                                                            tile_mask, grid_x, grid_y, keys, vals); count_launch();
     return 0;
 }
 
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_tiles, cudaStream_t stream)
 {
     SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream), "ranges memset");
-    if (R > 0) tile_ranges_kernel<<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, ranges);
+    if (R > 0) {
+        tile_ranges_kernel<<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, ranges);
+        count_launch();
+    }
     return 0;
 }
 

@@ -276,6 +276,7 @@ int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, cons
         set_error("blend_backward: unsupported channel count %d (3 or 4)", C);
         return -2;
     }
+    count_launch();
     return 0;
 }
 

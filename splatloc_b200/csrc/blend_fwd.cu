@@ -134,6 +134,7 @@ int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const
         set_error("blend_forward: unsupported channel count %d (3 or 4)", C);
         return -2;
     }
+    count_launch();
     return 0;
 }
 

@@ -6,6 +6,7 @@
 // read R -> emit pairs -> sort -> tile ranges -> blend; the backward follows
 // Rasterizer::backward (:586-692): blend backward -> per-Gaussian backward.
 // Everything is enqueued on the caller's stream.
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -40,6 +41,62 @@ int check_stage(bool debug, cudaStream_t stream, const char* what)
     return check_cuda(e, what);
 }
 
+// ---------------------------------------------------------------- stage profiler
+// Optional per-stage timing with CUDA events on the caller's stream
+// (sl_profile_enable / sl_profile_read).  Off by default; when off the hot path
+// records nothing.
+enum Stage {
+    ST_PREPROCESS = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
+    ST_COUNT
+};
+static const char* const kStageNames[ST_COUNT] = {
+    "preprocess", "scan", "emit_pairs", "sort_pairs", "tile_ranges", "blend_forward", "blend_backward",
+    "preprocess_backward"};
+
+struct Profiler {
+    bool enabled = false;
+    bool created = false;
+    cudaEvent_t ev[ST_COUNT][2];
+    bool recorded[ST_COUNT] = {};
+    double total_ms[ST_COUNT] = {};
+    long calls[ST_COUNT] = {};
+};
+static Profiler g_prof;
+static std::atomic<long long> g_launches{0};
+
+void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+
+struct StageTimer {
+    int st;
+    cudaStream_t stream;
+    bool on;
+    StageTimer(int st_, cudaStream_t s) : st(st_), stream(s), on(g_prof.enabled)
+    {
+        if (!on) return;
+        if (!g_prof.created) {
+            for (int i = 0; i < ST_COUNT; ++i)
+                for (int j = 0; j < 2; ++j) cudaEventCreate(&g_prof.ev[i][j]);
+            g_prof.created = true;
+        }
+        if (g_prof.recorded[st]) {  // fold the previous measurement of this stage
+            float ms = 0.f;
+            if (cudaEventSynchronize(g_prof.ev[st][1]) == cudaSuccess &&
+                cudaEventElapsedTime(&ms, g_prof.ev[st][0], g_prof.ev[st][1]) == cudaSuccess) {
+                g_prof.total_ms[st] += ms;
+                g_prof.calls[st] += 1;
+            }
+            g_prof.recorded[st] = false;
+        }
+        cudaEventRecord(g_prof.ev[st][0], stream);
+    }
+    ~StageTimer()
+    {
+        if (!on) return;
+        cudaEventRecord(g_prof.ev[st][1], stream);
+        g_prof.recorded[st] = true;
+    }
+};
+
 // Number of bits needed for tile ids: same value as the reference's getHigherMsb
 // (rasterizer_impl.cu:35-50) -- the position of the highest set bit, plus one.
 static int tile_id_bits(uint32_t n)
@@ -73,6 +130,40 @@ extern "C" {
 const char* sl_version(void) { return "splatloc_b200 0.1 sm_100a"; }
 
 const char* sl_last_error(void) { return last_error(); }
+
+long long sl_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+void sl_profile_enable(int on)
+{
+    g_prof.enabled = on != 0;
+    for (int i = 0; i < ST_COUNT; ++i) {
+        g_prof.total_ms[i] = 0.0;
+        g_prof.calls[i] = 0;
+        g_prof.recorded[i] = false;
+    }
+}
+
+int sl_profile_stage_count(void) { return ST_COUNT; }
+
+const char* sl_profile_stage_name(int stage) { return (stage >= 0 && stage < ST_COUNT) ? kStageNames[stage] : ""; }
+
+int sl_profile_read(double* total_ms, long long* calls, int n)
+{
+    for (int i = 0; i < ST_COUNT && i < n; ++i) {
+        if (g_prof.recorded[i]) {
+            float ms = 0.f;
+            if (cudaEventSynchronize(g_prof.ev[i][1]) == cudaSuccess &&
+                cudaEventElapsedTime(&ms, g_prof.ev[i][0], g_prof.ev[i][1]) == cudaSuccess) {
+                g_prof.total_ms[i] += ms;
+                g_prof.calls[i] += 1;
+            }
+            g_prof.recorded[i] = false;
+        }
+        total_ms[i] = g_prof.total_ms[i];
+        calls[i] = g_prof.calls[i];
+    }
+    return ST_COUNT;
+}
 
 size_t sl_geometry_bytes(int P) { return required_bytes<GeomState>((size_t)(P > 0 ? P : 0)); }
 size_t sl_binning_bytes(int R) { return required_bytes<BinningState>((size_t)(R > 0 ? R : 0)); }
@@ -145,13 +236,20 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     if (!img_chunk) { set_error("sl_forward: image allocation failed"); return SL_ERR_ALLOC; }
     ImageState img = ImageState::from_chunk(img_chunk, N, n_tiles);
 
-    int rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
+    int rc;
+    {
+        StageTimer t(ST_PREPROCESS, stream);
+        rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
                                colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered != 0, radii,
                                geom, stream);
+    }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess");
 
-    rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_desc, geom.counters, stream);
+    {
+        StageTimer t(ST_SCAN, stream);
+        rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_desc, geom.counters, stream);
+    }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "prefix sum");
 
@@ -171,25 +269,37 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     BinningState bin = BinningState::from_chunk(bin_chunk, R);
 
     if (R > 0) {
-        rc = launch_emit_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, bin.point_list_keys_unsorted,
-                               bin.point_list_unsorted, stream);
+        {
+            StageTimer t(ST_EMIT, stream);
+            rc = launch_emit_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, bin.point_list_keys_unsorted,
+                                   bin.point_list_unsorted, stream);
+        }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "emit pairs");
 
-        rc = launch_sort_pairs(bin.point_list_keys_unsorted, bin.point_list_unsorted, bin.point_list_keys,
-                               bin.point_list, bin.sort, R, 32 + tile_id_bits(n_tiles), stream);
+        {
+            StageTimer t(ST_SORT, stream);
+            rc = launch_sort_pairs(bin.point_list_keys_unsorted, bin.point_list_unsorted, bin.point_list_keys,
+                                   bin.point_list, bin.sort, R, 32 + tile_id_bits(n_tiles), stream);
+        }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "sort");
     }
 
-    rc = launch_tile_ranges(R, bin.point_list_keys, img.ranges, n_tiles, stream);
+    {
+        StageTimer t(ST_RANGES, stream);
+        rc = launch_tile_ranges(R, bin.point_list_keys, img.ranges, n_tiles, stream);
+    }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile ranges");
 
     const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
-    rc = launch_blend_forward(C, vp, img.ranges, bin.point_list, geom.means2D, features, geom.depths,
-                              geom.conic_opacity, background, out_color, out_depth, out_alpha, img.n_contrib,
-                              stream);
+    {
+        StageTimer t(ST_BLEND_FWD, stream);
+        rc = launch_blend_forward(C, vp, img.ranges, bin.point_list, geom.means2D, features, geom.depths,
+                                  geom.conic_opacity, background, out_color, out_depth, out_alpha, img.n_contrib,
+                                  stream);
+    }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend forward");
     return R;
@@ -240,17 +350,24 @@ int sl_backward(int P, int D, int M, int R, int C,
     if (radii == nullptr) radii = geom.internal_radii;
 
     const float* color_ptr = (colors_precomp != nullptr) ? colors_precomp : geom.rgb;
-    int rc = launch_blend_backward(C, vp, img.ranges, bin.point_list, background, geom.means2D,
+    int rc;
+    {
+        StageTimer t(ST_BLEND_BWD, stream);
+        rc = launch_blend_backward(C, vp, img.ranges, bin.point_list, background, geom.means2D,
                                    geom.conic_opacity, color_ptr, geom.depths, accum_alphas, img.n_contrib,
                                    dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic,
                                    dL_dopacity, dL_dcolor, dL_ddepth, stream);
+    }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend backward");
 
     const float* cov3D_ptr = (cov3D_precomp != nullptr) ? cov3D_precomp : geom.cov3D;
-    rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, scales, rotations, cov3D_ptr,
-                                    viewmatrix, projmatrix, campos, vp, dL_dmean2D, dL_dconic, dL_dmean3D,
-                                    dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream);
+    {
+        StageTimer t(ST_PREPROCESS_BWD, stream);
+        rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, scales, rotations, cov3D_ptr,
+                                        viewmatrix, projmatrix, campos, vp, dL_dmean2D, dL_dconic, dL_dmean3D,
+                                        dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream);
+    }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess backward");
     return 0;

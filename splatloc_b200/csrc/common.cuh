@@ -47,6 +47,9 @@ int check_stage(bool debug, cudaStream_t stream, const char* what);
         if (_rc != 0) return _rc;                              \
     } while (0)
 
+// Counts this library's own kernel launches (read back through sl_launch_count()).
+void count_launch(int n = 1);
+
 // --------------------------------------------------------------- small maths
 struct f3 { float x, y, z; };
 

@@ -256,14 +256,14 @@ int launch_knn(int P, const float* points, float* mean_dists, char* scratch, cud
     char* chunk = scratch;
     KnnScratch s = KnnScratch::from_chunk(chunk, (size_t)P, n_cells);
 
-    knn_bbox_init_kernel<<<1, 32, 0, stream>>>(s.bbox);
-    knn_bbox_kernel<<<min(ceil_div(P, 256), 148 * 8), 256, 0, stream>>>(P, points, s.bbox);
+    knn_bbox_init_kernel<<<1, 32, 0, stream>>>(s.bbox); count_launch();
+    knn_bbox_kernel<<<min(ceil_div(P, 256), 148 * 8), 256, 0, stream>>>(P, points, s.bbox); count_launch();
     SL_CUDA(cudaMemsetAsync(s.counts, 0, n_cells * sizeof(uint32_t), stream), "knn memset");
-    knn_count_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, s.bbox, L, s.cell_of, s.counts);
+    knn_count_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, s.bbox, L, s.cell_of, s.counts); count_launch();
     int rc = launch_inclusive_scan(s.counts, s.cell_end, (int)n_cells, s.scan_desc, s.ticket, stream);
     if (rc != 0) return rc;
-    knn_scatter_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, s.cell_of, s.counts, s.cell_end, s.sorted);
-    knn_query_kernel<<<ceil_div(P, 128), 128, 0, stream>>>(P, s.sorted, s.cell_end, s.bbox, L, mean_dists);
+    knn_scatter_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, s.cell_of, s.counts, s.cell_end, s.sorted); count_launch();
+    knn_query_kernel<<<ceil_div(P, 128), 128, 0, stream>>>(P, s.sorted, s.cell_end, s.bbox, L, mean_dists); count_launch();
     return 0;
 }
 

@@ -195,14 +195,14 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
     preprocess_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
         P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
         colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, g.means2D, g.depths,
-        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched);
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched); count_launch();
     return 0;
 }
 
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
                         uint8_t* present, cudaStream_t stream)
 {
-    mark_visible_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, means3D, viewmatrix, projmatrix, present);
+    mark_visible_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, means3D, viewmatrix, projmatrix, present); count_launch();
     return 0;
 }
 

@@ -234,7 +234,7 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
 {
     preprocess_backward_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
         P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrix, projmatrix, campos,
-        vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot);
+        vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot); count_launch();
     return 0;
 }
 

@@ -318,7 +318,7 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned lon
     const int blocks = ceil_div(n, SCAN_ITEMS_PER_BLOCK);
     SL_CUDA(cudaMemsetAsync(desc, 0, (size_t)(blocks + 1) * sizeof(unsigned long long), stream), "scan memset");
     SL_CUDA(cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream), "scan memset");
-    inclusive_scan_kernel<<<blocks, 256, 0, stream>>>(in, out, n, desc, ticket);
+    inclusive_scan_kernel<<<blocks, 256, 0, stream>>>(in, out, n, desc, ticket); count_launch();
     return 0;
 }
 
@@ -342,8 +342,8 @@ int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
                                  (int)sizeof(SortSmem)), "sort smem attribute");
     SL_CUDA(cudaMemsetAsync(sc.histograms, 0, sc.zero_bytes, stream), "sort memset");
     const int hist_blocks = min(ceil_div(n, 256 * 8), 148 * 8);
-    sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, sc.histograms);
-    sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(sc.histograms);
+    sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, sc.histograms); count_launch();
+    sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(sc.histograms); count_launch();
 
     const int blocks = (int)sc.sort_blocks;
     const uint64_t* kin = keys_in;
@@ -356,7 +356,7 @@ int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
         uint32_t* vout = to_final ? vals_out : sc.vals_tmp;
         sort_pass_kernel<<<blocks, SORT_THREADS, sizeof(SortSmem), stream>>>(
             kin, vin, kout, vout, n, p * SORT_RADIX_BITS, sc.histograms + p * SORT_RADIX,
-            sc.lookback + (size_t)p * blocks * SORT_RADIX, sc.tickets + p);
+            sc.lookback + (size_t)p * blocks * SORT_RADIX, sc.tickets + p); count_launch();
         kin = kout;
         vin = vout;
     }

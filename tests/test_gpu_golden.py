@@ -1,0 +1,70 @@
+"""GPU: libsplatloc_b200 against the committed reference outputs (tests/golden) and against the
+float64 oracle on the same inputs -- neither needs /root/reference or oracle/_ref at run time."""
+import numpy as np
+import pytest
+import torch
+
+from tests import helpers as H
+from tests.test_golden_cpu import CASES, frac_bad, load, run_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _inputs(g):
+    from splatloc_b200.scenes import Camera
+    t = lambda k: torch.from_numpy(g["in_" + k]).cuda()  # noqa: E731
+    W, H_ = (int(v) for v in g["in_size"])
+    d = {k: t(k) for k in ("means3D", "scales", "rotations", "opacities", "bg")}
+    for k in ("colors_precomp", "shs", "cov3D_precomp", "tile_mask"):
+        if "in_" + k in g:
+            d[k] = t(k)
+    d["cam"] = Camera(W, H_, float(g["in_tanfov"][0]), float(g["in_tanfov"][1]), t("viewmatrix"), t("projmatrix"), t("campos"))
+    d["sh_degree"] = int(g["in_sh_degree"])
+    d["grads"] = (t("grad0"), t("grad1"), t("grad2"))
+    return d
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_matches_committed_reference_outputs(name):
+    from splatloc_b200 import _C
+    g = load(name)
+    a = H.run_backend(_C, _inputs(g))
+    b = {k[4:]: (torch.from_numpy(v) if v.ndim else int(v)) for k, v in g.items() if k.startswith("ref_")}
+    bad = H.compare(a, b)
+    assert not bad, "\n".join(bad)
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_matches_float64_oracle(name):
+    """Budgets as in tests/test_golden_cpu.py (decision flips between float64 and float32)."""
+    from splatloc_b200 import _C
+    g = load(name)
+    a = H.run_backend(_C, _inputs(g))
+    fw, bw, _ = run_oracle(g)
+    assert (fw["pre"]["radii"].numpy() != a["radii"].numpy()).mean() <= 2e-3
+    assert abs(fw["R"] - a["R"]) <= max(4, 2e-3 * a["R"])
+    assert frac_bad(fw["color"], a["color"], 1e-4, 1e-5) <= 5e-3
+    assert frac_bad(fw["depth"], a["depth"][0], 1e-4, 1e-5) <= 5e-3
+    assert frac_bad(fw["alpha"], a["alpha"][0], 1e-4, 1e-5) <= 5e-3
+    for k in ("g_means2D", "g_abs2D", "g_colors", "g_opacity", "g_means3D", "g_cov3D", "g_scales", "g_rot", "g_sh"):
+        ref = bw[k].numpy()
+        if ref.size == 0:
+            continue
+        fb = frac_bad(a[k].numpy(), ref, 1e-4, 1e-5 * 16 * max(np.abs(ref).max(), 1e-30))
+        assert fb <= 1e-2, f"{k}: {fb:.4f} outside tolerance"
+
+
+@pytest.mark.parametrize("name", ["knn_7", "knn_5000"])
+def test_knn_matches_committed_reference_output(name):
+    from splatloc_b200 import _C
+    g = load(name)
+    out = _C.distCUDA2(torch.from_numpy(g["in_points"]).cuda()).cpu().numpy()
+    assert np.array_equal(out.view(np.int32), g["ref_dist"].view(np.int32))
+
+
+def test_mark_visible_matches_committed_reference_output():
+    from splatloc_b200 import _C
+    g = load("c4_precomp")
+    t = lambda k: torch.from_numpy(g["in_" + k]).cuda()  # noqa: E731
+    out = _C.mark_visible(t("means3D"), t("viewmatrix"), t("projmatrix")).cpu().numpy()
+    assert np.array_equal(out, g["in_visible"])
