@@ -234,11 +234,20 @@ def run_gpu(args, impl):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), wall, prof
 
-    # bring the GPU out of its idle clocks before anything is timed (a 10-step run lasts ~20 ms)
-    t_spin = time.perf_counter()
-    while time.perf_counter() - t_spin < 0.5:
-        step_resident(0)
+    # Spin-up, untimed: a fresh process on a fresh box needs a moment until step times settle (idle
+    # GPU clocks, first-touch paging of the image); run batches of steps until two consecutive
+    # batches agree within 3 %, for at least 1 s and at most 10 s.
+    t_spin, prev = time.perf_counter(), None
+    while True:
+        t0 = time.perf_counter()
+        for i in range(20):
+            step_resident(i)
         torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        el = time.perf_counter() - t_spin
+        if el > 10.0 or (el > 1.0 and prev is not None and abs(dt - prev) <= 0.03 * prev):
+            break
+        prev = dt
 
     n_ranks = world if impl == "ours" else 1
     launches0 = 0
@@ -246,7 +255,8 @@ def run_gpu(args, impl):
         from splatloc_b200 import _capi
         launches0 = _capi.load().sl_launch_count()
     sampler = ClockSampler(local)
-    sampler.start()
+    if not os.environ.get("BENCH_NO_SAMPLER"):
+        sampler.start()
     ms_total, wall, _ = timed(step_resident, args.steps, args.warmup)
     clocks = sampler.stop()
     launches = (_capi.load().sl_launch_count() - launches0) if impl == "ours" else 0

@@ -19,6 +19,7 @@
 //     Channel rule kept from the fork: channels >= 3 do not feed dL/dalpha
 //     (backward.cu:1153-1154) but do receive colour gradients.
 #include "kernels.h"
+#include "blend_common.cuh"
 
 namespace sl {
 
@@ -70,7 +71,8 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 
 template <int C>
 __global__ void __launch_bounds__(SL_TILE_PIX)
-blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                      const uint32_t* __restrict__ point_list,
                       int W, int H, int grid_x, const float* __restrict__ bg,
                       const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
                       const float* __restrict__ colors, const float* __restrict__ depths,
@@ -84,28 +86,28 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       float* __restrict__ dL_dcolor,      // (P,C)
                       float* __restrict__ dL_ddepth)      // (P,1)
 {
-    __shared__ int s_id[SL_TILE_PIX];
-    __shared__ float4 s_xyd[SL_TILE_PIX];
-    __shared__ float4 s_co[SL_TILE_PIX];
-    __shared__ float4 s_col[SL_TILE_PIX];
+    __shared__ int s_id[BLEND_BATCH];
+    __shared__ float4 s_xyd[BLEND_BATCH];
+    __shared__ float4 s_co[BLEND_BATCH];
+    __shared__ float4 s_col[BLEND_BATCH];
+    __shared__ uint8_t s_mask[BLEND_BATCH];
+    __shared__ uint8_t s_list[BLEND_WARPS][BLEND_BATCH];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
-    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
-    const int px = tile_x * SL_TILE_X + (warp & 1) * 8 + (lane & 7);
-    const int py = tile_y * SL_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const int tile = tile_order[blockIdx.x];
+    const PatchGeom pg = patch_geom(tile, grid_x, warp, lane);
+    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+    const int px = pg.px, py = pg.py;
     const bool inside = px < W && py < H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixf_x = (float)px, pixf_y = (float)py;
 
     const uint2 range = ranges[tile];
     const int total = range.y - range.x;
-    const int rounds = (total + SL_TILE_PIX - 1) / SL_TILE_PIX;
-    int todo = total;
+    const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
 
     const float T_final = inside ? (1 - out_alpha[pix_id]) : 0;
     float T = T_final;
-    uint32_t contributor = todo;
     const int last_contributor = inside ? n_contrib[pix_id] : 0;
 
     float accum_rec[C];
@@ -155,15 +157,27 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(FULL, warp_last, o));
 
-    for (int i = 0; i < rounds; ++i, todo -= SL_TILE_PIX) {
+    // The whole CTA can skip the batches that lie entirely behind its last contributor.
+    __shared__ int s_block_last;
+    if (tid == 0) s_block_last = 0;
+    __syncthreads();
+    if (lane == 0) atomicMax(&s_block_last, warp_last);
+    __syncthreads();
+    const int block_last = s_block_last;
+
+    for (int i = 0; i < rounds; ++i) {
+        // batch i holds list positions (0-based) hi_pos, hi_pos-1, ... in that order
+        const int hi_pos = total - 1 - i * BLEND_BATCH;
+        const int n = min(BLEND_BATCH, total - i * BLEND_BATCH);
+        if (hi_pos - (n - 1) >= block_last) continue;   // uniform over the CTA
         __syncthreads();
-        const int progress = i * SL_TILE_PIX + tid;
-        if (range.x + progress < range.y) {
-            const int id = point_list[range.y - progress - 1];
+        if (tid < n) {
+            const int id = point_list[range.x + hi_pos - tid];
             s_id[tid] = id;
             const float2 xy = means2D[id];
+            const float4 co = conic_opacity[id];
             s_xyd[tid] = make_float4(xy.x, xy.y, depths[id], 0.f);
-            s_co[tid] = conic_opacity[id];
+            s_co[tid] = co;
             if (C == 4) {
                 s_col[tid] = reinterpret_cast<const float4*>(colors)[id];
             } else {
@@ -173,14 +187,18 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 if (C > 2) f.z = colors[id * C + 2];
                 s_col[tid] = f;
             }
+            s_mask[tid] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
         }
         __syncthreads();
 
-        const int n = min(SL_TILE_PIX, todo);
-        // list position of batch entry j is (contributor_at_batch_start - 1 - j)
-        for (int j = 0; j < n; ++j) {
-            contributor--;
-            if ((int)contributor >= warp_last) continue;  // warp-uniform
+        uint8_t* list = s_list[warp];
+        const int cnt = compact_batch(list, n, lane, [&](int j) {
+            return ((s_mask[j] >> warp) & 1) && (hi_pos - j < warp_last);
+        });
+
+        for (int k = 0; k < cnt; ++k) {
+            const int j = list[k];
+            const int pos = hi_pos - j;   // 0-based list position == the reference's `contributor`
 
             const float4 xyd = s_xyd[j];
             const float4 co = s_co[j];
@@ -192,8 +210,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const float power = __fmaf_rn(s, -0.5f, -t3);
             const float G = __expf(power);
             const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
-            const bool blend = ((int)contributor < last_contributor) && !(power > 0.0f) &&
-                               !(alpha < 1.0f / 255.0f);
+            const bool blend = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(FULL, blend)) continue;
 
             float v[16];
@@ -255,7 +272,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     }
 }
 
-int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+                          const uint32_t* point_list,
                           const float* bg, const float2* means2D, const float4* conic_opacity,
                           const float* colors, const float* depths, const float* out_alpha,
                           const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,
@@ -265,11 +283,11 @@ int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, cons
 {
     const int tiles = vp.grid_x * vp.grid_y;
     if (C == 4)
-        blend_backward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x, bg,
+        blend_backward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
             means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
             dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
     else if (C == 3)
-        blend_backward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x, bg,
+        blend_backward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
             means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
             dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
     else {

@@ -15,14 +15,18 @@
 // Layout: a warp owns an 8x4 pixel patch (not two 16-pixel rows) so that whole
 // warps finish -- and skip the inner loop -- earlier; every batch of 256
 // Gaussians stages position, depth, conic/opacity *and* features in shared
-// memory, so the inner loop touches no global memory.
+// memory, so the inner loop touches no global memory; each warp only visits the
+// batch entries whose alpha-test bounding box reaches its patch
+// (blend_common.cuh).  CTAs take tiles in order of decreasing list length.
 #include "kernels.h"
+#include "blend_common.cuh"
 
 namespace sl {
 
 template <int C>
 __global__ void __launch_bounds__(SL_TILE_PIX)
-blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ point_list,
+blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
+                     const uint32_t* __restrict__ point_list,
                      int W, int H, int grid_x,
                      const float2* __restrict__ means2D, const float* __restrict__ features,
                      const float* __restrict__ depths, const float4* __restrict__ conic_opacity,
@@ -30,40 +34,43 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      float* __restrict__ out_depth, float* __restrict__ out_alpha,
                      uint32_t* __restrict__ n_contrib)
 {
-    __shared__ float4 s_xyd[SL_TILE_PIX];   // x, y, depth, -
-    __shared__ float4 s_co[SL_TILE_PIX];    // conic xx, xy, yy, opacity
-    __shared__ float4 s_col[SL_TILE_PIX];   // up to 4 feature channels
+    __shared__ float4 s_xyd[BLEND_BATCH];   // x, y, depth, -
+    __shared__ float4 s_co[BLEND_BATCH];    // conic xx, xy, yy, opacity
+    __shared__ float4 s_col[BLEND_BATCH];   // up to 4 feature channels
+    __shared__ uint8_t s_mask[BLEND_BATCH];               // bit w: may reach warp w's patch
+    __shared__ uint8_t s_list[BLEND_WARPS][BLEND_BATCH];  // per-warp surviving batch indices
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = blockIdx.x;
-    const int tile_x = tile % grid_x, tile_y = tile / grid_x;
-    const int px = tile_x * SL_TILE_X + (warp & 1) * 8 + (lane & 7);
-    const int py = tile_y * SL_TILE_Y + (warp >> 1) * 4 + (lane >> 3);
+    const int tile = tile_order[blockIdx.x];
+    const PatchGeom pg = patch_geom(tile, grid_x, warp, lane);
+    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+    const int px = pg.px, py = pg.py;
     const bool inside = px < W && py < H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixf_x = (float)px, pixf_y = (float)py;
 
     const uint2 range = ranges[tile];
-    const int rounds = ((int)(range.y - range.x) + SL_TILE_PIX - 1) / SL_TILE_PIX;
-    int todo = range.y - range.x;
+    const int total = range.y - range.x;
+    const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
 
     bool done = !inside;
     float T = 1.0f;
-    uint32_t contributor = 0, last_contributor = 0;
+    uint32_t last_contributor = 0;
     float acc[C];
 #pragma unroll
     for (int ch = 0; ch < C; ++ch) acc[ch] = 0.f;
     float D = 0.f;
 
-    for (int i = 0; i < rounds; ++i, todo -= SL_TILE_PIX) {
+    for (int i = 0; i < rounds; ++i) {
         if (__syncthreads_count(done) == SL_TILE_PIX) break;
 
-        const int progress = i * SL_TILE_PIX + tid;
-        if (range.x + progress < range.y) {
-            const int id = point_list[range.x + progress];
+        const int n = min(BLEND_BATCH, total - i * BLEND_BATCH);
+        if (tid < n) {
+            const int id = point_list[range.x + i * BLEND_BATCH + tid];
             const float2 xy = means2D[id];
+            const float4 co = conic_opacity[id];
             s_xyd[tid] = make_float4(xy.x, xy.y, depths[id], 0.f);
-            s_co[tid] = conic_opacity[id];
+            s_co[tid] = co;
             if (C == 4) {
                 s_col[tid] = reinterpret_cast<const float4*>(features)[id];
             } else {
@@ -73,38 +80,45 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                 if (C > 2) f.z = features[id * C + 2];
                 s_col[tid] = f;
             }
+            s_mask[tid] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
         }
         __syncthreads();
 
         // A warp whose 32 pixels are all finished only helps with staging.
         if (__all_sync(0xffffffffu, done)) continue;
 
-        const int n = min(SL_TILE_PIX, todo);
-        for (int j = 0; !done && j < n; ++j) {
-            contributor++;
-            const float4 xyd = s_xyd[j];
-            const float4 co = s_co[j];
-            const float dx = __fsub_rn(xyd.x, pixf_x);
-            const float dy = __fsub_rn(xyd.y, pixf_y);
-            const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
-            const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
-            const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
-            const float power = __fmaf_rn(s, -0.5f, -t3);
-            if (power > 0.0f) continue;
+        uint8_t* list = s_list[warp];
+        const int cnt = compact_batch(list, n, lane, [&](int j) { return (s_mask[j] >> warp) & 1; });
+        const uint32_t base = (uint32_t)i * BLEND_BATCH + 1u;   // list position (1-based) of batch entry 0
 
-            const float alpha = fminf(0.99f, __fmul_rn(co.w, __expf(power)));
-            if (alpha < 1.0f / 255.0f) continue;
-            const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
-
-            const float4 f = s_col[j];
-            acc[0] = __fmaf_rn(T, __fmul_rn(alpha, f.x), acc[0]);
-            if (C > 1) acc[1] = __fmaf_rn(T, __fmul_rn(alpha, f.y), acc[1]);
-            if (C > 2) acc[2] = __fmaf_rn(T, __fmul_rn(alpha, f.z), acc[2]);
-            if (C > 3) acc[3] = __fmaf_rn(T, __fmul_rn(alpha, f.w), acc[3]);
-            D = __fmaf_rn(T, __fmul_rn(alpha, xyd.z), D);
-            T = test_T;
-            last_contributor = contributor;
-            if (test_T < 0.0001f) done = true;
+        for (int k = 0; k < cnt; ++k) {
+            const int j = list[k];
+            if (!done) {
+                const float4 xyd = s_xyd[j];
+                const float4 co = s_co[j];
+                const float dx = __fsub_rn(xyd.x, pixf_x);
+                const float dy = __fsub_rn(xyd.y, pixf_y);
+                const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
+                const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
+                const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
+                const float power = __fmaf_rn(s, -0.5f, -t3);
+                if (!(power > 0.0f)) {
+                    const float alpha = fminf(0.99f, __fmul_rn(co.w, __expf(power)));
+                    if (!(alpha < 1.0f / 255.0f)) {
+                        const float test_T = __fmul_rn(T, __fsub_rn(1.0f, alpha));
+                        const float4 f = s_col[j];
+                        acc[0] = __fmaf_rn(T, __fmul_rn(alpha, f.x), acc[0]);
+                        if (C > 1) acc[1] = __fmaf_rn(T, __fmul_rn(alpha, f.y), acc[1]);
+                        if (C > 2) acc[2] = __fmaf_rn(T, __fmul_rn(alpha, f.z), acc[2]);
+                        if (C > 3) acc[3] = __fmaf_rn(T, __fmul_rn(alpha, f.w), acc[3]);
+                        D = __fmaf_rn(T, __fmul_rn(alpha, xyd.z), D);
+                        T = test_T;
+                        last_contributor = base + j;
+                        if (test_T < 0.0001f) done = true;
+                    }
+                }
+            }
+            if (__all_sync(0xffffffffu, done)) break;
         }
     }
 
@@ -118,17 +132,18 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     }
 }
 
-int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+                         const uint32_t* point_list,
                          const float2* means2D, const float* features, const float* depths,
                          const float4* conic_opacity, const float* bg, float* out_color,
                          float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream)
 {
     const int tiles = vp.grid_x * vp.grid_y;
     if (C == 4)
-        blend_forward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x,
+        blend_forward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x,
             means2D, features, depths, conic_opacity, bg, out_color, out_depth, out_alpha, n_contrib);
     else if (C == 3)
-        blend_forward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, point_list, vp.W, vp.H, vp.grid_x,
+        blend_forward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x,
             means2D, features, depths, conic_opacity, bg, out_color, out_depth, out_alpha, n_contrib);
     else {
         set_error("blend_forward: unsupported channel count %d (3 or 4)", C);

@@ -289,6 +289,7 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     {
         StageTimer t(ST_RANGES, stream);
         rc = launch_tile_ranges(R, bin.point_list_keys, img.ranges, n_tiles, stream);
+        if (rc == 0) rc = launch_tile_order(img.ranges, img.tile_order, n_tiles, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile ranges");
@@ -296,7 +297,7 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
     {
         StageTimer t(ST_BLEND_FWD, stream);
-        rc = launch_blend_forward(C, vp, img.ranges, bin.point_list, geom.means2D, features, geom.depths,
+        rc = launch_blend_forward(C, vp, img.ranges, img.tile_order, bin.point_list, geom.means2D, features, geom.depths,
                                   geom.conic_opacity, background, out_color, out_depth, out_alpha, img.n_contrib,
                                   stream);
     }
@@ -353,7 +354,7 @@ int sl_backward(int P, int D, int M, int R, int C,
     int rc;
     {
         StageTimer t(ST_BLEND_BWD, stream);
-        rc = launch_blend_backward(C, vp, img.ranges, bin.point_list, background, geom.means2D,
+        rc = launch_blend_backward(C, vp, img.ranges, img.tile_order, bin.point_list, background, geom.means2D,
                                    geom.conic_opacity, color_ptr, geom.depths, accum_alphas, img.n_contrib,
                                    dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic,
                                    dL_dopacity, dL_dcolor, dL_ddepth, stream);

@@ -42,14 +42,20 @@ int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
 // K5: per-tile [first, last+1) ranges (reference: identifyTileRanges, rasterizer_impl.cu:137-159).
 int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_tiles, cudaStream_t stream);
 
+// Tile ids ordered by decreasing list length: CTAs are dispatched in blockIdx order, so the
+// longest tiles start first and the short ones fill the tail (no reference counterpart).
+int launch_tile_order(const uint2* ranges, uint32_t* order, int n_tiles, cudaStream_t stream);
+
 // K6: forward alpha blending per 16x16 tile (reference: renderCUDA, forward.cu:844-963).
-int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+                         const uint32_t* point_list,
                          const float2* means2D, const float* features, const float* depths,
                          const float4* conic_opacity, const float* bg, float* out_color,
                          float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream);
 
 // K7: backward blending (reference: BACKWARD::render, backward.cu:1018-1209).
-int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* point_list,
+int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+                          const uint32_t* point_list,
                           const float* bg, const float2* means2D, const float4* conic_opacity,
                           const float* colors, const float* depths, const float* out_alpha,
                           const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,

@@ -65,12 +65,15 @@ struct GeomState {
 struct ImageState {
     uint32_t* n_contrib;  // [N] last contributing list position per pixel
     uint2* ranges;        // [Tn] [first, last+1) in the sorted pair list
+    // --- own scratch ---
+    uint32_t* tile_order; // [Tn] tile ids, longest list first (launch order of the blend CTAs)
 
     static ImageState from_chunk(char*& chunk, size_t N, size_t Tn)
     {
         ImageState s;
         carve(chunk, s.n_contrib, N);
         carve(chunk, s.ranges, Tn);
+        carve(chunk, s.tile_order, Tn);
         return s;
     }
 };
