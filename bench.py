@@ -234,6 +234,10 @@ def run_gpu(args, impl):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item()), wall, prof
 
+    sampler = ClockSampler(local)
+    if not os.environ.get("BENCH_NO_SAMPLER"):
+        sampler.start()       # started before the spin-up: nvidia-smi's own start-up (NVML init) perturbs launches
+
     # Spin-up, untimed: a fresh process on a fresh box needs a moment until step times settle (idle
     # GPU clocks, first-touch paging of the image); run batches of steps until two consecutive
     # batches agree within 3 %, for at least 1 s and at most 10 s.
@@ -254,9 +258,7 @@ def run_gpu(args, impl):
     if impl == "ours":
         from splatloc_b200 import _capi
         launches0 = _capi.load().sl_launch_count()
-    sampler = ClockSampler(local)
-    if not os.environ.get("BENCH_NO_SAMPLER"):
-        sampler.start()
+    sampler.lines.clear()    # keep only samples taken during the timed region
     ms_total, wall, _ = timed(step_resident, args.steps, args.warmup)
     clocks = sampler.stop()
     launches = (_capi.load().sl_launch_count() - launches0) if impl == "ours" else 0

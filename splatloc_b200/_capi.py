@@ -9,7 +9,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libsplatloc_b200.so")
+# SPLATLOC_B200_LIB: load another build of the same library (kernel tuning experiments)
+LIB_PATH = os.environ.get("SPLATLOC_B200_LIB") or os.path.join(_HERE, "libsplatloc_b200.so")
 
 ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
 

@@ -48,6 +48,8 @@ def _headers_mtime() -> float:
 
 def _compile(src: str, verbose: bool, extra: list[str]) -> str:
     obj = os.path.join(BUILD, src[:-3] + ".o")
+    # SL_NVCC_EXTRA: extra flags for tuning experiments, e.g. "-DSL_BLEND_CTA_WARPS=8"
+    extra = [*extra, *os.environ.get("SL_NVCC_EXTRA", "").split()]
     cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-c", os.path.join(CSRC, src), "-o", obj]
     if verbose:
         print(" ".join(cmd), flush=True)

@@ -70,7 +70,7 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 }  // namespace
 
 template <int C>
-__global__ void __launch_bounds__(SL_TILE_PIX)
+__global__ void __launch_bounds__(BLEND_THREADS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const uint32_t* __restrict__ point_list,
                       int W, int H, int grid_x, const float* __restrict__ bg,
@@ -86,21 +86,21 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       float* __restrict__ dL_dcolor,      // (P,C)
                       float* __restrict__ dL_ddepth)      // (P,1)
 {
-    __shared__ int s_id[BLEND_BATCH];
-    __shared__ float4 s_xyd[BLEND_BATCH];
-    __shared__ float4 s_co[BLEND_BATCH];
-    __shared__ float4 s_col[BLEND_BATCH];
+    __shared__ Staged s_rec[BLEND_BATCH];
     __shared__ uint8_t s_mask[BLEND_BATCH];
     __shared__ uint8_t s_list[BLEND_WARPS][BLEND_BATCH];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = tile_order[blockIdx.x];
-    const PatchGeom pg = patch_geom(tile, grid_x, warp, lane);
+    const int tile = tile_order[blockIdx.x / BLEND_SUBS];
+    const int patch = (blockIdx.x % BLEND_SUBS) * BLEND_WARPS + warp;   // this warp's patch of the tile
+    const PatchGeom pg = patch_geom(tile, grid_x, patch, lane);
     const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
     const int px = pg.px, py = pg.py;
     const bool inside = px < W && py < H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixf_x = (float)px, pixf_y = (float)py;
+
+    const uint32_t list_a = smem_addr(s_list[warp]), rec_a = smem_addr(s_rec);
 
     const uint2 range = ranges[tile];
     const int total = range.y - range.x;
@@ -171,44 +171,44 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         const int n = min(BLEND_BATCH, total - i * BLEND_BATCH);
         if (hi_pos - (n - 1) >= block_last) continue;   // uniform over the CTA
         __syncthreads();
-        if (tid < n) {
-            const int id = point_list[range.x + hi_pos - tid];
-            s_id[tid] = id;
+        for (int t = tid; t < n; t += BLEND_THREADS) {
+            const int id = point_list[range.x + hi_pos - t];
             const float2 xy = means2D[id];
             const float4 co = conic_opacity[id];
-            s_xyd[tid] = make_float4(xy.x, xy.y, depths[id], 0.f);
-            s_co[tid] = co;
+            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
             if (C == 4) {
-                s_col[tid] = reinterpret_cast<const float4*>(colors)[id];
+                f = reinterpret_cast<const float4*>(colors)[id];
             } else {
-                float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
                 f.x = colors[id * C + 0];
                 if (C > 1) f.y = colors[id * C + 1];
                 if (C > 2) f.z = colors[id * C + 2];
-                s_col[tid] = f;
             }
-            s_mask[tid] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
+            s_rec[t].xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float(id));
+            s_rec[t].co = co;
+            s_rec[t].col = f;
+            s_mask[t] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
         }
         __syncthreads();
 
         uint8_t* list = s_list[warp];
         const int cnt = compact_batch(list, n, lane, [&](int j) {
-            return ((s_mask[j] >> warp) & 1) && (hi_pos - j < warp_last);
+            return ((s_mask[j] >> patch) & 1) && (hi_pos - j < warp_last);
         });
 
         for (int k = 0; k < cnt; ++k) {
-            const int j = list[k];
+            const int j = (int)lds_u8(list_a + k);
             const int pos = hi_pos - j;   // 0-based list position == the reference's `contributor`
+            const uint32_t ra = rec_a + (uint32_t)j * (uint32_t)sizeof(Staged);
 
-            const float4 xyd = s_xyd[j];
-            const float4 co = s_co[j];
+            const float4 xyd = lds128(ra);
+            const float4 co = lds128(ra + 16);
             const float dx = __fsub_rn(xyd.x, pixf_x);
             const float dy = __fsub_rn(xyd.y, pixf_y);
             const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
             const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
             const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
             const float power = __fmaf_rn(s, -0.5f, -t3);
-            const float G = __expf(power);
+            const float G = exp_like_reference(power);
             const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
             const bool blend = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(FULL, blend)) continue;
@@ -221,7 +221,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 T = T / (1.f - alpha);
                 const float w = alpha * T;
                 float dL_dalpha = 0.0f;
-                const float4 f = s_col[j];
+                const float4 f = lds128(ra + 32);
                 const float c4[4] = {f.x, f.y, f.z, f.w};
 #pragma unroll
                 for (int ch = 0; ch < C; ++ch) {
@@ -265,7 +265,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
             const float total_v = warp_transpose_reduce16(v, lane);
             if (flush_base != nullptr) {
-                const int gid = s_id[j];
+                const int gid = __float_as_int(xyd.w);
                 atomicAdd(flush_base + (size_t)gid * flush_stride, total_v);
             }
         }
@@ -283,11 +283,11 @@ int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, cons
 {
     const int tiles = vp.grid_x * vp.grid_y;
     if (C == 4)
-        blend_backward_kernel<4><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
+        blend_backward_kernel<4><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
             means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
             dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
     else if (C == 3)
-        blend_backward_kernel<3><<<tiles, SL_TILE_PIX, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
+        blend_backward_kernel<3><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
             means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
             dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
     else {

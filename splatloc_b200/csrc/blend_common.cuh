@@ -18,8 +18,17 @@
 
 namespace sl {
 
-constexpr int BLEND_BATCH = SL_TILE_PIX;   // 256 entries per staged batch
-constexpr int BLEND_WARPS = SL_TILE_PIX / 32;
+constexpr int BLEND_BATCH = 256;           // entries per staged batch
+// A CTA owns BLEND_WARPS of a tile's 8 patches (a half tile by default): finer CTAs balance the
+// SMs better at the end of the launch and keep fewer warps waiting at each batch barrier, at the
+// price of staging every list 8 / BLEND_WARPS times.
+#ifndef SL_BLEND_CTA_WARPS
+#define SL_BLEND_CTA_WARPS 4
+#endif
+constexpr int BLEND_WARPS = SL_BLEND_CTA_WARPS;
+constexpr int BLEND_THREADS = BLEND_WARPS * 32;
+constexpr int BLEND_SUBS = 8 / BLEND_WARPS;   // CTAs per tile
+static_assert(BLEND_WARPS == 1 || BLEND_WARPS == 2 || BLEND_WARPS == 4 || BLEND_WARPS == 8, "patches per CTA");
 
 struct PatchGeom {
     int px, py;          // this thread's pixel
@@ -27,6 +36,7 @@ struct PatchGeom {
     float wy0, wy1;
 };
 
+// `warp` is the patch index inside the tile, 0..7 (two columns x four rows of 8x4 pixels).
 __device__ __forceinline__ PatchGeom patch_geom(int tile, int grid_x, int warp, int lane)
 {
     const int tile_x = tile % grid_x, tile_y = tile / grid_x;
@@ -70,6 +80,44 @@ __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4&
     for (int r = 0; r < 4; ++r)
         if (rows & (1u << r)) m |= cols << (2 * r);
     return m;
+}
+
+// One staged list entry: 48 bytes, read with three 16-byte shared loads off one base address.
+struct __align__(16) Staged {
+    float4 xyd;   // pixel-space x, y, view depth, Gaussian id (bit pattern)
+    float4 co;    // conic xx, xy, yy, opacity
+    float4 col;   // up to 4 feature channels
+};
+
+// Shared-space (32-bit) addressing done by hand: with generic pointers the compiler re-derives the
+// CTA's shared window base (S2R SR_CgaCtaId + shifts) inside the inner loop.
+__device__ __forceinline__ uint32_t smem_addr(const void* p)
+{
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+    asm volatile("mov.u32 %0, %0;" : "+r"(a));   // opaque: keeps the address in a register instead of
+    return a;                                     // letting the compiler rematerialise it per use
+}
+__device__ __forceinline__ float4 lds128(uint32_t a)
+{
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+    return v;
+}
+__device__ __forceinline__ uint32_t lds_u8(uint32_t a)
+{
+    uint32_t v;
+    asm volatile("ld.shared.u8 %0, [%1];" : "=r"(v) : "r"(a));
+    return v;
+}
+
+// exp(x) exactly as the reference's __expf computes it for every x that can still pass the alpha
+// test: __expf(x) = ex2.approx(x * log2e) with a rescaling guard that only acts below 2^-126, where
+// alpha = o * exp(x) is far under 1/255 anyway; .ftz drops the guard (3 instructions per evaluation).
+__device__ __forceinline__ float exp_like_reference(float x)
+{
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(__fmul_rn(x, 1.4426950216293334961f)));
+    return r;
 }
 
 // Order-preserving compaction of the staged batch into this warp's private list.

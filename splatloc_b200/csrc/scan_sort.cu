@@ -139,7 +139,8 @@ constexpr uint32_t LB_VALUE = ~LB_FLAGS;
 
 // Histogram of every digit place in one read of the keys.
 __global__ void __launch_bounds__(256)
-sort_histogram_kernel(const uint64_t* __restrict__ keys, int n, int passes, uint32_t* __restrict__ hist)
+sort_histogram_kernel(const uint64_t* __restrict__ keys, int n, int passes, int aggregate_from,
+                      uint32_t* __restrict__ hist)
 {
     __shared__ uint32_t s_hist[SORT_MAX_PASSES * SORT_RADIX];
     for (int i = threadIdx.x; i < passes * SORT_RADIX; i += blockDim.x) s_hist[i] = 0;
@@ -153,10 +154,14 @@ sort_histogram_kernel(const uint64_t* __restrict__ keys, int n, int passes, uint
         if (valid) {
             for (int p = 0; p < passes; ++p) {
                 const uint32_t d = (uint32_t)(k >> (p * SORT_RADIX_BITS)) & (SORT_RADIX - 1);
-                // Upper digit places hold tile-id bits shared by most of a warp:
-                // aggregate equal digits before touching shared memory.
-                const unsigned peers = __match_any_sync(act, d);
-                if (lane == __ffs(peers) - 1) atomicAdd(&s_hist[p * SORT_RADIX + d], (uint32_t)__popc(peers));
+                if (p < aggregate_from) {
+                    atomicAdd(&s_hist[p * SORT_RADIX + d], 1u);   // low (depth mantissa) digits: spread out
+                } else {
+                    // Upper digit places (exponent / tile-id bits) are shared by most of a warp:
+                    // aggregate equal digits before touching shared memory.
+                    const unsigned peers = __match_any_sync(act, d);
+                    if (lane == __ffs(peers) - 1) atomicAdd(&s_hist[p * SORT_RADIX + d], (uint32_t)__popc(peers));
+                }
             }
         }
     }
@@ -263,13 +268,26 @@ sort_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restric
         st_volatile_u32(mine, LB_INCL | count);
     } else {
         st_volatile_u32(mine, LB_AGG | count);
+        // Walk back over the predecessors LB_WINDOW at a time: the loads of one window are
+        // independent, so a window costs one L2 round trip instead of LB_WINDOW of them.
+        constexpr int LB_WINDOW = 8;
         int p = bid - 1;
-        while (true) {
-            const uint32_t v = ld_volatile_u32(lookback + (size_t)p * SORT_RADIX + tid);
-            if ((v & LB_FLAGS) == 0) continue;
-            prefix += v & LB_VALUE;
-            if (v & LB_INCL) break;
-            --p;
+        bool found = false;
+        while (!found) {
+            uint32_t v[LB_WINDOW];
+#pragma unroll
+            for (int k = 0; k < LB_WINDOW; ++k)
+                v[k] = (p - k >= 0) ? ld_volatile_u32(lookback + (size_t)(p - k) * SORT_RADIX + tid) : LB_INCL;
+#pragma unroll
+            for (int k = 0; k < LB_WINDOW; ++k) {
+                if (!found) {
+                    uint32_t x = v[k];
+                    while ((x & LB_FLAGS) == 0) x = ld_volatile_u32(lookback + (size_t)(p - k) * SORT_RADIX + tid);
+                    prefix += x & LB_VALUE;
+                    found = (x & LB_INCL) != 0;
+                }
+            }
+            p -= LB_WINDOW;
         }
         st_volatile_u32(mine, LB_INCL | (prefix + count));
     }
@@ -342,7 +360,7 @@ int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
                                  (int)sizeof(SortSmem)), "sort smem attribute");
     SL_CUDA(cudaMemsetAsync(sc.histograms, 0, sc.zero_bytes, stream), "sort memset");
     const int hist_blocks = min(ceil_div(n, 256 * 8), 148 * 8);
-    sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, sc.histograms); count_launch();
+    sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, /*aggregate_from=*/3, sc.histograms); count_launch();
     sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(sc.histograms); count_launch();
 
     const int blocks = (int)sc.sort_blocks;

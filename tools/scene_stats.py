@@ -29,7 +29,7 @@ for cs in range(3):
     # culling headroom on a sample of tiles
     g = torch.Generator().manual_seed(0)
     tiles = torch.randperm(1200, generator=g)[:150].tolist()
-    tot_wg = any_wg = tot_pg = any_pg = 0
+    tot_wg = any_wg = tot_pg = any_pg = aabb_wg = 0
     for tl in tiles:
         lo, hi = int(ranges[tl, 0]), int(ranges[tl, 1])
         if hi <= lo:
@@ -50,6 +50,14 @@ for cs in range(3):
         w = k2.view(4, 4, 2, 8, -1).permute(0, 2, 1, 3, 4).reshape(8, 32, -1)   # 8 patches of 8x4
         lw = live.view(4, 4, 2, 8, -1).permute(0, 2, 1, 3, 4).reshape(8, 32, -1)
         tot_wg += int(lw.any(1).sum()); any_wg += int(w.any(1).sum())
+        # AABB of the alpha >= 1/255 ellipse vs each 8x4 patch
+        t2 = 2 * torch.log(255 * co[:, 3])
+        det = co[:, 0] * co[:, 2] - co[:, 1] ** 2
+        hx = torch.sqrt(torch.clamp_min(t2, 0) * co[:, 2] / det); hy = torch.sqrt(torch.clamp_min(t2, 0) * co[:, 0] / det)
+        for wq in range(8):
+            x0 = tx * 16 + (wq & 1) * 8; y0 = ty * 16 + (wq >> 1) * 4
+            hit = (xy[:, 0] + hx >= x0) & (xy[:, 0] - hx <= x0 + 7) & (xy[:, 1] + hy >= y0) & (xy[:, 1] - hy <= y0 + 3) & (t2 > 0)
+            aabb_wg += int((hit & lw[wq].any(0)).sum())
         tot_pg += int(live.sum()); any_pg += int(k2.sum())
-    print(f"    sample: (patch,Gaussian) evaluated {tot_wg}, with >=1 blending pixel {any_wg} ({100*any_wg/max(tot_wg,1):.1f}%); "
+    print(f"    sample: (patch,Gaussian) evaluated {tot_wg}, with >=1 blending pixel {any_wg} ({100*any_wg/max(tot_wg,1):.1f}%), AABB survivors {aabb_wg} ({100*aabb_wg/max(tot_wg,1):.1f}%); "
           f"(pixel,Gaussian) evaluated {tot_pg}, blended {any_pg} ({100*any_pg/max(tot_pg,1):.1f}%)")
