@@ -103,7 +103,7 @@ def algorithmic_bytes(P, V, R, N, Tn, C, M_sh=0):
         "scan": 8 * P,
         "emit_pairs": 16 * V + 8 * P + 12 * R,
         "sort_pairs": 24 * R,
-        "tile_ranges": 8 * R + 8 * Tn,
+        "pair_records": 8 * R + 8 * Tn + (12 + 28 + 4 * C) * R + 49 * R,   # K5 ranges + gather -> records/masks
         "blend_forward": (32 + 4 * C) * R + (12 + 4 * C) * N,
         "blend_backward": (32 + 4 * C) * R + (16 + 4 * C) * N + (36 + 4 * C) * R,
         "preprocess_backward": 4 * P + 164 * V + (92 + 4 * C + 12 * M_sh) * P,

@@ -8,6 +8,7 @@
 // K5  per-tile [first, last+1) ranges in the sorted list
 //     (reference: identifyTileRanges, rasterizer_impl.cu:137-159).
 #include "kernels.h"
+#include "blend_common.cuh"
 
 namespace sl {
 
@@ -59,6 +60,69 @@ tile_ranges_kernel(int L, const uint64_t* __restrict__ keys, uint2* __restrict__
         }
     }
     if (idx == L - 1) ranges[cur].y = L;
+}
+
+// One thread per sorted pair: gather the Gaussian's screen-space data into a PairRecord, compute
+// which 8x4 patches of the pair's tile it can reach (blend_common.cuh), and mark tile boundaries
+// (the reference's identifyTileRanges).  After this kernel the blend kernels never touch the
+// per-Gaussian arrays or point_list again: they stream `records` / `masks` linearly.
+template <int C>
+__global__ void __launch_bounds__(256)
+build_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
+                     const float2* __restrict__ means2D, const float* __restrict__ depths,
+                     const float4* __restrict__ conic_opacity, const float* __restrict__ features,
+                     int grid_x, PairRecord* __restrict__ records, uint8_t* __restrict__ masks,
+                     uint2* __restrict__ ranges)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= R) return;
+    const uint32_t tile = (uint32_t)(keys[i] >> 32);
+    if (i == 0) {
+        ranges[tile].x = 0;
+    } else {
+        const uint32_t prev = (uint32_t)(keys[i - 1] >> 32);
+        if (tile != prev) {
+            ranges[prev].y = i;
+            ranges[tile].x = i;
+        }
+    }
+    if (i == R - 1) ranges[tile].y = R;
+
+    const int id = point_list[i];
+    const float2 xy = means2D[id];
+    const float4 co = conic_opacity[id];
+    float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (C == 4) {
+        f = reinterpret_cast<const float4*>(features)[id];
+    } else {
+        f.x = features[id * C + 0];
+        if (C > 1) f.y = features[id * C + 1];
+        if (C > 2) f.z = features[id * C + 2];
+    }
+    PairRecord rec;
+    rec.xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float(id));
+    rec.co = co;
+    rec.col = f;
+    records[i] = rec;
+    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+    masks[i] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
+}
+
+int launch_build_records(int R, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
+                         const GeomState& g, const float* features, int grid_x, int n_tiles,
+                         PairRecord* records, uint8_t* masks, uint2* ranges, cudaStream_t stream)
+{
+    SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream), "ranges memset");
+    if (R > 0) {
+        if (C == 4)
+            build_records_kernel<4><<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, point_list, g.means2D, g.depths,
+                g.conic_opacity, features, grid_x, records, masks, ranges);
+        else
+            build_records_kernel<3><<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, point_list, g.means2D, g.depths,
+                g.conic_opacity, features, grid_x, records, masks, ranges);
+        count_launch();
+    }
+    return 0;
 }
 
 // Counting sort of the tiles by list length, longest first; one CTA, any number of tiles.

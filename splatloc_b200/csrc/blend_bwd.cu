@@ -7,7 +7,10 @@
 //     per-Gaussian partial gradients leave the CTA.
 //
 //     The reference issues 9 + C global float atomics per blended
-//     (pixel, Gaussian) pair.  Here a warp owns an 8x4 pixel patch; for every
+//     (pixel, Gaussian) pair.  Here a warp owns an 8x4 pixel patch and streams
+//     the tile's PairRecords back to front on its own (blend_common.cuh; same
+//     chunked survivor pipeline as the forward, starting at the patch's largest
+//     n_contrib); for every
 //     Gaussian that at least one of its 32 pixels blends, the partials are
 //     reduced across the warp with a 16-shuffle transpose-reduction (16 values,
 //     halving the live set at each of the 5 butterfly levels) and the 9 + C sums
@@ -72,10 +75,8 @@ __device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lan
 template <int C>
 __global__ void __launch_bounds__(BLEND_THREADS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
-                      const uint32_t* __restrict__ point_list,
+                      const PairRecord* __restrict__ records, const uint8_t* __restrict__ masks,
                       int W, int H, int grid_x, const float* __restrict__ bg,
-                      const float2* __restrict__ means2D, const float4* __restrict__ conic_opacity,
-                      const float* __restrict__ colors, const float* __restrict__ depths,
                       const float* __restrict__ out_alpha, const uint32_t* __restrict__ n_contrib,
                       const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
                       const float* __restrict__ dL_dpix_alpha,
@@ -86,25 +87,22 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       float* __restrict__ dL_dcolor,      // (P,C)
                       float* __restrict__ dL_ddepth)      // (P,1)
 {
-    __shared__ Staged s_rec[BLEND_BATCH];
-    __shared__ uint8_t s_mask[BLEND_BATCH];
-    __shared__ uint8_t s_list[BLEND_WARPS][BLEND_BATCH];
+    __shared__ PairRecord s_rec[BLEND_WARPS][BLEND_CHUNK];
+    __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = tile_order[blockIdx.x / BLEND_SUBS];
-    const int patch = (blockIdx.x % BLEND_SUBS) * BLEND_WARPS + warp;   // this warp's patch of the tile
+    const int patch = (blockIdx.x % BLEND_SUBS) * BLEND_WARPS + warp;
     const PatchGeom pg = patch_geom(tile, grid_x, patch, lane);
-    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
     const int px = pg.px, py = pg.py;
     const bool inside = px < W && py < H;
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixf_x = (float)px, pixf_y = (float)py;
-
-    const uint32_t list_a = smem_addr(s_list[warp]), rec_a = smem_addr(s_rec);
+    const uint32_t rec_a = smem_addr(&s_rec[warp][0]), lane_a = smem_addr(&s_lane[warp][0]);
+    const unsigned lt = (1u << lane) - 1u;
 
     const uint2 range = ranges[tile];
-    const int total = range.y - range.x;
-    const int rounds = (total + BLEND_BATCH - 1) / BLEND_BATCH;
+    const int lo = range.x;
 
     const float T_final = inside ? (1 - out_alpha[pix_id]) : 0;
     float T = T_final;
@@ -127,6 +125,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     float bg_dot_dpixel = 0.f;
 #pragma unroll
     for (int ch = 0; ch < C; ++ch) bg_dot_dpixel += bg[ch] * dL_dpixel[ch];
+    const float neg_Tfinal_bg = -T_final * bg_dot_dpixel;
 
     const float ddelx_dx = 0.5 * W;
     const float ddely_dy = 0.5 * H;
@@ -152,54 +151,19 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         }
     }
 
-    // Entries at list positions >= the warp's largest n_contrib are never blended by it.
+    // Entries at list positions >= the patch's largest n_contrib are never blended by it:
+    // the walk starts there (positions are 0-based here, like the reference's `contributor`).
     int warp_last = last_contributor;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(FULL, warp_last, o));
+    if (warp_last == 0) return;
 
-    // The whole CTA can skip the batches that lie entirely behind its last contributor.
-    __shared__ int s_block_last;
-    if (tid == 0) s_block_last = 0;
-    __syncthreads();
-    if (lane == 0) atomicMax(&s_block_last, warp_last);
-    __syncthreads();
-    const int block_last = s_block_last;
-
-    for (int i = 0; i < rounds; ++i) {
-        // batch i holds list positions (0-based) hi_pos, hi_pos-1, ... in that order
-        const int hi_pos = total - 1 - i * BLEND_BATCH;
-        const int n = min(BLEND_BATCH, total - i * BLEND_BATCH);
-        if (hi_pos - (n - 1) >= block_last) continue;   // uniform over the CTA
-        __syncthreads();
-        for (int t = tid; t < n; t += BLEND_THREADS) {
-            const int id = point_list[range.x + hi_pos - t];
-            const float2 xy = means2D[id];
-            const float4 co = conic_opacity[id];
-            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (C == 4) {
-                f = reinterpret_cast<const float4*>(colors)[id];
-            } else {
-                f.x = colors[id * C + 0];
-                if (C > 1) f.y = colors[id * C + 1];
-                if (C > 2) f.z = colors[id * C + 2];
-            }
-            s_rec[t].xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float(id));
-            s_rec[t].co = co;
-            s_rec[t].col = f;
-            s_mask[t] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
-        }
-        __syncthreads();
-
-        uint8_t* list = s_list[warp];
-        const int cnt = compact_batch(list, n, lane, [&](int j) {
-            return ((s_mask[j] >> patch) & 1) && (hi_pos - j < warp_last);
-        });
-
+    // Back-propagate through the `cnt` records parked in the warp's buffer; `top_pos` is the list
+    // position of the chunk's entry 0 (entries run towards the front of the list).
+    auto backprop_parked = [&](int cnt, int top_pos) {
         for (int k = 0; k < cnt; ++k) {
-            const int j = (int)lds_u8(list_a + k);
-            const int pos = hi_pos - j;   // 0-based list position == the reference's `contributor`
-            const uint32_t ra = rec_a + (uint32_t)j * (uint32_t)sizeof(Staged);
-
+            const uint32_t ra = rec_a + (uint32_t)k * (uint32_t)sizeof(PairRecord);
+            const int pos = top_pos - (int)lds_u8(lane_a + k);
             const float4 xyd = lds128(ra);
             const float4 co = lds128(ra + 16);
             const float dx = __fsub_rn(xyd.x, pixf_x);
@@ -215,10 +179,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
             float v[16];
 #pragma unroll
-            for (int k = 0; k < 16; ++k) v[k] = 0.f;
+            for (int q = 0; q < 16; ++q) v[q] = 0.f;
 
             if (blend) {
-                T = T / (1.f - alpha);
+                // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha)
+                const float inv = __frcp_rn(1.f - alpha);
+                T = T * inv;
                 const float w = alpha * T;
                 float dL_dalpha = 0.0f;
                 const float4 f = lds128(ra + 32);
@@ -229,8 +195,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
                     last_color[ch] = c;
                     const float dL_dchannel = dL_dpixel[ch];
-                    const float weight = (ch > 2) ? 0.0f : 1.0f;
-                    dL_dalpha += (c - accum_rec[ch]) * dL_dchannel * weight;
+                    if (ch <= 2) dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;   // channels >= 3 are masked out
                     v[ch] = w * dL_dchannel;
                 }
                 const float dep = xyd.z;
@@ -244,7 +209,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
                 dL_dalpha *= T;
                 last_alpha = alpha;
-                dL_dalpha += (-T_final / (1.f - alpha)) * bg_dot_dpixel;
+                dL_dalpha += neg_Tfinal_bg * inv;
 
                 const float dL_dG = co.w * dL_dalpha;
                 const float gdx = G * dx;
@@ -269,27 +234,59 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 atomicAdd(flush_base + (size_t)gid * flush_stride, total_v);
             }
         }
+    };
+
+    int parked = 0, parked_top = 0;
+    const int start = lo + warp_last - 1;                 // global index of the first entry to visit
+    uint32_t m_next = (start - lane >= lo) ? masks[start - lane] : 0u;
+
+    for (int t = start; t >= lo; t -= BLEND_CHUNK) {
+        const uint32_t m = m_next;
+        const bool bit = (t - lane >= lo) && ((m >> patch) & 1u);
+        const unsigned b = __ballot_sync(FULL, bit);
+        float4 r0, r1, r2;
+        if (bit) {
+            const float4* src = reinterpret_cast<const float4*>(records + (t - lane));
+            r0 = __ldg(src);
+            r1 = __ldg(src + 1);
+            r2 = __ldg(src + 2);
+        }
+        m_next = (t - BLEND_CHUNK - lane >= lo) ? masks[t - BLEND_CHUNK - lane] : 0u;
+
+        backprop_parked(parked, parked_top);
+
+        __syncwarp();
+        if (bit) {
+            const int slot = __popc(b & lt);
+            PairRecord* dst = &s_rec[warp][slot];
+            dst->xyd = r0;
+            dst->co = r1;
+            dst->col = r2;
+            s_lane[warp][slot] = (uint8_t)lane;
+        }
+        __syncwarp();
+        parked = __popc(b);
+        parked_top = t - lo;
     }
+    backprop_parked(parked, parked_top);
 }
 
 int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
-                          const uint32_t* point_list,
-                          const float* bg, const float2* means2D, const float4* conic_opacity,
-                          const float* colors, const float* depths, const float* out_alpha,
-                          const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,
-                          const float* dL_dpix_alpha, float* dL_dmean2D, float* dL_dabsmean2D,
-                          float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_ddepth,
-                          cudaStream_t stream)
+                          const PairRecord* records, const uint8_t* masks, const float* bg,
+                          const float* out_alpha, const uint32_t* n_contrib, const float* dL_dpix,
+                          const float* dL_dpix_depth, const float* dL_dpix_alpha, float* dL_dmean2D,
+                          float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                          float* dL_ddepth, cudaStream_t stream)
 {
     const int tiles = vp.grid_x * vp.grid_y;
     if (C == 4)
-        blend_backward_kernel<4><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
-            means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
-            dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
+        blend_backward_kernel<4><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
+            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_alpha, n_contrib, dL_dpix,
+            dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
     else if (C == 3)
-        blend_backward_kernel<3><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(ranges, tile_order, point_list, vp.W, vp.H, vp.grid_x, bg,
-            means2D, conic_opacity, colors, depths, out_alpha, n_contrib, dL_dpix, dL_dpix_depth,
-            dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
+        blend_backward_kernel<3><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
+            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_alpha, n_contrib, dL_dpix,
+            dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
     else {
         set_error("blend_backward: unsupported channel count %d (3 or 4)", C);
         return -2;

@@ -1,27 +1,28 @@
 // splatloc_b200/csrc/blend_common.cuh -- pieces shared by the forward and backward blend kernels.
 //
-// Work decomposition.  A CTA owns one 16x16 tile, a warp an 8x4 pixel patch of it.  The tile's
-// list is consumed in batches of 256 (tile, Gaussian) entries staged in shared memory.  While
-// staging, each thread also computes for its Gaussian the axis-aligned bounding box of the region
-// where it can pass the reference's alpha test at all:
+// Work decomposition.  A warp owns an 8x4 pixel patch of a 16x16 tile and walks the tile's sorted
+// list on its own: no shared staging between warps, no CTA barrier.  The list arrives as an array
+// of 48-byte PairRecords (state.cuh) plus one mask byte per pair, both written once per frame by
+// the binning stage (binning.cu).  Bit w of the mask says whether the Gaussian can pass the
+// reference's alpha test anywhere in patch w; it comes from the axis-aligned bounding box of
 //     alpha = min(0.99, o * exp(power)) >= 1/255   <=>   d^T Q d <= 2 ln(255 o),  Q = conic
-// whose box has half-widths  hx = sqrt(2 ln(255 o) * Qyy / det Q),  hy = sqrt(2 ln(255 o) * Qxx / det Q)
-// (padded by 0.2 % + 0.05 px, far more than any float32 / ex2.approx error).  Entries whose box
-// misses a warp's patch are dropped from that warp's private, order-preserving index list, so the
-// warp's inner loop only visits Gaussians that can contribute to one of its 32 pixels.  The test is
-// conservative, every surviving entry is still evaluated with the reference's exact arithmetic and
-// list positions are kept, so colour, depth, alpha and n_contrib stay bit-identical -- the
-// reference would have `continue`d on the dropped ones (forward.cu:925-931).  On the config-2
-// scene ~75 % of (patch, Gaussian) evaluations are dropped (tools/scene_stats.py).
+// whose half-widths are  hx = sqrt(2 ln(255 o) * Qyy / det Q),  hy = sqrt(2 ln(255 o) * Qxx / det Q)
+// (padded by 0.2 % + 0.05 px and 2e-5 in power units, far more than any float32 / ex2.approx
+// error).  A warp reads 32 mask bytes per step, ballots the survivors, fetches only their records
+// into a warp-private shared buffer (while it blends the previous chunk) and evaluates those with
+// the reference's exact arithmetic.  The test is conservative and list positions are kept, so
+// colour, depth, alpha and n_contrib stay bit-identical -- the reference would have `continue`d on
+// the dropped entries (forward.cu:925-931).  On the config-2 scene ~64 % of (patch, Gaussian)
+// evaluations are dropped (tools/scene_stats.py).
 #pragma once
 #include "common.cuh"
+#include "state.cuh"
 
 namespace sl {
 
-constexpr int BLEND_BATCH = 256;           // entries per staged batch
-// A CTA owns BLEND_WARPS of a tile's 8 patches (a half tile by default): finer CTAs balance the
-// SMs better at the end of the launch and keep fewer warps waiting at each batch barrier, at the
-// price of staging every list 8 / BLEND_WARPS times.
+constexpr int BLEND_CHUNK = 32;            // list entries examined per warp step
+// A CTA is BLEND_WARPS of a tile's 8 patches (a half tile by default).  Warps never synchronise
+// with each other; the CTA size only sets the granularity at which work is handed to the SMs.
 #ifndef SL_BLEND_CTA_WARPS
 #define SL_BLEND_CTA_WARPS 4
 #endif
@@ -82,13 +83,6 @@ __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4&
     return m;
 }
 
-// One staged list entry: 48 bytes, read with three 16-byte shared loads off one base address.
-struct __align__(16) Staged {
-    float4 xyd;   // pixel-space x, y, view depth, Gaussian id (bit pattern)
-    float4 co;    // conic xx, xy, yy, opacity
-    float4 col;   // up to 4 feature channels
-};
-
 // Shared-space (32-bit) addressing done by hand: with generic pointers the compiler re-derives the
 // CTA's shared window base (S2R SR_CgaCtaId + shifts) inside the inner loop.
 __device__ __forceinline__ uint32_t smem_addr(const void* p)
@@ -118,25 +112,6 @@ __device__ __forceinline__ float exp_like_reference(float x)
     float r;
     asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(__fmul_rn(x, 1.4426950216293334961f)));
     return r;
-}
-
-// Order-preserving compaction of the staged batch into this warp's private list.
-// keep(j) decides per staged entry; returns the number of entries kept.
-template <typename Keep>
-__device__ __forceinline__ int compact_batch(uint8_t* __restrict__ list, int n, int lane, Keep keep)
-{
-    int cnt = 0;
-    const unsigned lt = (1u << lane) - 1u;
-#pragma unroll 1
-    for (int c = 0; c * 32 < n; ++c) {
-        const int j = c * 32 + lane;
-        const bool bit = (j < n) && keep(j);
-        const unsigned b = __ballot_sync(0xffffffffu, bit);
-        if (bit) list[cnt + __popc(b & lt)] = (uint8_t)j;
-        cnt += __popc(b);
-    }
-    __syncwarp();
-    return cnt;
 }
 
 }  // namespace sl

@@ -50,7 +50,7 @@ enum Stage {
     ST_COUNT
 };
 static const char* const kStageNames[ST_COUNT] = {
-    "preprocess", "scan", "emit_pairs", "sort_pairs", "tile_ranges", "blend_forward", "blend_backward",
+    "preprocess", "scan", "emit_pairs", "sort_pairs", "pair_records", "blend_forward", "blend_backward",
     "preprocess_backward"};
 
 struct Profiler {
@@ -286,20 +286,20 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         SL_STAGE(dbg, stream, "sort");
     }
 
+    const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
     {
         StageTimer t(ST_RANGES, stream);
-        rc = launch_tile_ranges(R, bin.point_list_keys, img.ranges, n_tiles, stream);
+        rc = launch_build_records(R, C, bin.point_list_keys, bin.point_list, geom, features, vp.grid_x, n_tiles,
+                                  bin.records, bin.masks, img.ranges, stream);
         if (rc == 0) rc = launch_tile_order(img.ranges, img.tile_order, n_tiles, stream);
     }
     if (rc) return rc;
-    SL_STAGE(dbg, stream, "tile ranges");
+    SL_STAGE(dbg, stream, "pair records");
 
-    const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
     {
         StageTimer t(ST_BLEND_FWD, stream);
-        rc = launch_blend_forward(C, vp, img.ranges, img.tile_order, bin.point_list, geom.means2D, features, geom.depths,
-                                  geom.conic_opacity, background, out_color, out_depth, out_alpha, img.n_contrib,
-                                  stream);
+        rc = launch_blend_forward(C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background, out_color,
+                                  out_depth, out_alpha, img.n_contrib, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend forward");
@@ -350,14 +350,12 @@ int sl_backward(int P, int D, int M, int R, int C,
     ImageState img = ImageState::from_chunk(image_chunk, (size_t)width * height, n_tiles);
     if (radii == nullptr) radii = geom.internal_radii;
 
-    const float* color_ptr = (colors_precomp != nullptr) ? colors_precomp : geom.rgb;
     int rc;
     {
         StageTimer t(ST_BLEND_BWD, stream);
-        rc = launch_blend_backward(C, vp, img.ranges, img.tile_order, bin.point_list, background, geom.means2D,
-                                   geom.conic_opacity, color_ptr, geom.depths, accum_alphas, img.n_contrib,
-                                   dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic,
-                                   dL_dopacity, dL_dcolor, dL_ddepth, stream);
+        rc = launch_blend_backward(C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background,
+                                   accum_alphas, img.n_contrib, dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D,
+                                   dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend backward");

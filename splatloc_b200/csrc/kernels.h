@@ -46,22 +46,24 @@ int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_
 // longest tiles start first and the short ones fill the tail (no reference counterpart).
 int launch_tile_order(const uint2* ranges, uint32_t* order, int n_tiles, cudaStream_t stream);
 
+// Gather, once per frame, everything the blend kernels read for each sorted pair (PairRecord) plus
+// the per-patch reach mask, and write the per-tile ranges (reference: identifyTileRanges).
+int launch_build_records(int R, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
+                         const GeomState& g, const float* features, int grid_x, int n_tiles,
+                         PairRecord* records, uint8_t* masks, uint2* ranges, cudaStream_t stream);
+
 // K6: forward alpha blending per 16x16 tile (reference: renderCUDA, forward.cu:844-963).
 int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
-                         const uint32_t* point_list,
-                         const float2* means2D, const float* features, const float* depths,
-                         const float4* conic_opacity, const float* bg, float* out_color,
+                         const PairRecord* records, const uint8_t* masks, const float* bg, float* out_color,
                          float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream);
 
 // K7: backward blending (reference: BACKWARD::render, backward.cu:1018-1209).
 int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
-                          const uint32_t* point_list,
-                          const float* bg, const float2* means2D, const float4* conic_opacity,
-                          const float* colors, const float* depths, const float* out_alpha,
-                          const uint32_t* n_contrib, const float* dL_dpix, const float* dL_dpix_depth,
-                          const float* dL_dpix_alpha, float* dL_dmean2D, float* dL_dabsmean2D,
-                          float* dL_dconic, float* dL_dopacity, float* dL_dcolor, float* dL_ddepth,
-                          cudaStream_t stream);
+                          const PairRecord* records, const uint8_t* masks, const float* bg,
+                          const float* out_alpha, const uint32_t* n_contrib, const float* dL_dpix,
+                          const float* dL_dpix_depth, const float* dL_dpix_alpha, float* dL_dmean2D,
+                          float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
+                          float* dL_ddepth, cudaStream_t stream);
 
 // K8+K9 fused: per-Gaussian backward (reference: BACKWARD::preprocess, backward.cu:1810-1876).
 int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,

@@ -78,6 +78,13 @@ struct ImageState {
     }
 };
 
+// One (tile, Gaussian) pair as the blend kernels consume it: 48 bytes, three 16-byte loads.
+struct __align__(16) PairRecord {
+    float4 xyd;   // pixel-space x, y, view depth, Gaussian id (bit pattern)
+    float4 co;    // conic xx, xy, yy, opacity
+    float4 col;   // up to 4 feature channels
+};
+
 // Scratch of one radix sort of n (u64 key, u32 value) pairs.
 struct SortScratch {
     uint64_t* keys_tmp;      // [n] ping-pong
@@ -111,6 +118,8 @@ struct BinningState {
     uint64_t* point_list_keys;        // [R] sorted (tile << 32 | depth bits)
     uint64_t* point_list_keys_unsorted;  // [R]
     // --- own scratch ---
+    PairRecord* records;     // [R] per sorted pair: everything the blend kernels read, gathered once
+    uint8_t* masks;          // [R] bit w: the pair can reach the w-th 8x4 patch of its tile
     SortScratch sort;
 
     static BinningState from_chunk(char*& chunk, size_t R)
@@ -120,6 +129,8 @@ struct BinningState {
         carve(chunk, b.point_list_unsorted, R);
         carve(chunk, b.point_list_keys, R);
         carve(chunk, b.point_list_keys_unsorted, R);
+        carve(chunk, b.records, R);
+        carve(chunk, b.masks, R + 64);   // slack: the blend kernels prefetch one 32-entry chunk ahead
         b.sort = SortScratch::from_chunk(chunk, R);
         return b;
     }
