@@ -97,15 +97,17 @@ class ClockSampler:
 
 def algorithmic_bytes(P, V, R, N, Tn, C, M_sh=0):
     """Compulsory HBM bytes per stage: every stage reads its inputs and writes
-    its outputs exactly once."""
+    its outputs exactly once.  K2 (per-Gaussian prefix sum) has no counterpart in the
+    tile-bucketed binning; the bytes of K5 (ranges) are carried by tile_scan; the record gather
+    (44 + 4C in, 49 + 4C out per pair; no reference counterpart) is counted with the segment sort."""
     return {
         "preprocess": P * (44 + 12 * M_sh) + 8 * P + 52 * V,
-        "scan": 8 * P,
-        "emit_pairs": 16 * V + 8 * P + 12 * R,
-        "sort_pairs": 24 * R,
-        "pair_records": 8 * R + 8 * Tn + (12 + 28 + 4 * C) * R + 49 * R,   # K5 ranges + gather -> records/masks
-        "blend_forward": (32 + 4 * C) * R + (12 + 4 * C) * N,
-        "blend_backward": (32 + 4 * C) * R + (16 + 4 * C) * N + (36 + 4 * C) * R,
+        "tile_scan": 8 * Tn + 8 * Tn,
+        "emit_pairs": 16 * V + 4 * P + 12 * R,
+        "sort_pairs": 24 * R + (28 + 4 * C) * R + (33 + 4 * C) * R,
+        "pair_records": (12 + 28 + 4 * C) * R + (33 + 4 * C) * R,     # radix fallback only
+        "blend_forward": (33 + 4 * C) * R + (12 + 4 * C) * N,
+        "blend_backward": (33 + 4 * C) * R + (16 + 4 * C) * N + (36 + 4 * C) * R,
         "preprocess_backward": 4 * P + 164 * V + (92 + 4 * C + 12 * M_sh) * P,
     }
 

@@ -132,6 +132,12 @@ int sl_knn(int P, const float* points, float* mean_dists,
 /* Number of this library's kernels launched by the process so far. */
 long long sl_launch_count(void);
 
+/* Binning strategy of sl_forward: 0 (default) = per-tile counting sort + in-CTA segment sort,
+ * falling back to the global radix sort only when a tile's list is too long for one CTA;
+ * 1 = always the global radix sort (the reference's pipeline shape).  Both produce identical
+ * sorted lists; the switch exists so tests can cover the fallback. */
+void sl_set_binning_mode(int mode);
+
 /* Per-stage device timing with CUDA events recorded on the caller's stream
  * around each stage of sl_forward / sl_backward.  sl_profile_enable(1) resets
  * and starts accumulation, sl_profile_enable(0) stops it.  sl_profile_read

@@ -54,6 +54,7 @@ SIGNATURES = {
     "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),
     "sl_launch_count": (C.c_longlong, []),
+    "sl_set_binning_mode": (None, [C.c_int]),
     "sl_profile_enable": (None, [C.c_int]),
     "sl_profile_stage_count": (C.c_int, []),
     "sl_profile_stage_name": (C.c_char_p, [C.c_int]),

@@ -5,8 +5,9 @@
 //     Pairs are written at the Gaussian's prefix-sum offset in row-major tile
 //     order, so the emission order -- and with it the tie-break of the stable
 //     sort -- is the reference's.
-// K5  per-tile [first, last+1) ranges in the sorted list
-//     (reference: identifyTileRanges, rasterizer_impl.cu:137-159).
+// K5  per-tile [first, last+1) ranges in the sorted list (reference: identifyTileRanges,
+//     rasterizer_impl.cu:137-159), folded into the record gather below.
+// These two kernels serve the radix-sort fallback path; the default path is tile_binning.cu.
 #include "kernels.h"
 #include "blend_common.cuh"
 
@@ -42,24 +43,6 @@ emit_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __rest
             off++;
         }
     }
-}
-
-__global__ void __launch_bounds__(256)
-tile_ranges_kernel(int L, const uint64_t* __restrict__ keys, uint2* __restrict__ ranges)
-{
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= L) return;
-    const uint32_t cur = (uint32_t)(keys[idx] >> 32);
-    if (idx == 0) {
-        ranges[cur].x = 0;
-    } else {
-        const uint32_t prev = (uint32_t)(keys[idx - 1] >> 32);
-        if (cur != prev) {
-            ranges[prev].y = idx;
-            ranges[cur].x = idx;
-        }
-    }
-    if (idx == L - 1) ranges[cur].y = L;
 }
 
 // One thread per sorted pair: gather the Gaussian's screen-space data into a PairRecord, compute
@@ -125,73 +108,11 @@ int launch_build_records(int R, int C, const uint64_t* sorted_keys, const uint32
     return 0;
 }
 
-// Counting sort of the tiles by list length, longest first; one CTA, any number of tiles.
-__global__ void __launch_bounds__(1024)
-tile_order_kernel(const uint2* __restrict__ ranges, uint32_t* __restrict__ order, int n_tiles)
-{
-    constexpr int NB = 1024;
-    __shared__ uint32_t s_hist[NB];
-    __shared__ uint32_t s_warp[32];
-    __shared__ uint32_t s_max;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    s_hist[tid] = 0;
-    if (tid == 0) s_max = 0;
-    __syncthreads();
-    uint32_t mx = 0;
-    for (int t = tid; t < n_tiles; t += NB) mx = max(mx, ranges[t].y - ranges[t].x);
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-    if (lane == 0) atomicMax(&s_max, mx);
-    __syncthreads();
-    const uint32_t width = s_max / NB + 1;             // bucket b holds lengths [b*width, (b+1)*width)
-    for (int t = tid; t < n_tiles; t += NB) {
-        const uint32_t len = ranges[t].y - ranges[t].x;
-        atomicAdd(&s_hist[NB - 1 - len / width], 1u);   // descending: longest lists in bucket 0
-    }
-    __syncthreads();
-    // exclusive scan of the 1024 bucket counts
-    const uint32_t c = s_hist[tid];
-    uint32_t incl = c;
-#pragma unroll
-    for (int o = 1; o < 32; o <<= 1) {
-        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-        if (lane >= o) incl += v;
-    }
-    if (lane == 31) s_warp[warp] = incl;
-    __syncthreads();
-    uint32_t off = 0;
-    for (int w = 0; w < warp; ++w) off += s_warp[w];
-    __syncthreads();
-    s_hist[tid] = off + incl - c;
-    __syncthreads();
-    for (int t = tid; t < n_tiles; t += NB) {
-        const uint32_t len = ranges[t].y - ranges[t].x;
-        order[atomicAdd(&s_hist[NB - 1 - len / width], 1u)] = t;
-    }
-}
-
-int launch_tile_order(const uint2* ranges, uint32_t* order, int n_tiles, cudaStream_t stream)
-{
-    tile_order_kernel<<<1, 1024, 0, stream>>>(ranges, order, n_tiles);
-    count_launch();
-    return 0;
-}
-
 int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
                       int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream)
 {
     emit_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
                                                             tile_mask, grid_x, grid_y, keys, vals); count_launch();
-    return 0;
-}
-
-int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_tiles, cudaStream_t stream)
-{
-    SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream), "ranges memset");
-    if (R > 0) {
-        tile_ranges_kernel<<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, ranges);
-        count_launch();
-    }
     return 0;
 }
 

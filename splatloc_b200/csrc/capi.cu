@@ -50,7 +50,7 @@ enum Stage {
     ST_COUNT
 };
 static const char* const kStageNames[ST_COUNT] = {
-    "preprocess", "scan", "emit_pairs", "sort_pairs", "pair_records", "blend_forward", "blend_backward",
+    "preprocess", "tile_scan", "emit_pairs", "sort_pairs", "pair_records", "blend_forward", "blend_backward",
     "preprocess_backward"};
 
 struct Profiler {
@@ -63,6 +63,7 @@ struct Profiler {
 };
 static Profiler g_prof;
 static std::atomic<long long> g_launches{0};
+static std::atomic<int> g_force_radix{0};   // sl_set_binning_mode(): 1 = always take the radix-sort path
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -142,6 +143,8 @@ void sl_profile_enable(int on)
         g_prof.recorded[i] = false;
     }
 }
+
+void sl_set_binning_mode(int mode) { g_force_radix.store(mode == 1 ? 1 : 0, std::memory_order_relaxed); }
 
 int sl_profile_stage_count(void) { return ST_COUNT; }
 
@@ -236,47 +239,71 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     if (!img_chunk) { set_error("sl_forward: image allocation failed"); return SL_ERR_ALLOC; }
     ImageState img = ImageState::from_chunk(img_chunk, N, n_tiles);
 
+    // Per-tile pair counters (one 128-byte line each), filled by preprocess.
+    SL_CUDA(cudaMemsetAsync(img.tile_counts, 0, (size_t)n_tiles * TILE_COUNTER_STRIDE * sizeof(uint32_t), stream),
+            "tile counter memset");
     int rc;
     {
         StageTimer t(ST_PREPROCESS, stream);
         rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
                                colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered != 0, radii,
-                               geom, stream);
+                               geom, img.tile_counts, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess");
 
     {
         StageTimer t(ST_SCAN, stream);
-        rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_desc, geom.counters, stream);
+        rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles, stream);
     }
     if (rc) return rc;
-    SL_STAGE(dbg, stream, "prefix sum");
+    SL_STAGE(dbg, stream, "tile scan");
 
     // The binning chunk is sized by R, which only the device knows: one blocking read.
-    uint32_t num_rendered = 0;
-    SL_CUDA(cudaMemcpyAsync(&num_rendered, geom.point_offsets + P - 1, sizeof(uint32_t),
-                            cudaMemcpyDeviceToHost, stream), "read R");
+    BinInfo info;
+    SL_CUDA(cudaMemcpyAsync(&info, img.bin_info, sizeof(BinInfo), cudaMemcpyDeviceToHost, stream), "read R");
     SL_CUDA(cudaStreamSynchronize(stream), "read R");
-    if (num_rendered >= (1u << 30)) {
-        set_error("sl_forward: %u (tile, Gaussian) pairs exceed the 2^30 limit", num_rendered);
+    if (info.num_pairs >= (1u << 30)) {
+        set_error("sl_forward: %u (tile, Gaussian) pairs exceed the 2^30 limit", info.num_pairs);
         return SL_ERR_CAPACITY;
     }
-    const int R = (int)num_rendered;
+    const int R = (int)info.num_pairs;
 
     char* bin_chunk = binning_alloc(binning_ctx, sl_binning_bytes(R));
     if (!bin_chunk) { set_error("sl_forward: binning allocation failed"); return SL_ERR_ALLOC; }
     BinningState bin = BinningState::from_chunk(bin_chunk, R);
+    const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
 
-    if (R > 0) {
+    // Default: tile-bucketed binning (tile_binning.cu).  Fallback when a tile's list exceeds what one
+    // CTA sorts in shared memory (or on request, for tests): the reference's own pipeline shape --
+    // prefix sum, Gaussian-major emit, global radix sort -- which produces the same sorted arrays.
+    const bool radix_path = info.n_huge > 0 || g_force_radix.load(std::memory_order_relaxed) != 0;
+    if (R > 0 && !radix_path) {
         {
             StageTimer t(ST_EMIT, stream);
-            rc = launch_emit_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, bin.point_list_keys_unsorted,
-                                   bin.point_list_unsorted, stream);
+            rc = launch_scatter_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges, img.tile_counts,
+                                      bin.point_list_keys_unsorted, bin.point_list_unsorted, stream);
+        }
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "scatter pairs");
+        {
+            StageTimer t(ST_SORT, stream);
+            rc = launch_tile_sort(C, info, img.ranges, img.tile_order, img.large_tiles, n_tiles, vp.grid_x, bin.point_list_keys_unsorted,
+                                  bin.point_list_unsorted, bin.point_list_keys, bin.point_list, geom, features,
+                                  bin.records, bin.masks, stream);
+        }
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "tile sort");
+    } else if (R > 0) {
+        {
+            StageTimer t(ST_EMIT, stream);
+            rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_desc, geom.counters, stream);
+            if (rc == 0)
+                rc = launch_emit_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, bin.point_list_keys_unsorted,
+                                       bin.point_list_unsorted, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "emit pairs");
-
         {
             StageTimer t(ST_SORT, stream);
             rc = launch_sort_pairs(bin.point_list_keys_unsorted, bin.point_list_unsorted, bin.point_list_keys,
@@ -284,17 +311,14 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "sort");
+        {
+            StageTimer t(ST_RANGES, stream);
+            rc = launch_build_records(R, C, bin.point_list_keys, bin.point_list, geom, features, vp.grid_x, n_tiles,
+                                      bin.records, bin.masks, img.ranges, stream);
+        }
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "pair records");
     }
-
-    const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
-    {
-        StageTimer t(ST_RANGES, stream);
-        rc = launch_build_records(R, C, bin.point_list_keys, bin.point_list, geom, features, vp.grid_x, n_tiles,
-                                  bin.records, bin.masks, img.ranges, stream);
-        if (rc == 0) rc = launch_tile_order(img.ranges, img.tile_order, n_tiles, stream);
-    }
-    if (rc) return rc;
-    SL_STAGE(dbg, stream, "pair records");
 
     {
         StageTimer t(ST_BLEND_FWD, stream);

@@ -20,7 +20,7 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
                       const float* viewmatrix, const float* projmatrix, const float* cam_pos,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      cudaStream_t stream);
+                      uint32_t* tile_counts, cudaStream_t stream);
 
 // K10: frustum visibility (reference: checkFrustum, rasterizer_impl.cu:54-66).
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -34,17 +34,26 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned lon
 int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
                       int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
 
+// ---- tile-bucketed binning (the default path; no counterpart in the reference, which sorts all
+// pairs globally): per-tile counts come out of preprocess, one CTA turns them into ranges, launch
+// order and the totals the host reads back; pairs are scattered straight into their tile's segment
+// and each segment is sorted on (depth bits, Gaussian id) in shared memory by one CTA, which also
+// writes the PairRecords and masks.  The result equals the stable global sort on (tile | depth).
+int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
+                     int n_tiles, cudaStream_t stream);
+int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask, int grid_x,
+                         int grid_y, const uint2* ranges, uint32_t* cursors, uint64_t* keys, uint32_t* vals,
+                         cudaStream_t stream);
+int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
+                     const uint32_t* large_tiles, int n_tiles,
+                     int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                     uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
+                     uint8_t* masks, cudaStream_t stream);
+
 // K4: stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit);
 // result in (keys_out, vals_out); the inputs are preserved.
 int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                       uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream);
-
-// K5: per-tile [first, last+1) ranges (reference: identifyTileRanges, rasterizer_impl.cu:137-159).
-int launch_tile_ranges(int R, const uint64_t* sorted_keys, uint2* ranges, int n_tiles, cudaStream_t stream);
-
-// Tile ids ordered by decreasing list length: CTAs are dispatched in blockIdx order, so the
-// longest tiles start first and the short ones fill the tail (no reference counterpart).
-int launch_tile_order(const uint2* ranges, uint32_t* order, int n_tiles, cudaStream_t stream);
 
 // Gather, once per frame, everything the blend kernels read for each sorted pair (PairRecord) plus
 // the per-patch reach mask, and write the per-tile ranges (reference: identifyTileRanges).

@@ -97,7 +97,8 @@ preprocess_kernel(int P, int D, int M, int C,
                   float* __restrict__ rgb,
                   uint8_t* __restrict__ clamped,
                   float4* __restrict__ conic_opacity,
-                  uint32_t* __restrict__ tiles_touched)
+                  uint32_t* __restrict__ tiles_touched,
+                  uint32_t* __restrict__ tile_counts)
 {
     int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P) return;
@@ -160,6 +161,15 @@ preprocess_kernel(int P, int D, int M, int C,
     }
     tiles_touched[idx] = touched;
 
+    // Per-tile pair counts for the tile-bucketed binning (one counter per 128-byte line).
+    if (tile_counts != nullptr) {
+        for (uint32_t y = rmin.y; y < rmax.y; y++)
+            for (uint32_t x = rmin.x; x < rmax.x; x++) {
+                const uint32_t t = y * vp.grid_x + x;
+                if (tile_mask == nullptr || tile_mask[t]) atomicAdd(&tile_counts[(size_t)t * TILE_COUNTER_STRIDE], 1u);
+            }
+    }
+
     conic_opacity[idx] = {conic.x, conic.y, conic.z, opacities[idx]};
 
     if (colors_precomp == nullptr) {
@@ -190,12 +200,12 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
                       const float* viewmatrix, const float* projmatrix, const float* cam_pos,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      cudaStream_t stream)
+                      uint32_t* tile_counts, cudaStream_t stream)
 {
     preprocess_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
         P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
         colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, g.means2D, g.depths,
-        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched); count_launch();
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts); count_launch();
     return 0;
 }
 

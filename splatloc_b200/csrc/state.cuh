@@ -18,6 +18,17 @@ constexpr int SORT_ITEMS_PER_BLOCK = 4096;   // 256 threads x 16 keys
 constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 8;
+constexpr int TILE_COUNTER_STRIDE = 32;      // u32 words between per-tile counters: one 128-byte line each
+constexpr int TILE_SORT_SMALL = 2048;        // pairs a 256-thread CTA sorts in 16 KB of shared memory
+constexpr int TILE_SORT_LARGE = 16384;       // pairs a 1024-thread CTA sorts in 128 KB of shared memory
+
+// What the host reads back after the per-tile scan (one 16-byte copy).
+struct BinInfo {
+    uint32_t num_pairs;      // R
+    uint32_t n_large;        // tiles with more than TILE_SORT_SMALL pairs
+    uint32_t n_huge;         // tiles with more than TILE_SORT_LARGE pairs (-> radix-sort fallback)
+    uint32_t max_pairs;      // longest tile list
+};
 
 template <typename T>
 __host__ __device__ inline void carve(char*& chunk, T*& ptr, size_t count, size_t alignment = 128)
@@ -67,6 +78,9 @@ struct ImageState {
     uint2* ranges;        // [Tn] [first, last+1) in the sorted pair list
     // --- own scratch ---
     uint32_t* tile_order; // [Tn] tile ids, longest list first (launch order of the blend CTAs)
+    uint32_t* large_tiles;// [Tn] ids of the tiles whose list needs the large segment sort
+    uint32_t* tile_counts;// [Tn * TILE_COUNTER_STRIDE] per-tile pair counters, then scatter cursors
+    BinInfo* bin_info;    // [1]
 
     static ImageState from_chunk(char*& chunk, size_t N, size_t Tn)
     {
@@ -74,6 +88,9 @@ struct ImageState {
         carve(chunk, s.n_contrib, N);
         carve(chunk, s.ranges, Tn);
         carve(chunk, s.tile_order, Tn);
+        carve(chunk, s.large_tiles, Tn);
+        carve(chunk, s.tile_counts, Tn * TILE_COUNTER_STRIDE);
+        carve(chunk, s.bin_info, 1);
         return s;
     }
 };

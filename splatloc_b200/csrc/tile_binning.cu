@@ -1,0 +1,289 @@
+// splatloc_b200/csrc/tile_binning.cu
+//
+// Tile-bucketed binning: the default replacement for the reference's
+//   prefix sum (rasterizer_impl.cu:518) -> duplicateWithKeys (:70-132) -> global 64-bit radix
+//   sort (:546-551) -> identifyTileRanges (:137-159)
+// chain.  The reference sorts all R pairs globally on (tile << 32 | depth bits), ~6 digit passes
+// over 24 B per pair.  But the tile of every pair is known when it is emitted, so:
+//   1. preprocess counts the pairs of every tile (preprocess.cu),
+//   2. tile_scan_kernel (one CTA) turns the counts into the per-tile ranges, the CTA launch order
+//      (longest list first), and the totals the host needs,
+//   3. scatter_pairs_kernel writes each pair straight into its tile's segment,
+//   4. tile_sort_kernel sorts every segment in shared memory (bitonic network on the 64-bit
+//      composite depth bits << 32 | Gaussian id) and, in the same pass, writes the sorted keys and
+//      ids and gathers the PairRecords / reach masks the blend kernels stream.
+// Pairs move twice instead of seven times and the sort is done by Tn independent CTAs.
+// The output is the same total order (tile, depth bits, Gaussian id) the reference's stable sort
+// produces -- its emission order within equal keys is ascending Gaussian id -- so point_list,
+// sorted keys and ranges are bit-identical.  Segments longer than TILE_SORT_LARGE fall back to the
+// global radix sort (capi.cu), which yields the same arrays.
+#include "kernels.h"
+#include "blend_common.cuh"
+
+namespace sl {
+
+// ------------------------------------------------------------------ 2. per-tile scan (one CTA)
+__global__ void __launch_bounds__(1024)
+tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
+                 uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles)
+{
+    constexpr int NT = 1024;
+    __shared__ uint32_t s_warp[32];
+    __shared__ uint32_t s_hist[NT];
+    __shared__ uint32_t s_carry, s_max, s_large, s_huge;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (tid == 0) { s_carry = 0; s_max = 0; s_large = 0; s_huge = 0; }
+    s_hist[tid] = 0;
+    __syncthreads();
+
+    // exclusive scan over the tiles, 1024 at a time; counters become the scatter cursors (zeroed)
+    uint32_t mx = 0, n_huge = 0;
+    for (int base = 0; base < n_tiles; base += NT) {
+        const int t = base + tid;
+        const uint32_t c = (t < n_tiles) ? tile_counts[(size_t)t * TILE_COUNTER_STRIDE] : 0u;
+        uint32_t incl = c;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+            const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+            if (lane >= o) incl += v;
+        }
+        if (lane == 31) s_warp[warp] = incl;
+        __syncthreads();
+        uint32_t off = s_carry;
+        for (int w = 0; w < warp; ++w) off += s_warp[w];
+        const uint32_t start = off + incl - c;
+        if (t < n_tiles) {
+            ranges[t] = c ? make_uint2(start, start + c) : make_uint2(0u, 0u);   // empty tiles stay (0, 0)
+            tile_counts[(size_t)t * TILE_COUNTER_STRIDE] = 0u;
+        }
+        mx = max(mx, c);
+        if (c > (uint32_t)TILE_SORT_SMALL) large_tiles[atomicAdd(&s_large, 1u)] = t;   // segment-sort work list
+        n_huge += c > (uint32_t)TILE_SORT_LARGE;
+        __syncthreads();
+        if (tid == NT - 1) s_carry = off + incl;
+        __syncthreads();
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        mx = max(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+        n_huge += __shfl_xor_sync(0xffffffffu, n_huge, o);
+    }
+    if (lane == 0) {
+        atomicMax(&s_max, mx);
+        atomicAdd(&s_huge, n_huge);
+    }
+    __syncthreads();
+    if (tid == 0) {
+        info->num_pairs = s_carry;
+        info->n_large = s_large;
+        info->n_huge = s_huge;
+        info->max_pairs = s_max;
+    }
+
+    // launch order: counting sort of the tiles by list length, longest first
+    const uint32_t width = s_max / NT + 1;
+    for (int t = tid; t < n_tiles; t += NT) {
+        const uint32_t len = ranges[t].y - ranges[t].x;
+        atomicAdd(&s_hist[NT - 1 - len / width], 1u);
+    }
+    __syncthreads();
+    const uint32_t c = s_hist[tid];
+    uint32_t incl = c;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+        const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+        if (lane >= o) incl += v;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    uint32_t off = 0;
+    for (int w = 0; w < warp; ++w) off += s_warp[w];
+    __syncthreads();
+    s_hist[tid] = off + incl - c;
+    __syncthreads();
+    for (int t = tid; t < n_tiles; t += NT) {
+        const uint32_t len = ranges[t].y - ranges[t].x;
+        order[atomicAdd(&s_hist[NT - 1 - len / width], 1u)] = t;
+    }
+}
+
+// ------------------------------------------------------------------ 3. scatter pairs into tile segments
+// A Gaussian that covers a handful of tiles is emitted by its own thread; one that covers many
+// (a near or very flat splat can cover thousands) is emitted by its whole warp, tile k to lane
+// k mod 32, so that no single thread serialises thousands of returning atomics.
+__global__ void __launch_bounds__(256)
+scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
+                     const uint32_t* __restrict__ tiles_touched, const int* __restrict__ radii,
+                     const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y,
+                     const uint2* __restrict__ ranges, uint32_t* cursors,
+                     uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+{
+    constexpr uint32_t SOLO_MAX = 8;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
+    uint32_t depth_bits = 0, area = 0;
+    if (idx < P) {
+        const int r = radii[idx];
+        if (r > 0 && tiles_touched[idx] != 0) {
+            const float2 xy = means2D[idx];
+            tile_rect(xy.x, xy.y, r, grid_x, grid_y, rmin, rmax);
+            depth_bits = __float_as_uint(depths[idx]);
+            area = (rmax.x - rmin.x) * (rmax.y - rmin.y);
+        }
+    }
+    auto emit = [&](uint32_t t, uint32_t dbits, uint32_t id) {
+        if (tile_mask != nullptr && !tile_mask[t]) return;
+        const uint32_t slot = ranges[t].x + atomicAdd(&cursors[(size_t)t * TILE_COUNTER_STRIDE], 1u);
+        keys[slot] = ((uint64_t)t << 32) | dbits;
+        vals[slot] = id;
+    };
+    if (area > 0 && area <= SOLO_MAX) {
+        for (uint32_t y = rmin.y; y < rmax.y; y++)
+            for (uint32_t x = rmin.x; x < rmax.x; x++) emit(y * grid_x + x, depth_bits, (uint32_t)idx);
+    }
+    unsigned big = __ballot_sync(0xffffffffu, area > SOLO_MAX);
+    while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, src), y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+        const uint32_t w = __shfl_sync(0xffffffffu, rmax.x, src) - x0;
+        const uint32_t n = __shfl_sync(0xffffffffu, area, src);
+        const uint32_t dbits = __shfl_sync(0xffffffffu, depth_bits, src);
+        const uint32_t id = (uint32_t)(idx - lane + src);
+        for (uint32_t k = lane; k < n; k += 32) emit((y0 + k / w) * grid_x + x0 + k % w, dbits, id);
+    }
+}
+
+// ------------------------------------------------------------------ 4. per-tile sort + record gather
+// One CTA per tile, tiles taken from `order` starting at `first`.  Sorts the tile's segment on the
+// composite (depth bits << 32 | id) with a bitonic network in shared memory, then writes the sorted
+// ids / keys and gathers the PairRecords and reach masks.  `max_len`: segments longer than this are
+// left to another launch.
+template <int C, int THREADS>
+__global__ void __launch_bounds__(THREADS)
+tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int first, int grid_x,
+                 uint32_t min_len, uint32_t max_len,
+                 const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                 uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
+                 const float2* __restrict__ means2D, const float* __restrict__ depths,
+                 const float4* __restrict__ conic_opacity, const float* __restrict__ features,
+                 PairRecord* __restrict__ records, uint8_t* __restrict__ masks)
+{
+    extern __shared__ __align__(16) unsigned long long s_key[];
+    const int tid = threadIdx.x;
+    const uint32_t tile = order[first + blockIdx.x];
+    const uint2 range = ranges[tile];
+    const uint32_t n = range.y - range.x;
+    if (n <= min_len || n > max_len) return;
+
+    uint32_t n_pad = 32;
+    while (n_pad < n) n_pad <<= 1;
+    for (uint32_t i = tid; i < n_pad; i += THREADS) {
+        unsigned long long k = ~0ull;
+        if (i < n) k = (keys_in[range.x + i] << 32) | (unsigned long long)vals_in[range.x + i];
+        s_key[i] = k;
+    }
+    __syncthreads();
+
+    for (uint32_t k = 2; k <= n_pad; k <<= 1) {
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t i = tid; i < (n_pad >> 1); i += THREADS) {
+                const uint32_t a = ((i & ~(j - 1)) << 1) | (i & (j - 1));
+                const uint32_t b = a | j;
+                const unsigned long long x = s_key[a], y = s_key[b];
+                const bool up = (a & k) == 0;
+                if ((x > y) == up) {
+                    s_key[a] = y;
+                    s_key[b] = x;
+                }
+            }
+            __syncthreads();
+        }
+    }
+
+    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+    for (uint32_t i = tid; i < n; i += THREADS) {
+        const unsigned long long k = s_key[i];
+        const uint32_t id = (uint32_t)k;
+        const uint32_t slot = range.x + i;
+        point_list[slot] = id;
+        keys_out[slot] = ((unsigned long long)tile << 32) | (k >> 32);
+        const float2 xy = means2D[id];
+        const float4 co = conic_opacity[id];
+        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (C == 4) {
+            f = reinterpret_cast<const float4*>(features)[id];
+        } else {
+            f.x = features[id * C + 0];
+            if (C > 1) f.y = features[id * C + 1];
+            if (C > 2) f.z = features[id * C + 2];
+        }
+        PairRecord rec;
+        rec.xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float((int)id));
+        rec.co = co;
+        rec.col = f;
+        records[slot] = rec;
+        masks[slot] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
+    }
+}
+
+int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
+                     int n_tiles, cudaStream_t stream)
+{
+    tile_scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles);
+    count_launch();
+    return 0;
+}
+
+int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask, int grid_x,
+                         int grid_y, const uint2* ranges, uint32_t* cursors, uint64_t* keys, uint32_t* vals,
+                         cudaStream_t stream)
+{
+    scatter_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.tiles_touched, radii,
+                                                               tile_mask, grid_x, grid_y, ranges, cursors, keys, vals);
+    count_launch();
+    return 0;
+}
+
+template <int C>
+static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
+                              const uint32_t* large_tiles, int n_tiles,
+                              int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                              uint32_t* point_list, const GeomState& g, const float* features,
+                              PairRecord* records, uint8_t* masks, cudaStream_t stream)
+{
+    // Long segments (work list written by tile_scan_kernel) get a 1024-thread CTA with 128 KB of
+    // shared memory each; the 256-thread launch covers all tiles and skips those.
+    if (info.n_large > 0) {
+        constexpr int T = 1024;
+        const size_t smem = (size_t)TILE_SORT_LARGE * sizeof(unsigned long long);
+        SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+                "tile sort smem attribute");
+        tile_sort_kernel<C, T><<<(int)info.n_large, T, smem, stream>>>(
+            ranges, large_tiles, 0, grid_x, (uint32_t)TILE_SORT_SMALL, (uint32_t)TILE_SORT_LARGE, keys_in, vals_in,
+            keys_out, point_list, g.means2D, g.depths, g.conic_opacity, features, records, masks);
+        count_launch();
+    }
+    constexpr int T = 256;
+    tile_sort_kernel<C, T><<<n_tiles, T, (size_t)TILE_SORT_SMALL * sizeof(unsigned long long), stream>>>(
+        ranges, tile_order, 0, grid_x, 0u, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list,
+        g.means2D, g.depths, g.conic_opacity, features, records, masks);
+    count_launch();
+    return 0;
+}
+
+int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
+                     const uint32_t* large_tiles, int n_tiles,
+                     int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                     uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
+                     uint8_t* masks, cudaStream_t stream)
+{
+    if (C == 4)
+        return tile_sort_launches<4>(info, ranges, tile_order, large_tiles, n_tiles, grid_x, keys_in, vals_in, keys_out, point_list,
+                                     g, features, records, masks, stream);
+    return tile_sort_launches<3>(info, ranges, tile_order, large_tiles, n_tiles, grid_x, keys_in, vals_in, keys_out, point_list, g,
+                                 features, records, masks, stream);
+}
+
+}  // namespace sl

@@ -63,7 +63,7 @@ def run_backend(be, d, debug=False, backward=True):
         g = interpret_geomBuffer(geom, P)
         vis = radii > 0
         out["tiles_touched"] = g["tiles_touched"]
-        out["point_offsets"] = g["point_offsets"]
+        out["point_offsets"] = g["point_offsets"]   # (only filled by the radix-sort path; not in INT_KEYS)
         # per-Gaussian intermediates are only defined where the Gaussian survived preprocess
         out["depths_vis"] = g["depths"][vis].view(torch.int32)
         out["means2D_vis"] = g["means2D"][vis].view(torch.int32)
@@ -79,8 +79,14 @@ def run_backend(be, d, debug=False, backward=True):
         out["ranges"] = im["ranges"]
         if R > 0:
             b = interpret_binningBuffer(binning, R)
-            out["keys_unsorted"] = b["point_list_keys_unsorted"]
-            out["vals_unsorted"] = b["point_list_unsorted"]
+            # The emitted (key, id) pairs as a multiset: their order in the unsorted arrays is an
+            # implementation detail (Gaussian-major in the reference, tile-bucketed here by default).
+            ku, vu = b["point_list_keys_unsorted"].clone(), b["point_list_unsorted"].clone().long()
+            o = torch.argsort(vu, stable=True)
+            ku, vu = ku[o], vu[o]
+            o = torch.argsort(ku, stable=True)
+            out["emitted_keys"] = ku[o]
+            out["emitted_vals"] = vu[o].int()
             out["keys_sorted"] = b["point_list_keys"]
             out["point_list"] = b["point_list"]
     if backward:
@@ -95,8 +101,8 @@ def run_backend(be, d, debug=False, backward=True):
     return {k: (v.detach().cpu().clone() if isinstance(v, torch.Tensor) else v) for k, v in out.items()}
 
 
-INT_KEYS = ("radii", "tiles_touched", "point_offsets", "depths_vis", "means2D_vis", "n_contrib", "ranges",
-            "keys_unsorted", "vals_unsorted", "keys_sorted", "point_list", "clamped_vis")
+INT_KEYS = ("radii", "tiles_touched", "depths_vis", "means2D_vis", "n_contrib", "ranges",
+            "emitted_keys", "emitted_vals", "keys_sorted", "point_list", "clamped_vis")
 FLOAT_KEYS = ("color", "depth", "alpha", "conic_opacity_vis", "cov3D_vis", "rgb_vis")
 GRAD_KEYS = ("g_abs2D", "g_means2D", "g_colors", "g_opacity", "g_means3D", "g_cov3D", "g_sh", "g_scales", "g_rot")
 
@@ -143,3 +149,15 @@ def compare(a, b, rtol=RTOL, atol=ATOL, grad_scale_aware=True):
                 bad.append(f"{k}: {nbad}/{y.numel()} outside tol, max err {float(err.max()):.3e}, "
                            f"max ref {float(y.abs().max()):.3e}")
     return bad
+
+
+def golden_reference(g):
+    """tests/golden/*.npz -> the dict layout of run_backend() (reference side)."""
+    b = {k[4:]: (torch.from_numpy(v) if v.ndim else int(v)) for k, v in g.items() if k.startswith("ref_")}
+    if "keys_unsorted" in b:
+        ku, vu = b["keys_unsorted"].clone(), b["vals_unsorted"].clone().long()
+        o = torch.argsort(vu, stable=True)
+        ku, vu = ku[o], vu[o]
+        o = torch.argsort(ku, stable=True)
+        b["emitted_keys"], b["emitted_vals"] = ku[o], vu[o].int()
+    return b

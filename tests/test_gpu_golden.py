@@ -29,7 +29,7 @@ def test_matches_committed_reference_outputs(name):
     from splatloc_b200 import _C
     g = load(name)
     a = H.run_backend(_C, _inputs(g))
-    b = {k[4:]: (torch.from_numpy(v) if v.ndim else int(v)) for k, v in g.items() if k.startswith("ref_")}
+    b = H.golden_reference(g)
     bad = H.compare(a, b)
     assert not bad, "\n".join(bad)
 

@@ -36,15 +36,47 @@ CASES = [
 ]
 
 
+@pytest.fixture(params=["tile_binning", "radix_fallback"])
+def binning_mode(request):
+    """Both binning strategies of sl_forward must give the reference's sorted lists."""
+    from splatloc_b200 import _capi
+    _capi.load().sl_set_binning_mode(1 if request.param == "radix_fallback" else 0)
+    yield request.param
+    _capi.load().sl_set_binning_mode(0)
+
+
 @pytest.mark.parametrize("case", CASES, ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items() if k != "bg"))
-def test_matches_reference_cuda(case):
+def test_matches_reference_cuda(case, binning_mode):
     ref, ours = _ref(), _ours()
     d = H.scene_inputs(**case)
     b = H.run_backend(ref, d)
     a = H.run_backend(ours, d)
     assert b["R"] > 0
     bad = H.compare(a, b)
+    if binning_mode == "radix_fallback" and not torch.equal(a["point_offsets"], b["point_offsets"]):
+        bad.append("point_offsets differ")      # only this path computes the per-Gaussian prefix sum
     assert not bad, "\n".join(bad)
+
+
+def test_long_tile_lists_take_the_large_and_fallback_sorts():
+    """Many Gaussians stacked on a few tiles: segments beyond 2048 pairs use the 1024-thread segment
+    sort, beyond 16384 the radix fallback; all must still match the reference bit for bit."""
+    ref, ours = _ref(), _ours()
+    for P, spread in ((40000, 0.25), (120000, 0.05)):
+        d = H.scene_inputs(P, 21, size=(128, 96))
+        cam = d["cam"]
+        fwd, right, down = cam.viewmatrix[:3, 2], cam.viewmatrix[:3, 0], cam.viewmatrix[:3, 1]
+        g = torch.Generator().manual_seed(P)
+        u = (spread * torch.randn((P, 2), generator=g)).cuda()
+        z = (2.0 + 2.0 * torch.rand((P, 1), generator=g)).cuda()
+        d["means3D"] = (cam.campos[None, :] + z * fwd[None, :] + u[:, :1] * right[None, :] + u[:, 1:] * down[None, :]).contiguous()
+        d["scales"] = (d["scales"] * 0.3).contiguous()
+        b = H.run_backend(ref, d)
+        a = H.run_backend(ours, d)
+        longest = int((b["ranges"][:, 1] - b["ranges"][:, 0]).max())
+        assert longest > (2048 if P == 40000 else 16384), longest
+        bad = H.compare(a, b)
+        assert not bad, f"longest list {longest}\n" + "\n".join(bad)
 
 
 def test_empty_and_invisible():
