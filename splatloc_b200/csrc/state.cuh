@@ -19,7 +19,7 @@ constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 8;
 constexpr int TILE_COUNTER_STRIDE = 32;      // u32 words between per-tile counters: one 128-byte line each
-constexpr int TILE_SORT_SMALL = 2048;        // pairs a 256-thread CTA sorts in 16 KB of shared memory
+constexpr int TILE_SORT_SMALL = 4096;        // pairs a 256-thread CTA sorts (16 keys per thread, 32 KB of smem)
 constexpr int TILE_SORT_LARGE = 16384;       // pairs a 1024-thread CTA sorts in 128 KB of shared memory
 
 // What the host reads back after the per-tile scan (one 16-byte copy).

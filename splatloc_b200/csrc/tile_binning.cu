@@ -156,14 +156,117 @@ scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __r
 }
 
 // ------------------------------------------------------------------ 4. per-tile sort + record gather
-// One CTA per tile, tiles taken from `order` starting at `first`.  Sorts the tile's segment on the
-// composite (depth bits << 32 | id) with a bitonic network in shared memory, then writes the sorted
-// ids / keys and gathers the PairRecords and reach masks.  `max_len`: segments longer than this are
-// left to another launch.
+// Bitonic network over N = E * THREADS keys held E per thread; key (warp w, slot r, lane l) is
+// element w * 32E + 32 r + l.  Compare-exchange distances below 32 are warp shuffles, distances
+// 32 .. 16E stay inside a thread's registers, and only the few distances that cross warps go
+// through shared memory (6 of the 55 steps at N = 1024) -- the rest of the network needs no barrier.
+template <int E, int THREADS>
+__device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], unsigned long long* smem, int tid)
+{
+    constexpr int N = E * THREADS;
+    const int lane = tid & 31;
+    const int wbase = (tid >> 5) * 32 * E + lane;
+#pragma unroll 1
+    for (int k = 2; k <= N; k <<= 1) {
+#pragma unroll 1
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            if (j >= 32 * E) {
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < E; ++r) smem[wbase + 32 * r] = key[r];
+                __syncthreads();
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const int g = wbase + 32 * r;
+                    const unsigned long long other = smem[g ^ j];
+                    const bool take_min = ((g & j) == 0) == ((g & k) == 0);
+                    key[r] = take_min ? min(key[r], other) : max(key[r], other);
+                }
+            } else if (j >= 32) {
+#pragma unroll
+                for (int dr = E / 2; dr >= 1; dr >>= 1) {
+                    if (j == 32 * dr) {
+#pragma unroll
+                        for (int r = 0; r < E; ++r) {
+                            if ((r & dr) == 0) {
+                                const bool up = ((wbase + 32 * r) & k) == 0;
+                                const unsigned long long x = key[r], y = key[r | dr];
+                                if ((x > y) == up) {
+                                    key[r] = y;
+                                    key[r | dr] = x;
+                                }
+                            }
+                        }
+                    }
+                }
+            } else {
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const unsigned long long other = __shfl_xor_sync(0xffffffffu, key[r], j);
+                    const bool take_min = ((lane & j) == 0) == (((wbase + 32 * r) & k) == 0);
+                    key[r] = take_min ? min(key[r], other) : max(key[r], other);
+                }
+            }
+        }
+    }
+}
+
+// Sort one tile's segment (n <= E * THREADS pairs) and write every per-pair output.
+template <int C, int E, int THREADS>
+__device__ __forceinline__ void sort_and_emit_tile(
+    uint32_t tile, uint2 range, int grid_x, unsigned long long* smem,
+    const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+    uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
+    const float2* __restrict__ means2D, const float* __restrict__ depths,
+    const float4* __restrict__ conic_opacity, const float* __restrict__ features,
+    PairRecord* __restrict__ records, uint8_t* __restrict__ masks)
+{
+    const int tid = threadIdx.x, lane = tid & 31;
+    const uint32_t n = range.y - range.x;
+    const uint32_t wbase = (uint32_t)(tid >> 5) * 32 * E + lane;
+    unsigned long long key[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint32_t g = wbase + 32 * r;
+        key[r] = (g < n) ? ((keys_in[range.x + g] << 32) | (unsigned long long)vals_in[range.x + g]) : ~0ull;
+    }
+    cta_bitonic_sort<E, THREADS>(key, smem, tid);
+
+    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const uint32_t g = wbase + 32 * r;
+        if (g < n) {
+            const unsigned long long k = key[r];
+            const uint32_t id = (uint32_t)k;
+            const uint32_t slot = range.x + g;
+            point_list[slot] = id;
+            keys_out[slot] = ((unsigned long long)tile << 32) | (k >> 32);
+            const float2 xy = means2D[id];
+            const float4 co = conic_opacity[id];
+            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (C == 4) {
+                f = reinterpret_cast<const float4*>(features)[id];
+            } else {
+                f.x = features[id * C + 0];
+                if (C > 1) f.y = features[id * C + 1];
+                if (C > 2) f.z = features[id * C + 2];
+            }
+            PairRecord rec;
+            rec.xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float((int)id));
+            rec.co = co;
+            rec.col = f;
+            records[slot] = rec;
+            masks[slot] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
+        }
+    }
+}
+
+// One CTA per tile of `tiles[blockIdx.x]`; handles segments with min_len < n <= 16 * THREADS and
+// picks the network size from n.
 template <int C, int THREADS>
 __global__ void __launch_bounds__(THREADS)
-tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ order, int first, int grid_x,
-                 uint32_t min_len, uint32_t max_len,
+tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tiles, int grid_x, uint32_t min_len,
                  const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
                  const float2* __restrict__ means2D, const float* __restrict__ depths,
@@ -171,61 +274,19 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  PairRecord* __restrict__ records, uint8_t* __restrict__ masks)
 {
     extern __shared__ __align__(16) unsigned long long s_key[];
-    const int tid = threadIdx.x;
-    const uint32_t tile = order[first + blockIdx.x];
+    const uint32_t tile = tiles[blockIdx.x];
     const uint2 range = ranges[tile];
     const uint32_t n = range.y - range.x;
-    if (n <= min_len || n > max_len) return;
-
-    uint32_t n_pad = 32;
-    while (n_pad < n) n_pad <<= 1;
-    for (uint32_t i = tid; i < n_pad; i += THREADS) {
-        unsigned long long k = ~0ull;
-        if (i < n) k = (keys_in[range.x + i] << 32) | (unsigned long long)vals_in[range.x + i];
-        s_key[i] = k;
-    }
-    __syncthreads();
-
-    for (uint32_t k = 2; k <= n_pad; k <<= 1) {
-        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-            for (uint32_t i = tid; i < (n_pad >> 1); i += THREADS) {
-                const uint32_t a = ((i & ~(j - 1)) << 1) | (i & (j - 1));
-                const uint32_t b = a | j;
-                const unsigned long long x = s_key[a], y = s_key[b];
-                const bool up = (a & k) == 0;
-                if ((x > y) == up) {
-                    s_key[a] = y;
-                    s_key[b] = x;
-                }
-            }
-            __syncthreads();
-        }
-    }
-
-    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
-    for (uint32_t i = tid; i < n; i += THREADS) {
-        const unsigned long long k = s_key[i];
-        const uint32_t id = (uint32_t)k;
-        const uint32_t slot = range.x + i;
-        point_list[slot] = id;
-        keys_out[slot] = ((unsigned long long)tile << 32) | (k >> 32);
-        const float2 xy = means2D[id];
-        const float4 co = conic_opacity[id];
-        float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (C == 4) {
-            f = reinterpret_cast<const float4*>(features)[id];
-        } else {
-            f.x = features[id * C + 0];
-            if (C > 1) f.y = features[id * C + 1];
-            if (C > 2) f.z = features[id * C + 2];
-        }
-        PairRecord rec;
-        rec.xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float((int)id));
-        rec.co = co;
-        rec.col = f;
-        records[slot] = rec;
-        masks[slot] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
-    }
+    if (n <= min_len || n > 16u * THREADS) return;
+#define SL_SORT_CASE(EE)                                                                                         \
+    sort_and_emit_tile<C, EE, THREADS>(tile, range, grid_x, s_key, keys_in, vals_in, keys_out, point_list, means2D, \
+                                       depths, conic_opacity, features, records, masks)
+    if (n <= 1u * THREADS) SL_SORT_CASE(1);
+    else if (n <= 2u * THREADS) SL_SORT_CASE(2);
+    else if (n <= 4u * THREADS) SL_SORT_CASE(4);
+    else if (n <= 8u * THREADS) SL_SORT_CASE(8);
+    else SL_SORT_CASE(16);
+#undef SL_SORT_CASE
 }
 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
@@ -261,14 +322,18 @@ static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const ui
         SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 "tile sort smem attribute");
         tile_sort_kernel<C, T><<<(int)info.n_large, T, smem, stream>>>(
-            ranges, large_tiles, 0, grid_x, (uint32_t)TILE_SORT_SMALL, (uint32_t)TILE_SORT_LARGE, keys_in, vals_in,
-            keys_out, point_list, g.means2D, g.depths, g.conic_opacity, features, records, masks);
+            ranges, large_tiles, grid_x, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list, g.means2D,
+            g.depths, g.conic_opacity, features, records, masks);
         count_launch();
     }
     constexpr int T = 256;
-    tile_sort_kernel<C, T><<<n_tiles, T, (size_t)TILE_SORT_SMALL * sizeof(unsigned long long), stream>>>(
-        ranges, tile_order, 0, grid_x, 0u, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list,
-        g.means2D, g.depths, g.conic_opacity, features, records, masks);
+    // shared memory is only touched by the cross-warp steps: size it for the longest short segment
+    const uint32_t longest = info.max_pairs < (uint32_t)TILE_SORT_SMALL ? info.max_pairs : (uint32_t)TILE_SORT_SMALL;
+    uint32_t pad = T;
+    while (pad < longest) pad <<= 1;
+    tile_sort_kernel<C, T><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
+        ranges, tile_order, grid_x, 0u, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
+        features, records, masks);
     count_launch();
     return 0;
 }
