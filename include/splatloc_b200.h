@@ -126,6 +126,21 @@ size_t sl_knn_scratch_bytes(int P);
 int sl_knn(int P, const float* points, float* mean_dists,
            char* scratch, size_t scratch_bytes, void* stream);
 
+/* distCUDA2 without any allocation (no counterpart in the reference, whose SimpleKNN::knn
+ * allocates with cudaMalloc and thrust on every call).  Same result as sl_knn, but the scratch is
+ * a fixed 3.5 MiB array inside the library's device image, so a caller that must not allocate --
+ * a real-time keyframe hook that cannot afford an allocation's device-wide synchronisation, a
+ * plugin in a process whose device memory is owned by another allocator -- passes only the input
+ * and the output.  Limits and rules:
+ *   - at most SL_KNN_STATIC_MAX_POINTS = 65536 points; more returns SL_ERR_CAPACITY (use sl_knn);
+ *   - the array occupies 3.5 MiB on every GPU that loads the library until the process exits;
+ *   - the first call on each device resolves the array's device address once and caches it:
+ *     make that first call before any stream capture starts;
+ *   - every call on a device uses the same array (each call re-zeroes what it needs): calls whose
+ *     GPU work may overlap -- other streams, other threads -- race; serialise them. */
+#define SL_KNN_STATIC_MAX_POINTS 65536
+int sl_knn_static(int P, const float* points, float* mean_dists, void* stream);
+
 /* ---- instrumentation (no counterpart in the reference, which has no tracing,
  * SURVEY.md section 5) ------------------------------------------------------ */
 

@@ -53,6 +53,7 @@ SIGNATURES = {
     "sl_mark_visible": (C.c_int, [C.c_int, _F, _F, _F, _F, C.c_void_p]),
     "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),
+    "sl_knn_static": (C.c_int, [C.c_int, _F, _F, C.c_void_p]),
     "sl_launch_count": (C.c_longlong, []),
     "sl_set_binning_mode": (None, [C.c_int]),
     "sl_profile_enable": (None, [C.c_int]),

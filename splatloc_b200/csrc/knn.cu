@@ -19,6 +19,7 @@
 // array and widens the block shell by shell until the third-best distance is
 // provably inside the searched block.
 #include <cfloat>
+#include <mutex>
 #include "kernels.h"
 
 namespace sl {
@@ -268,3 +269,76 @@ int launch_knn(int P, const float* points, float* mean_dists, char* scratch, cud
 }
 
 }  // namespace sl
+
+namespace sl {
+
+// ---------------------------------------------------------------------------------------------
+// sl_knn_static: distCUDA2 for callers that must not allocate.
+//
+// Who needs it.  sl_knn asks its caller for a scratch buffer, and a caller normally gets one
+// from cudaMalloc or from torch's allocator.  Some callers cannot: a keyframe-insertion hook
+// running inside a real-time tracking loop, where an allocation may synchronise the whole device
+// and blow the frame budget; a plugin loaded into a process whose device memory is entirely owned
+// by another allocator, where a fresh cudaMalloc can simply fail; code running while device-wide
+// synchronisation is forbidden.  For them this entry point carries its own scratch: a fixed array
+// in device memory that belongs to the library image.
+//
+// What it costs.  The array exists on every GPU that loads the library, from load to process
+// exit, whether or not this function is ever called: 3.5 MiB (kKnnStaticScratchBytes), sized
+// for at most 65536 points (kKnnStaticMaxPoints; SL_KNN_STATIC_MAX_POINTS in the header) -- ample for SplatLoc, which runs distCUDA2
+// on the few thousand points a keyframe adds (gaussian_model.py:178-207).  Larger inputs are
+// refused with SL_ERR_CAPACITY; use sl_knn for those.
+//
+// Rules.  * The first call on each device looks the array's device address up once
+//           (cudaGetSymbolAddress, with that device current) and caches it; make that first call
+//           before any stream capture begins.
+//         * All calls on a device share the one array.  Each call re-initialises the parts that
+//           must start from zero (cell counters, scan descriptors, ticket, bounding box), so
+//           back-to-back calls on one stream are fine, but two calls whose GPU work can overlap
+//           (different streams, different host threads) race on it and give garbage.
+//         * No cudaMalloc / cudaFree / allocating library call is made, on any call.
+constexpr int kKnnStaticMaxPoints = 65536;
+constexpr size_t kKnnStaticScratchBytes = 3670016;   // 3.5 MiB >= knn_scratch_bytes(65536) = 3408928
+
+static __device__ __align__(256) unsigned char g_knn_static_scratch[kKnnStaticScratchBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_knn_static_mutex;
+char* g_knn_static_ptr[kMaxDevices] = {};   // device address of g_knn_static_scratch, per device
+}  // namespace
+
+}  // namespace sl
+
+extern "C" int sl_knn_static(int P, const float* points, float* mean_dists, void* stream_)
+{
+    using namespace sl;
+    set_error("%s", "");
+    if (P < 0) { set_error("sl_knn_static: P < 0"); return -2; }
+    if (P == 0) return 0;
+    if (!points || !mean_dists) { set_error("sl_knn_static: a required pointer is NULL"); return -2; }
+    if (P > kKnnStaticMaxPoints || knn_scratch_bytes(P) > kKnnStaticScratchBytes) {
+        set_error("sl_knn_static: %d points exceed the built-in scratch (at most %d points, %zu bytes); "
+                  "use sl_knn with caller-provided scratch", P, kKnnStaticMaxPoints, kKnnStaticScratchBytes);
+        return -3;
+    }
+    int dev = -1;
+    SL_CUDA(cudaGetDevice(&dev), "sl_knn_static: cudaGetDevice");
+    if (dev < 0 || dev >= kMaxDevices) { set_error("sl_knn_static: device index %d out of range", dev); return -2; }
+    char* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(g_knn_static_mutex);
+        if (g_knn_static_ptr[dev] == nullptr) {
+            // In host code the array's name is only a handle for the runtime, not a device address.
+            void* p = nullptr;
+            SL_CUDA(cudaGetSymbolAddress(&p, g_knn_static_scratch), "sl_knn_static: cudaGetSymbolAddress");
+            g_knn_static_ptr[dev] = static_cast<char*>(p);
+        }
+        scratch = g_knn_static_ptr[dev];
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    int rc = launch_knn(P, points, mean_dists, scratch, stream);
+    if (rc) return rc;
+    return check_cuda(cudaGetLastError(), "sl_knn_static");
+}
+
