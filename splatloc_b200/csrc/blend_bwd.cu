@@ -134,7 +134,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     //   0..C-1 colour | C depth | C+1,C+2 mean2D x,y | C+3,C+4 |mean2D| x,y |
     //   C+5..C+7 conic xx,xy,yy | C+8 opacity
     float* flush_base = nullptr;
-    int flush_stride = 0;
+    uint32_t flush_stride = 0;
     {
         const int v = lane >> 1;
         if ((lane & 1) == 0) {
@@ -182,8 +182,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             for (int q = 0; q < 16; ++q) v[q] = 0.f;
 
             if (blend) {
-                // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha)
-                const float inv = __frcp_rn(1.f - alpha);
+                // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha); 1 - alpha is in
+                // [0.01, 1], so MUFU.RCP plus one Newton step is within an ulp of the reference's division
+                const float om = 1.f - alpha;
+                float inv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(om));
+                inv = __fmaf_rn(__fmaf_rn(-om, inv, 1.f), inv, inv);
                 T = T * inv;
                 const float w = alpha * T;
                 float dL_dalpha = 0.0f;
@@ -231,7 +235,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const float total_v = warp_transpose_reduce16(v, lane);
             if (flush_base != nullptr) {
                 const int gid = __float_as_int(xyd.w);
-                atomicAdd(flush_base + (size_t)gid * flush_stride, total_v);
+                atomicAdd(flush_base + (uint32_t)gid * (uint32_t)flush_stride, total_v);
             }
         }
     };

@@ -30,6 +30,7 @@ for cs in range(3):
     g = torch.Generator().manual_seed(0)
     tiles = torch.randperm(1200, generator=g)[:150].tolist()
     tot_wg = any_wg = tot_pg = any_pg = aabb_wg = 0
+    lane_hist = torch.zeros(33, dtype=torch.long)
     for tl in tiles:
         lo, hi = int(ranges[tl, 0]), int(ranges[tl, 1])
         if hi <= lo:
@@ -50,6 +51,7 @@ for cs in range(3):
         w = k2.view(4, 4, 2, 8, -1).permute(0, 2, 1, 3, 4).reshape(8, 32, -1)   # 8 patches of 8x4
         lw = live.view(4, 4, 2, 8, -1).permute(0, 2, 1, 3, 4).reshape(8, 32, -1)
         tot_wg += int(lw.any(1).sum()); any_wg += int(w.any(1).sum())
+        lane_hist += torch.bincount(w.sum(1).reshape(-1).cpu(), minlength=33)[:33]
         # AABB of the alpha >= 1/255 ellipse vs each 8x4 patch
         t2 = 2 * torch.log(255 * co[:, 3])
         det = co[:, 0] * co[:, 2] - co[:, 1] ** 2
@@ -59,5 +61,8 @@ for cs in range(3):
             hit = (xy[:, 0] + hx >= x0) & (xy[:, 0] - hx <= x0 + 7) & (xy[:, 1] + hy >= y0) & (xy[:, 1] - hy <= y0 + 3) & (t2 > 0)
             aabb_wg += int((hit & lw[wq].any(0)).sum())
         tot_pg += int(live.sum()); any_pg += int(k2.sum())
+    lh = lane_hist[1:].float(); lh = lh / lh.sum()
+    print("    blending lanes per any-blend (patch,Gaussian): 1:%.2f 2:%.2f 3-4:%.2f 5-8:%.2f 9-16:%.2f 17-31:%.2f 32:%.2f" % (
+        lh[0], lh[1], lh[2:4].sum(), lh[4:8].sum(), lh[8:16].sum(), lh[16:31].sum(), lh[31]))
     print(f"    sample: (patch,Gaussian) evaluated {tot_wg}, with >=1 blending pixel {any_wg} ({100*any_wg/max(tot_wg,1):.1f}%), AABB survivors {aabb_wg} ({100*aabb_wg/max(tot_wg,1):.1f}%); "
           f"(pixel,Gaussian) evaluated {tot_pg}, blended {any_pg} ({100*any_pg/max(tot_pg,1):.1f}%)")
