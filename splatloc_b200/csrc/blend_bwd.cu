@@ -247,8 +247,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     for (int t = start; t >= lo; t -= BLEND_CHUNK) {
         const uint32_t m = m_next;
         const bool bit = (t - lane >= lo) && ((m >> patch) & 1u);
-        const unsigned b = __ballot_sync(FULL, bit);
-        float4 r0, r1, r2;
+        float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
         if (bit) {
             const float4* src = reinterpret_cast<const float4*>(records + (t - lane));
             r0 = __ldg(src);
@@ -260,6 +259,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         backprop_parked(parked, parked_top);
 
         __syncwarp();
+        const unsigned b = __ballot_sync(0xffffffffu, bit);
         if (bit) {
             const int slot = __popc(b & lt);
             PairRecord* dst = &s_rec[warp][slot];

@@ -4,11 +4,13 @@
 // list on its own: no shared staging between warps, no CTA barrier.  The list arrives as an array
 // of 48-byte PairRecords (state.cuh) plus one mask byte per pair, both written once per frame by
 // the binning stage (binning.cu).  Bit w of the mask says whether the Gaussian can pass the
-// reference's alpha test anywhere in patch w; it comes from the axis-aligned bounding box of
+// reference's alpha test anywhere in patch w:
 //     alpha = min(0.99, o * exp(power)) >= 1/255   <=>   d^T Q d <= 2 ln(255 o),  Q = conic
-// whose half-widths are  hx = sqrt(2 ln(255 o) * Qyy / det Q),  hy = sqrt(2 ln(255 o) * Qxx / det Q)
-// (padded by 0.2 % + 0.05 px and 2e-5 in power units, far more than any float32 / ex2.approx
-// error).  A warp reads 32 mask bytes per step, ballots the survivors, fetches only their records
+// The mask byte holds the axis-aligned bounding box test of that ellipse, half-widths
+//     hx = sqrt(2 ln(255 o) * Qyy / det Q),  hy = sqrt(2 ln(255 o) * Qxx / det Q);
+// refined, for the patches the box touches, by the exact minimum of d^T Q d over the patch
+// rectangle (patch_reached) -- everything padded by 0.2-0.4 % + 0.05 px and >= 2e-5 in power
+// units, far more than any float32 / ex2.approx error.  A warp reads 32 mask bytes per step, ballots the survivors, fetches only their records
 // into a warp-private shared buffer (while it blends the previous chunk) and evaluates those with
 // the reference's exact arithmetic.  The test is conservative and list positions are kept, so
 // colour, depth, alpha and n_contrib stay bit-identical -- the reference would have `continue`d on
@@ -51,6 +53,31 @@ __device__ __forceinline__ PatchGeom patch_geom(int tile, int grid_x, int warp, 
     return g;
 }
 
+// Exact refinement of the reach mask for ONE patch: can d^T Q d drop to `limit` (2 ln(255 o), padded)
+// anywhere on the patch rectangle [wx0, wx1] x [wy0, wy1]?  The form is convex with its minimum at the Gaussian's centre,
+// so if the centre is outside the rectangle the minimum lies on an edge facing the centre (at most
+// two), where it is the clamped vertex of a 1-D parabola.
+__device__ __forceinline__ bool patch_reached(float cx, float cy, const float4& co, float limit,
+                                              float wx0, float wx1, float wy0, float wy1)
+{
+    const float x0 = wx0 - 0.05f - cx, x1 = wx1 + 0.05f - cx;   // rectangle relative to the centre
+    const float y0 = wy0 - 0.05f - cy, y1 = wy1 + 0.05f - cy;
+    const bool in_x = x0 <= 0.f && x1 >= 0.f, in_y = y0 <= 0.f && y1 >= 0.f;
+    if (in_x && in_y) return true;
+    float best = 3.4e38f;
+    if (!in_x) {
+        const float u = x0 > 0.f ? x0 : x1;                                  // the edge facing the centre
+        const float v = fminf(fmaxf(__fdividef(-co.y * u, co.z), y0), y1);
+        best = co.x * u * u + 2.0f * co.y * u * v + co.z * v * v;
+    }
+    if (!in_y) {
+        const float v = y0 > 0.f ? y0 : y1;
+        const float u = fminf(fmaxf(__fdividef(-co.y * v, co.x), x0), x1);
+        best = fminf(best, co.x * u * u + 2.0f * co.y * u * v + co.z * v * v);
+    }
+    return !(best > limit);
+}
+
 // Bit w of the result: the Gaussian may reach a pixel of warp w's 8x4 patch.
 __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4& co, int tile_x0, int tile_y0)
 {
@@ -80,6 +107,17 @@ __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4&
 #pragma unroll
     for (int r = 0; r < 4; ++r)
         if (rows & (1u << r)) m |= cols << (2 * r);
+
+    // exact test for the patches the box touches (typically 2-4 of them)
+    const float limit = t2 * 1.004f + 1e-4f;
+    const float ux = cx - (float)tile_x0, uy = cy - (float)tile_y0;
+    uint32_t cand = m;
+    while (cand) {
+        const int w = __ffs(cand) - 1;
+        cand &= cand - 1;
+        const float wx0 = (float)((w & 1) * 8), wy0 = (float)((w >> 1) * 4);
+        if (!patch_reached(ux, uy, co, limit, wx0, wx0 + 7.f, wy0, wy0 + 3.f)) m &= ~(1u << w);
+    }
     return m;
 }
 

@@ -104,8 +104,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
         // (1) survivors of this chunk, (2) their records in flight
         const uint32_t m = m_next;
         const bool bit = (c + lane < hi) && ((m >> patch) & 1u);
-        const unsigned b = __ballot_sync(0xffffffffu, bit);
-        float4 r0, r1, r2;
+        float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
         if (bit) {
             const float4* src = reinterpret_cast<const float4*>(records + (c + lane));
             r0 = __ldg(src);
@@ -120,6 +119,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
         // (4) park this chunk's survivors, in list order
         __syncwarp();
+        const unsigned b = __ballot_sync(0xffffffffu, bit);
         if (bit) {
             const int slot = __popc(b & lt);
             PairRecord* dst = &s_rec[warp][slot];

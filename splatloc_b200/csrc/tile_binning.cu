@@ -180,7 +180,7 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
                     const int g = wbase + 32 * r;
                     const unsigned long long other = smem[g ^ j];
                     const bool take_min = ((g & j) == 0) == ((g & k) == 0);
-                    key[r] = take_min ? min(key[r], other) : max(key[r], other);
+                    key[r] = ((key[r] < other) == take_min) ? key[r] : other;
                 }
             } else if (j >= 32) {
 #pragma unroll
@@ -204,7 +204,7 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
                 for (int r = 0; r < E; ++r) {
                     const unsigned long long other = __shfl_xor_sync(0xffffffffu, key[r], j);
                     const bool take_min = ((lane & j) == 0) == (((wbase + 32 * r) & k) == 0);
-                    key[r] = take_min ? min(key[r], other) : max(key[r], other);
+                    key[r] = ((key[r] < other) == take_min) ? key[r] : other;
                 }
             }
         }

@@ -11,9 +11,9 @@ EMPTY = torch.Tensor([])
 
 
 def scene_inputs(P, seed, cam_seed=None, channels=4, sh_degree=None, intrinsics=None, size=None,
-                 device="cuda", use_cov3d=False, tile_mask_seed=None, bg=None):
-    sc = scenes.make_scene(P, seed, channels=channels, sh_degree=sh_degree)
-    cam = scenes.make_camera(seed if cam_seed is None else cam_seed, intrinsics=intrinsics, size=size)
+                 device="cuda", use_cov3d=False, tile_mask_seed=None, bg=None, scale=1.0):
+    sc = scenes.make_scene(P, seed, channels=channels, sh_degree=sh_degree, scale=scale)
+    cam = scenes.make_camera(seed if cam_seed is None else cam_seed, intrinsics=intrinsics, size=size, scale=scale)
     C = 3 if sh_degree is not None else channels
     d = {k: v.to(device) for k, v in sc.items()}
     d["cam"] = cam.to(device)

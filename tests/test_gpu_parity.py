@@ -79,6 +79,26 @@ def test_long_tile_lists_take_the_large_and_fallback_sorts():
         assert not bad, f"longest list {longest}\n" + "\n".join(bad)
 
 
+@pytest.mark.parametrize("name,case", [
+    ("config1_200k_sh3", dict(P=200000, seed=0, sh_degree=3)),
+    ("config3_1200k_scenes12", dict(P=1200000, seed=1, intrinsics="scenes12")),
+    ("config4_3M_1296x968", dict(P=3000000, seed=2, size=(1296, 968), scale=1.5)),
+])
+def test_baseline_configs_match_reference_cuda(name, case):
+    """BASELINE.json's configurations at full size, one view each, against the reference CUDA build."""
+    from splatloc_b200 import scenes
+    ref, ours = _ref(), _ours()
+    case = dict(case)
+    if case.get("intrinsics") == "scenes12":
+        case["intrinsics"] = scenes.SCENES12_INTRINSICS
+    d = H.scene_inputs(**case)
+    b = H.run_backend(ref, d)
+    a = H.run_backend(ours, d)
+    assert b["R"] > 100000
+    bad = H.compare(a, b)
+    assert not bad, f"{name}: R={b['R']}\n" + "\n".join(bad)
+
+
 def test_empty_and_invisible():
     ours = _ours()
     # P == 0 -> zero outputs, R == 0
@@ -116,7 +136,7 @@ def test_mark_visible_matches_reference():
     assert 0 < int(a.sum()) < a.numel()
 
 
-@pytest.mark.parametrize("P", [1, 2, 3, 5, 1000, 100000, 1000000])
+@pytest.mark.parametrize("P", [1, 2, 3, 5, 1000, 100000, 1000000, 5000000])
 def test_knn_bit_exact(P):
     from splatloc_b200 import scenes
     ref, ours = _ref(), _ours()
