@@ -141,7 +141,9 @@ def run_gpu(args, impl):
         world = 1
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=dev)
+        import datetime
+        # short collective timeout: a rank that dies must not park the others for NCCL's default 10 minutes
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
 
     be, Settings, Rasterizer = load_backend(impl)
     P, C = args.points, C_DEFAULT
