@@ -112,6 +112,15 @@ def algorithmic_bytes(P, V, R, N, Tn, C, M_sh=0):
     }
 
 
+def measured_traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the committed `ncu --set full` capture (profiles/)."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
+
+
 def measured_peaks():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -324,7 +333,7 @@ def run_gpu(args, impl):
         top = max(stages, key=lambda k: stages[k]["ms"])
         ach = stages[top]["GBps"]
         out["roofline"] = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
-                           "frac": round(ach / peak, 4), "traffic": None, "peak_source": how,
+                           "frac": round(ach / peak, 4), "traffic": measured_traffic(top), "peak_source": how,
                            "note": "blend kernels are FP32/SFU/atomic-bound; see profiles/ for pipe utilisation",
                            "step_alg_MB": round(sum(alg.values()) / 1e6, 1),
                            "step_frac": round(sum(alg.values()) / (ms_step * 1e-3) / 1e9 / peak, 4)}
