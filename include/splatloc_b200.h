@@ -111,6 +111,44 @@ int sl_backward(int P, int D, int M, int R, int C,
                 float* dL_dsh, float* dL_dscale, float* dL_drot,
                 int debug, void* stream);
 
+/* ---- extensions named by the task's north_star that the reference does NOT have (its rasterizer
+ * returns no camera gradient and no n_touched, DGR/diff_gauss/__init__.py:122,162,170-181); both are
+ * MonoGS-style additions, opt-in, and leave every reference-facing result unchanged.
+ *
+ * sl_forward_ext = sl_forward + n_touched [P] int32 (may be NULL): number of pixels in which the
+ * Gaussian is blended while the transmittance behind it is still above 0.5.
+ *
+ * sl_backward_ext = sl_backward + dL_dtau [6] (may be NULL; must be ZERO on entry): gradient of the loss
+ * w.r.t. a left perturbation of the world-to-camera transform, W2C' = Exp(rho, theta) * W2C, evaluated
+ * at rho = theta = 0; dL_dtau = (dL/drho xyz, dL/dtheta xyz).  It accounts for the projected centre,
+ * the depth, the EWA covariance (through the camera-frame mean and the rotation) and, with SH colours,
+ * the view direction. */
+int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                   sl_alloc_fn binning_alloc, void* binning_ctx,
+                   sl_alloc_fn image_alloc, void* image_ctx,
+                   int P, int D, int M, int C,
+                   const float* background, int width, int height,
+                   const float* means3D, const float* shs, const float* colors_precomp,
+                   const float* opacities, const float* scales, float scale_modifier,
+                   const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                   const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                   float tan_fovx, float tan_fovy, int prefiltered,
+                   float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                   int debug, void* stream);
+int sl_backward_ext(int P, int D, int M, int R, int C,
+                    const float* background, int width, int height,
+                    const float* means3D, const float* shs, const float* colors_precomp,
+                    const float* scales, float scale_modifier, const float* rotations,
+                    const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                    const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                    char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                    const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                    const float* dL_dpix_alpha,
+                    float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                    float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                    float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                    int debug, void* stream);
+
 /* Frustum visibility, present[i] in {0,1}.  Replaces
  * CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:71-76,
  * rasterizer_impl.cu:379-391), bound by markVisible (DGR/rasterize_points.cu:215-234). */

@@ -265,6 +265,7 @@ def blend_forward(pre, pairs, features, bg, W, H):
     depth = torch.zeros((H, W), dtype=dtype)
     alpha_out = torch.zeros((H, W), dtype=dtype)
     n_contrib = torch.zeros((H, W), dtype=torch.int32)
+    n_touched = torch.zeros(features.shape[0], dtype=torch.int64)
     xy_all, co_all, dep_all = pre["means2D"], pre["conic_opacity"], pre["depths"]
     pl = pairs["point_list"].long()
     for tile, (lo, hi) in enumerate(pairs["ranges"].tolist()):
@@ -285,6 +286,9 @@ def blend_forward(pre, pairs, features, bg, W, H):
             T_before = torch.cat([T[:, None], T_after[:, :-1]], 1)
             inc = keep & ~done[:, None] & ~(T_before < 0.0001)
             w = torch.where(inc, alpha * T_before, torch.zeros_like(alpha))
+            # extension (no reference counterpart): pixels where the Gaussian is blended and more than
+            # half of the light still passes behind it
+            n_touched.index_add_(0, ids, (inc & (T_after.detach() > 0.5)).sum(0))
             acc = acc + w @ features[ids]
             D = D + w @ dep_all[ids]
             pos = torch.arange(s - lo + 1, s - lo + 1 + ids.numel())
@@ -297,6 +301,7 @@ def blend_forward(pre, pairs, features, bg, W, H):
         depth[py, px] = D
         alpha_out[py, px] = 1 - T
         n_contrib[py, px] = last.to(torch.int32)
+    pre["n_touched"] = n_touched.to(torch.int32)
     return color, depth, alpha_out, n_contrib
 
 
@@ -389,11 +394,29 @@ def forward(means3D, opacities, view, proj, campos, W, H, tan_fovx, tan_fovy, bg
     bg64 = _f64(bg).reshape(-1)[: feats.shape[1]]
     color, depth, alpha, n_contrib = blend_forward(pre, pairs, feats, bg64, W, H)
     return dict(pre=pre, pairs=pairs, color=color, depth=depth, alpha=alpha, n_contrib=n_contrib, bg=bg64,
-                R=int(pairs["keys_sorted"].numel()))
+                n_touched=pre["n_touched"], R=int(pairs["keys_sorted"].numel()))
+
+
+def perturbed_camera(view0, proj0, tau):
+    """viewmatrix / projmatrix / campos (reference convention: transposed, utils/camera_utils.py:129-139) of
+    the camera W2C' = Exp(rho, theta) W2C, to first order in tau = (rho, theta) -- exact for the gradient at
+    tau = 0, which is where MonoGS-style pose refinement evaluates it.  Extension; no reference counterpart."""
+    rho, th = tau[:3], tau[3:]
+    z = torch.zeros((), dtype=tau.dtype)
+    skew = torch.stack([torch.stack([z, -th[2], th[1]]), torch.stack([th[2], z, -th[0]]), torch.stack([-th[1], th[0], z])])
+    M = torch.eye(4, dtype=tau.dtype)
+    M = torch.cat([torch.cat([torch.eye(3, dtype=tau.dtype) + skew, rho.reshape(3, 1)], 1), M[3:]], 0)
+    w2c0 = view0.reshape(4, 4).transpose(0, 1)
+    w2c = M @ w2c0
+    view = w2c.transpose(0, 1)
+    proj_t = torch.linalg.inv(view0.reshape(4, 4)) @ proj0.reshape(4, 4)       # P^T
+    proj = view @ proj_t
+    campos = torch.linalg.inv(view)[3, :3]
+    return view.reshape(-1), proj.reshape(-1), campos
 
 
 def backward(fw, means3D, view, proj, campos, W, H, tan_fovx, tan_fovy, dL_dcolor, dL_ddepth, dL_dalpha,
-             shs=None, sh_degree=0, scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0):
+             shs=None, sh_degree=0, scales=None, rotations=None, cov3D_precomp=None, scale_modifier=1.0, pose=False):
     """rasterizer_impl.cu:586-692 (Rasterizer::backward): blend backward (explicit, above), then the
     per-Gaussian chain of backward.cu:534-664 (computeCov2DCUDA) and :949-1015 (preprocessCUDA) obtained
     by reverse-mode differentiation of the float64 forward expressions -- which is what those two
@@ -406,6 +429,11 @@ def backward(fw, means3D, view, proj, campos, W, H, tan_fovx, tan_fovy, dL_dcolo
     vi = torch.nonzero(vis).squeeze(1)
     m3 = _f64(means3D).clone().requires_grad_(True)
     view64, proj64 = _f64(view).reshape(-1), _f64(proj).reshape(-1)
+    campos64 = _f64(campos)
+    tau = None
+    if pose:
+        tau = torch.zeros(6, dtype=torch.float64, requires_grad=True)
+        view64, proj64, campos64 = perturbed_camera(view64, proj64, tau)
     sc = rot = c3p = sh = None
     # the chain is evaluated on the visible subset only (culled Gaussians may have singular
     # covariances); autograd scatters zeros to the rest, like the kernels' `radii > 0` guard
@@ -435,7 +463,7 @@ def backward(fw, means3D, view, proj, campos, W, H, tan_fovx, tan_fovy, dL_dcolo
     g_sh = None
     if shs is not None:
         sh = _f64(shs).clone().requires_grad_(True)
-        rgb, _ = sh_to_rgb(sh_degree, sh[vi], m3v, _f64(campos))
+        rgb, _ = sh_to_rgb(sh_degree, sh[vi], m3v, campos64)
         loss = loss + (rgb * gb["color"][vi]).sum()
     loss.backward()
     P = m3.shape[0]
@@ -449,7 +477,8 @@ def backward(fw, means3D, view, proj, campos, W, H, tan_fovx, tan_fovy, dL_dcolo
                 g_abs2D=torch.cat([gb["absmean2D"], torch.zeros((P, 1), dtype=torch.float64)], 1),
                 g_colors=gb["color"], g_opacity=gb["opacity"].reshape(P, 1), g_means3D=z(m3, (P, 3)),
                 g_cov3D=g_cov3D, g_sh=g_sh if g_sh is not None else torch.zeros((P, 0, 3), dtype=torch.float64),
-                g_scales=z(sc, (P, 3)), g_rot=z(rot, (P, 4)), g_conic=gb["conic"], g_depth=gb["depth"])
+                g_scales=z(sc, (P, 3)), g_rot=z(rot, (P, 4)), g_conic=gb["conic"], g_depth=gb["depth"],
+                g_tau=None if tau is None else (tau.grad if tau.grad is not None else torch.zeros(6, dtype=torch.float64)))
 
 
 def mark_visible(means3D, view, proj):

@@ -72,8 +72,9 @@ def _channels(colors: torch.Tensor) -> int:
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
                         cov3D_precomp, tile_mask, viewmatrix, projmatrix, tan_fovx, tan_fovy,
-                        image_height, image_width, sh, degree, campos, prefiltered, debug):
-    """-> (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer)."""
+                        image_height, image_width, sh, degree, campos, prefiltered, debug, want_n_touched=False):
+    """-> (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer)
+    [+ n_touched (P,) int32 as a 9th element when `want_n_touched` -- an extension, see sl_forward_ext]."""
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     lib = _capi.load()
@@ -111,8 +112,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         out_alpha = torch.empty((1, H, W), **f_opts)
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         geom, binning, img = _Chunk(dev), _Chunk(dev), _Chunk(dev)
+        n_touched = torch.zeros((P,), dtype=torch.int32, device=dev) if want_n_touched else None
         rendered = 0
-        rc = lib.sl_forward(
+        rc = lib.sl_forward_ext(
             geom.callback, None, binning.callback, None, img.callback, None,
             P, int(degree), M, n_ch,
             _ptr(background), W, H,
@@ -121,10 +123,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             _ptr(rotations), _ptr(cov3D_precomp), _ptr(tile_mask),
             _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos),
             float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-            _ptr(out_color), _ptr(out_depth), _ptr(out_alpha), _ptr(radii),
+            _ptr(out_color), _ptr(out_depth), _ptr(out_alpha), _ptr(radii), _ptr(n_touched),
             int(bool(debug)), _stream(dev))
         rendered = _capi.check(rc)
-    return rendered, out_color, out_depth, out_alpha, radii, geom.tensor, binning.tensor, img.tensor
+    out = (rendered, out_color, out_depth, out_alpha, radii, geom.tensor, binning.tensor, img.tensor)
+    return out + (n_touched,) if want_n_touched else out
 
 
 def _grad_block(P: int, widths: list[int], device) -> list[torch.Tensor]:
@@ -141,9 +144,10 @@ def _grad_block(P: int, widths: list[int], device) -> list[torch.Tensor]:
 def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rotations, scale_modifier,
                                  cov3D_precomp, viewmatrix, projmatrix, tan_fovx, tan_fovy,
                                  dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
-                                 geomBuffer, R, binningBuffer, imageBuffer, out_alpha, debug):
+                                 geomBuffer, R, binningBuffer, imageBuffer, out_alpha, debug, want_pose=False):
     """-> (dL_dabsmeans2D, dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D,
-           dL_dsh, dL_dscales, dL_drotations)."""
+           dL_dsh, dL_dscales, dL_drotations)
+    [+ dL_dtau (6,) = (dL/drho, dL/dtheta) as a 10th element when `want_pose` -- see sl_backward_ext]."""
     lib = _capi.load()
     dev = means3D.device
     P = int(means3D.shape[0])
@@ -170,8 +174,9 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     with torch.cuda.device(dev):
         (g_mean3D, g_mean2D, g_abs2D, g_color, g_depth, g_conic, g_opac, g_cov3D, g_sh, g_scale,
          g_rot) = _grad_block(P, [3, 3, 3, n_ch, 1, 4, 1, 6, 3 * M, 3, 4], dev)
+        g_tau = torch.zeros(6, dtype=torch.float32, device=dev) if want_pose else None
         if P != 0:
-            rc = lib.sl_backward(
+            rc = lib.sl_backward_ext(
                 P, int(degree), M, int(R), n_ch,
                 _ptr(background), W, H,
                 _ptr(means3D), _ptr(sh), _ptr(colors),
@@ -182,12 +187,13 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
                 _ptr(out_alpha), _ptr(dL_dout_color), _ptr(dL_dout_depth), _ptr(dL_dout_alpha),
                 g_mean2D.data_ptr(), g_abs2D.data_ptr(), g_conic.data_ptr(), g_opac.data_ptr(),
                 g_color.data_ptr(), g_depth.data_ptr(), g_mean3D.data_ptr(), g_cov3D.data_ptr(),
-                _ptr(g_sh), g_scale.data_ptr(), g_rot.data_ptr(),
+                _ptr(g_sh), g_scale.data_ptr(), g_rot.data_ptr(), _ptr(g_tau),
                 int(bool(debug)), _stream(dev))
             _capi.check(rc)
-    return (g_abs2D.view(P, 3), g_mean2D.view(P, 3), g_color.view(P, n_ch), g_opac.view(P, 1),
-            g_mean3D.view(P, 3), g_cov3D.view(P, 6), g_sh.view(P, M, 3), g_scale.view(P, 3),
-            g_rot.view(P, 4))
+    out = (g_abs2D.view(P, 3), g_mean2D.view(P, 3), g_color.view(P, n_ch), g_opac.view(P, 1),
+           g_mean3D.view(P, 3), g_cov3D.view(P, 6), g_sh.view(P, M, 3), g_scale.view(P, 3),
+           g_rot.view(P, 4))
+    return out + (g_tau,) if want_pose else out
 
 
 def mark_visible(means3D, viewmatrix, projmatrix):

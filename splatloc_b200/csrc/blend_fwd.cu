@@ -23,13 +23,14 @@
 
 namespace sl {
 
-template <int C>
+template <int C, bool TOUCH>
 __global__ void __launch_bounds__(BLEND_THREADS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                      const PairRecord* __restrict__ records, const uint8_t* __restrict__ masks,
                      int W, int H, int grid_x, const float* __restrict__ bg,
                      float* __restrict__ out_color, float* __restrict__ out_depth,
-                     float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib)
+                     float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
+                     int* __restrict__ n_touched)
 {
     __shared__ PairRecord s_rec[BLEND_WARPS][BLEND_CHUNK];
     __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];   // chunk-relative index of each parked record
@@ -73,6 +74,7 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                     const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
                     const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
                     const float power = __fmaf_rn(s, -0.5f, -t3);
+                    bool touched = false;
                     if (!(power > 0.0f)) {
                         const float alpha = fminf(0.99f, __fmul_rn(co.w, exp_like_reference(power)));
                         if (!(alpha < 1.0f / 255.0f)) {
@@ -86,7 +88,15 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                             T = test_T;
                             last_contributor = first_pos + lds_u8(lane_a + k);
                             if (test_T < 0.0001f) done = true;
+                            touched = test_T > 0.5f;
                         }
+                    }
+                    if (TOUCH) {
+                        // extension (MonoGS-style n_touched): pixels in which this Gaussian is blended
+                        // while more than half of the light still passes behind it
+                        const unsigned tb = __ballot_sync(__activemask(), touched);
+                        if (touched && (tb & ((1u << (threadIdx.x & 31)) - 1u)) == 0)
+                            atomicAdd(&n_touched[__float_as_int(xyd.w)], __popc(tb));
                     }
                 }
             }
@@ -146,19 +156,23 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
 int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                          const PairRecord* records, const uint8_t* masks, const float* bg, float* out_color,
-                         float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream)
+                         float* out_depth, float* out_alpha, uint32_t* n_contrib, int* n_touched,
+                         cudaStream_t stream)
 {
     const int tiles = vp.grid_x * vp.grid_y;
-    if (C == 4)
-        blend_forward_kernel<4><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
-            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_color, out_depth, out_alpha, n_contrib);
-    else if (C == 3)
-        blend_forward_kernel<3><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
-            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_color, out_depth, out_alpha, n_contrib);
-    else {
+#define SL_LAUNCH_FWD(CC, TT)                                                                                    \
+    blend_forward_kernel<CC, TT><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(                               \
+        ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_color, out_depth, out_alpha, n_contrib, \
+        n_touched)
+    if (C == 4) {
+        if (n_touched) SL_LAUNCH_FWD(4, true); else SL_LAUNCH_FWD(4, false);
+    } else if (C == 3) {
+        if (n_touched) SL_LAUNCH_FWD(3, true); else SL_LAUNCH_FWD(3, false);
+    } else {
         set_error("blend_forward: unsupported channel count %d (3 or 4)", C);
         return -2;
     }
+#undef SL_LAUNCH_FWD
     count_launch();
     return 0;
 }

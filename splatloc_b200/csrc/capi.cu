@@ -189,6 +189,25 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                float* out_color, float* out_depth, float* out_alpha, int* radii,
                int debug, void* stream_)
 {
+    return sl_forward_ext(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, C,
+                          background, width, height, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
+                          rotations, cov3D_precomp, tile_mask, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
+                          prefiltered, out_color, out_depth, out_alpha, radii, nullptr, debug, stream_);
+}
+
+int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                   sl_alloc_fn binning_alloc, void* binning_ctx,
+                   sl_alloc_fn image_alloc, void* image_ctx,
+                   int P, int D, int M, int C,
+                   const float* background, int width, int height,
+                   const float* means3D, const float* shs, const float* colors_precomp,
+                   const float* opacities, const float* scales, float scale_modifier,
+                   const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                   const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                   float tan_fovx, float tan_fovy, int prefiltered,
+                   float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                   int debug, void* stream_)
+{
     g_error[0] = 0;
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool dbg = debug != 0;
@@ -210,6 +229,7 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         SL_CUDA(cudaMemsetAsync(out_alpha, 0, N * sizeof(float), stream), "forward memset");
         return 0;
     }
+    if (n_touched != nullptr) SL_CUDA(cudaMemsetAsync(n_touched, 0, (size_t)P * sizeof(int), stream), "n_touched memset");
     if (!means3D || !opacities || (!cov3D_precomp && (!scales || !rotations))) {
         set_error("sl_forward: means3D, opacities and either cov3D_precomp or scales+rotations are required");
         return SL_ERR_ARGUMENT;
@@ -323,7 +343,7 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     {
         StageTimer t(ST_BLEND_FWD, stream);
         rc = launch_blend_forward(C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background, out_color,
-                                  out_depth, out_alpha, img.n_contrib, stream);
+                                  out_depth, out_alpha, img.n_contrib, n_touched, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend forward");
@@ -343,6 +363,27 @@ int sl_backward(int P, int D, int M, int R, int C,
                 float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
                 float* dL_dsh, float* dL_dscale, float* dL_drot,
                 int debug, void* stream_)
+{
+    return sl_backward_ext(P, D, M, R, C, background, width, height, means3D, shs, colors_precomp, scales,
+                           scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx, tan_fovy,
+                           radii, geometry_chunk, binning_chunk, image_chunk, accum_alphas, dL_dpix, dL_dpix_depth,
+                           dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth,
+                           dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, nullptr, debug, stream_);
+}
+
+int sl_backward_ext(int P, int D, int M, int R, int C,
+                    const float* background, int width, int height,
+                    const float* means3D, const float* shs, const float* colors_precomp,
+                    const float* scales, float scale_modifier, const float* rotations,
+                    const float* cov3D_precomp, const float* viewmatrix, const float* projmatrix,
+                    const float* campos, float tan_fovx, float tan_fovy, const int* radii,
+                    char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                    const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                    const float* dL_dpix_alpha,
+                    float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                    float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                    float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                    int debug, void* stream_)
 {
     g_error[0] = 0;
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -389,7 +430,7 @@ int sl_backward(int P, int D, int M, int R, int C,
         StageTimer t(ST_PREPROCESS_BWD, stream);
         rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, scales, rotations, cov3D_ptr,
                                         viewmatrix, projmatrix, campos, vp, dL_dmean2D, dL_dconic, dL_dmean3D,
-                                        dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, stream);
+                                        dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess backward");

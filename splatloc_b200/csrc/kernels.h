@@ -64,7 +64,8 @@ int launch_build_records(int R, int C, const uint64_t* sorted_keys, const uint32
 // K6: forward alpha blending per 16x16 tile (reference: renderCUDA, forward.cu:844-963).
 int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                          const PairRecord* records, const uint8_t* masks, const float* bg, float* out_color,
-                         float* out_depth, float* out_alpha, uint32_t* n_contrib, cudaStream_t stream);
+                         float* out_depth, float* out_alpha, uint32_t* n_contrib, int* n_touched,
+                         cudaStream_t stream);
 
 // K7: backward blending (reference: BACKWARD::render, backward.cu:1018-1209).
 int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
@@ -81,7 +82,7 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
                                const float* projmatrix, const float* campos, const ViewParams& vp,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, const float* dL_ddepth, float* dL_dcov3D, float* dL_dsh,
-                               float* dL_dscale, float* dL_drot, cudaStream_t stream);
+                               float* dL_dscale, float* dL_drot, float* dL_dtau, cudaStream_t stream);
 
 // K11-K15: mean squared distance to the 3 nearest neighbours (reference: SimpleKNN::knn,
 // simple_knn.cu:186-221).  `scratch` must hold knn_scratch_bytes(P) bytes.

@@ -17,8 +17,10 @@
 
 namespace sl {
 
-__global__ void __launch_bounds__(256)
-preprocess_backward_kernel(int P, int D, int M, int C,
+// One visible Gaussian.  `pose` (when wanted) receives this Gaussian's contribution to the gradient of
+// the loss w.r.t. a left perturbation Exp(rho, theta) of the world-to-camera transform.
+__device__ __forceinline__ void
+per_gaussian_backward(int idx, int D, int M, int C,
                            const float* __restrict__ means3D, const int* __restrict__ radii,
                            const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                            const float* __restrict__ scales, const float* __restrict__ rotations,
@@ -33,11 +35,9 @@ preprocess_backward_kernel(int P, int D, int M, int C,
                            float* __restrict__ dL_dcov,           // (P,6)
                            float* __restrict__ dL_dsh,            // (P,M,3)
                            float* __restrict__ dL_dscale,         // (P,3)
-                           float* __restrict__ dL_drot)           // (P,4)
+                           float* __restrict__ dL_drot,           // (P,4)
+                           bool want_pose, float (&pose)[6])
 {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P || !(radii[idx] > 0)) return;
-
     const float* cov3D = cov3Ds + 6 * idx;
     const f3 mean = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     const float h_x = vp.focal_x, h_y = vp.focal_y;
@@ -45,6 +45,7 @@ preprocess_backward_kernel(int P, int D, int M, int C,
     // ---------------------------------------------------------------- conic -> cov2D -> cov3D, t
     const f3 dL_dconic = {dL_dconics[4 * idx], dL_dconics[4 * idx + 1], dL_dconics[4 * idx + 3]};
     f3 t = xform_4x3(mean, view);
+    const f3 t_cam = t;   // camera-frame position before the covariance clamp
 
     const float limx = 1.3f * vp.tan_fovx;
     const float limy = 1.3f * vp.tan_fovy;
@@ -159,6 +160,38 @@ preprocess_backward_kernel(int P, int D, int M, int C,
         g_mean.z += g.z;
     }
 
+    // ---------------------------------------------------------------- camera pose (extension)
+    // W2C' = Exp(rho, theta) W2C moves every camera-frame point by rho + theta x t and rotates the
+    // rows of the world-to-camera rotation R (the W of the EWA projection, T = W J).  With g_t the
+    // gradient w.r.t. the camera-frame mean (covariance path directly, projection and depth paths
+    // rotated from the world frame) and G = dL/dR from dL/dT:
+    //     dL/drho = g_t (+ R g_SH),   dL/dtheta = t x g_t + sum_r R[:, r] x G[:, r].
+    if (want_pose) {
+        // world-frame pieces so far minus the covariance piece = projection + depth paths
+        const float wx = g_mean.x - (view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz);
+        const float wy = g_mean.y - (view[4] * dL_dtx + view[5] * dL_dty + view[6] * dL_dtz);
+        const float wz = g_mean.z - (view[8] * dL_dtx + view[9] * dL_dty + view[10] * dL_dtz);
+        const float gtx = dL_dtx + view[0] * wx + view[4] * wy + view[8] * wz;
+        const float gty = dL_dty + view[1] * wx + view[5] * wy + view[9] * wz;
+        const float gtz = dL_dtz + view[2] * wx + view[6] * wy + view[10] * wz;
+        pose[0] = gtx;
+        pose[1] = gty;
+        pose[2] = gtz;
+        pose[3] = t_cam.y * gtz - t_cam.z * gty;
+        pose[4] = t_cam.z * gtx - t_cam.x * gtz;
+        pose[5] = t_cam.x * gty - t_cam.y * gtx;
+        const float dT0[3] = {dL_dT00, dL_dT01, dL_dT02}, dT1[3] = {dL_dT10, dL_dT11, dL_dT12};
+#pragma unroll
+        for (int r = 0; r < 3; ++r) {
+            const float G0 = dT0[r] * J.c[0][0], G1 = dT1[r] * J.c[1][1];
+            const float G2 = dT0[r] * J.c[0][2] + dT1[r] * J.c[1][2];
+            const float R0 = view[4 * r + 0], R1 = view[4 * r + 1], R2 = view[4 * r + 2];   // column r of R
+            pose[3] += R1 * G2 - R2 * G1;
+            pose[4] += R2 * G0 - R0 * G2;
+            pose[5] += R0 * G1 - R1 * G0;
+        }
+    }
+
     // ---------------------------------------------------------------- colour -> SH (+ view direction)
     if (shs != nullptr) {
         f3 cp = {campos[0], campos[1], campos[2]};
@@ -167,6 +200,11 @@ preprocess_backward_kernel(int P, int D, int M, int C,
         g_mean.x += g.x;
         g_mean.y += g.y;
         g_mean.z += g.z;
+        if (want_pose) {   // the camera centre moves by -R^T rho: dL/drho += R g_SH
+            pose[0] += view[0] * g.x + view[4] * g.y + view[8] * g.z;
+            pose[1] += view[1] * g.x + view[5] * g.y + view[9] * g.z;
+            pose[2] += view[2] * g.x + view[6] * g.y + view[10] * g.z;
+        }
     }
     dL_dmeans[3 * idx + 0] = g_mean.x;
     dL_dmeans[3 * idx + 1] = g_mean.y;
@@ -224,17 +262,59 @@ preprocess_backward_kernel(int P, int D, int M, int C,
     }
 }
 
+__global__ void __launch_bounds__(256)
+preprocess_backward_kernel(int P, int D, int M, int C,
+                           const float* __restrict__ means3D, const int* __restrict__ radii,
+                           const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
+                           const float* __restrict__ scales, const float* __restrict__ rotations,
+                           const float* __restrict__ cov3Ds, const float* __restrict__ view,
+                           const float* __restrict__ proj, const float* __restrict__ campos,
+                           ViewParams vp,
+                           const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconics,
+                           float* __restrict__ dL_dmeans, const float* __restrict__ dL_dcolor,
+                           const float* __restrict__ dL_ddepth, float* __restrict__ dL_dcov,
+                           float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,
+                           float* __restrict__ dL_drot, float* dL_dtau)
+{
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const bool want_pose = dL_dtau != nullptr;
+    float pose[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    if (idx < P && radii[idx] > 0)
+        per_gaussian_backward(idx, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3Ds, view, proj,
+                              campos, vp, dL_dmean2D, dL_dconics, dL_dmeans, dL_dcolor, dL_ddepth, dL_dcov, dL_dsh,
+                              dL_dscale, dL_drot, want_pose, pose);
+    if (!want_pose) return;
+
+    // 6 floats per view: warp shuffle, then shared memory across the 8 warps, one atomic per CTA and value
+    __shared__ float s_pose[8][6];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+#pragma unroll
+    for (int k = 0; k < 6; ++k) {
+        float v = pose[k];
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+        if (lane == 0) s_pose[warp][k] = v;
+    }
+    __syncthreads();
+    if (threadIdx.x < 6) {
+        float v = 0.f;
+#pragma unroll
+        for (int w = 0; w < 8; ++w) v += s_pose[w][threadIdx.x];
+        if (v != 0.f) atomicAdd(&dL_dtau[threadIdx.x], v);
+    }
+}
+
 int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
                                const float* shs, const uint8_t* clamped, const float* scales,
                                const float* rotations, const float* cov3D, const float* viewmatrix,
                                const float* projmatrix, const float* campos, const ViewParams& vp,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
                                float* dL_dcolor, const float* dL_ddepth, float* dL_dcov3D, float* dL_dsh,
-                               float* dL_dscale, float* dL_drot, cudaStream_t stream)
+                               float* dL_dscale, float* dL_drot, float* dL_dtau, cudaStream_t stream)
 {
     preprocess_backward_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
         P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrix, projmatrix, campos,
-        vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot); count_launch();
+        vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau); count_launch();
     return 0;
 }
 

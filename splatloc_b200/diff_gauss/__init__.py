@@ -63,23 +63,27 @@ def _call_with_snapshot(fn, args, debug, dump_path, what):
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                cov3Ds_precomp, tile_mask, raster_settings):
+                cov3Ds_precomp, tile_mask, raster_settings, theta=None, rho=None, want_n_touched=False):
         rs = raster_settings
         fw_args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
                    cov3Ds_precomp, tile_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                    rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
-        (num_rendered, color, depth, alpha, radii, geom, binning, img) = _call_with_snapshot(
-            _C.rasterize_gaussians, fw_args, rs.debug, _DUMP_FW, "forward")
+        res = _call_with_snapshot(_C.rasterize_gaussians, fw_args + (want_n_touched,), rs.debug, _DUMP_FW, "forward")
+        (num_rendered, color, depth, alpha, radii, geom, binning, img) = res[:8]
 
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
+        ctx.want_pose = theta is not None or rho is not None
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geom, binning, img, alpha, means2D)
         ctx.mark_non_differentiable(radii)
+        if want_n_touched:
+            ctx.mark_non_differentiable(res[8])
+            return color, depth, alpha, radii, res[8]
         return color, depth, alpha, radii
 
     @staticmethod
-    def backward(ctx, grad_color, grad_depth, grad_alpha, _grad_radii):
+    def backward(ctx, grad_color, grad_depth, grad_alpha, _grad_radii, _grad_n_touched=None):
         rs = ctx.raster_settings
         (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img,
          alpha, means2D) = ctx.saved_tensors
@@ -87,19 +91,24 @@ class _RasterizeGaussians(torch.autograd.Function):
                    cov3Ds_precomp, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                    grad_color, grad_depth, grad_alpha, sh, rs.sh_degree, rs.campos,
                    geom, ctx.num_rendered, binning, img, alpha, rs.debug)
-        (g_abs2D, g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales, g_rot) = \
-            _call_with_snapshot(_C.rasterize_gaussians_backward, bw_args, rs.debug, _DUMP_BW, "backward")
+        res = _call_with_snapshot(_C.rasterize_gaussians_backward, bw_args + (ctx.want_pose,), rs.debug, _DUMP_BW,
+                                  "backward")
+        (g_abs2D, g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales, g_rot) = res[:9]
+        g_theta = g_rho = None
+        if ctx.want_pose:   # extension: camera-pose gradient, (rho, theta) order in the C ABI
+            g_rho, g_theta = res[9][:3], res[9][3:]
 
         # densification statistics read |dL/dmean2D| from this attribute
         means2D.absgrad = g_abs2D
         # one gradient per forward input; tile_mask and the settings have none
-        return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, None)
+        return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, None,
+                g_theta, g_rho, None)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                        cov3Ds_precomp, tile_mask, raster_settings):
+                        cov3Ds_precomp, tile_mask, raster_settings, theta=None, rho=None, want_n_touched=False):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, tile_mask, raster_settings)
+                                     cov3Ds_precomp, tile_mask, raster_settings, theta, rho, want_n_touched)
 
 
 def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: torch.Tensor):
@@ -108,16 +117,24 @@ def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: 
 
 
 class GaussianRasterizer(nn.Module):
-    def __init__(self, raster_settings: GaussianRasterizationSettings):
+    """The fork's module.  Two opt-in extensions the reference does not have (SURVEY.md section 0,
+    D1/D2) leave the default call unchanged:
+      * `theta=` / `rho=` (3-vectors, MonoGS's `cam_rot_delta` / `cam_trans_delta`): placeholders whose
+        values are taken as zero; after backward their `.grad` holds dL/dtheta, dL/drho for the left
+        perturbation W2C' = Exp(rho, theta) W2C of `viewmatrix` (and of `projmatrix`, `campos`);
+      * `return_n_touched=True` at construction: forward returns a 5th tensor, n_touched (P,) int32."""
+
+    def __init__(self, raster_settings: GaussianRasterizationSettings, return_n_touched: bool = False):
         super().__init__()
         self.raster_settings = raster_settings
+        self.return_n_touched = return_n_touched
 
     def markVisible(self, positions):
         rs = self.raster_settings
         return mark_visible(positions, rs.viewmatrix, rs.projmatrix)
 
     def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
-                rotations=None, cov3D_precomp=None, tile_mask=None):
+                rotations=None, cov3D_precomp=None, tile_mask=None, *, theta=None, rho=None):
         if (shs is None) == (colors_precomp is None):
             raise Exception('Please provide excatly one of either SHs or precomputed colors!')
         has_sr = scales is not None or rotations is not None
@@ -137,7 +154,8 @@ class GaussianRasterizer(nn.Module):
             tile_mask = tile_mask.bool()
 
         return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
-                                   cov3D_precomp, tile_mask, self.raster_settings)
+                                   cov3D_precomp, tile_mask, self.raster_settings, theta, rho,
+                                   self.return_n_touched)
 
 
 # ------------------------------------------------------------------ scratch-buffer views

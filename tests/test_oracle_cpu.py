@@ -81,3 +81,34 @@ def test_knn_oracle_kdtree_path_equals_brute_force():
         three = knn_oracle.dist_cuda2(pts[:3])         # 2 neighbours: (d1 + d2 + FLT_MAX) / 3 stays finite
         two = knn_oracle.dist_cuda2(pts[:2])           # 1 neighbour: d1 + FLT_MAX + FLT_MAX overflows
     assert np.isfinite(three).all() and (three > 1e37).all() and np.isinf(two).all()
+
+
+def test_pose_gradient_oracle_matches_finite_differences():
+    """Extension with no reference counterpart: dL/d(rho, theta) of the oracle (autograd through the
+    per-Gaussian chain with the camera written as Exp(tau) W2C) against central differences of the
+    complete float64 forward.  A small step keeps the differences away from the compositing's
+    discontinuities (alpha / transmittance thresholds, tile rectangles)."""
+    sc = scenes.make_scene(600, 5, channels=3)
+    cam = scenes.make_camera(5, size=(64, 48))
+    W, H = cam.W, cam.H
+    bg = torch.tensor([0.1, 0.2, 0.3], dtype=torch.float64)
+    gc, gd, ga = (t.double() for t in scenes.make_pixel_grads(5, 3, H, W, normalised=False))
+    v0, p0 = cam.viewmatrix.double().reshape(-1), cam.projmatrix.double().reshape(-1)
+
+    def run(tau):
+        v, p, c = O.perturbed_camera(v0, p0, tau)
+        fw = O.forward(sc["means3D"], sc["opacities"], v, p, c, W, H, cam.tanfovx, cam.tanfovy, bg,
+                       colors_precomp=sc["colors_precomp"], scales=sc["scales"], rotations=sc["rotations"])
+        return float((fw["color"] * gc).sum() + (fw["depth"] * gd[0]).sum() + (fw["alpha"] * ga[0]).sum()), fw
+
+    _, fw = run(torch.zeros(6, dtype=torch.float64))
+    bw = O.backward(fw, sc["means3D"], cam.viewmatrix, cam.projmatrix, cam.campos, W, H, cam.tanfovx, cam.tanfovy,
+                    gc, gd, ga, scales=sc["scales"], rotations=sc["rotations"], pose=True)
+    eps = 1e-7
+    for k in range(6):
+        e = torch.zeros(6, dtype=torch.float64)
+        e[k] = eps
+        fd = (run(e)[0] - run(-e)[0]) / (2 * eps)
+        assert abs(fd - float(bw["g_tau"][k])) <= 1e-4 * abs(fd) + 1e-3, (k, fd, float(bw["g_tau"][k]))
+    # n_touched is a subset count of the blended pairs
+    assert int(fw["n_touched"].sum()) > 0 and int(fw["n_touched"].max()) <= W * H
