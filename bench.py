@@ -368,6 +368,62 @@ def run_cpu_reference(args):
             "e2e": {"value": cb["value"], "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
 
 
+def run_pose_refine(args):
+    """Secondary workload (BASELINE.json config 3; not the default bench line): query frames are
+    refined independently against a 1.2 M-Gaussian map, 12-Scenes intrinsics, frames sharded over the
+    ranks with no collective per iteration.  Metric: pose-refine iterations per second, whole job."""
+    from splatloc_b200.multiview import gather_frames, shard_range
+    from splatloc_b200.pose_refine import PoseRefiner, perturb_pose, pose_error
+    rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        import datetime
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
+    P, iters, n_frames = args.points if args.points != P_DEFAULT else 1_200_000, args.steps, args.frames * world
+    gaussians = scenes.make_scene(P, seed=0, channels=4)
+    k = scenes.SCENES12_INTRINSICS
+    ref = PoseRefiner(gaussians, k, device=dev)
+    mine = list(shard_range(n_frames, rank, world))
+    frames = []
+    for f in mine:
+        w2c_gt = scenes.make_camera(seed=500 + f, intrinsics=k).viewmatrix.transpose(0, 1).double()
+        with torch.no_grad():
+            color, depth, _, _ = ref.render(w2c_gt.to(dev))
+        frames.append((w2c_gt, perturb_pose(w2c_gt, seed=f), color.detach(), depth.detach()))
+    ref.refine(frames[0][1], frames[0][2], frames[0][3], iters=max(args.warmup, 3))   # warm-up
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    results = []
+    for w2c_gt, w2c0, color, depth in frames:
+        w2c, _ = ref.refine(w2c0, color, depth, iters=iters)
+        results.append(w2c.reshape(1, 16))
+    e1.record()
+    torch.cuda.synchronize()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    allposes = gather_frames(torch.cat(results, 0), n_frames)
+    errs = [pose_error(w.reshape(4, 4), f[0]) for w, f in zip(torch.cat(results, 0), frames)]
+    errs0 = [pose_error(f[1], f[0]) for f in frames]
+    out = {"metric": "pose-refine iters/s", "value": round(n_frames * iters / (float(ms) * 1e-3), 2), "unit": "iters/s",
+           "n_gpus": world, "steps": iters, "warmup": args.warmup, "ms_per_step": round(float(ms) / (len(mine) * iters), 4),
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "impl": "ours",
+           "config": {"workload": "scenes12_pose_refine_1200k_640x480_c4", "gaussians": P, "frames": n_frames,
+                      "iters_per_frame": iters, "gathered_poses": list(allposes.shape),
+                      "note": "extension workload: the reference has no rasterizer-based pose refinement",
+                      "mean_trans_err_m": [round(sum(e[0] for e in errs0) / len(errs0), 4), round(sum(e[0] for e in errs) / len(errs), 4)],
+                      "mean_rot_err_deg": [round(sum(e[1] for e in errs0) / len(errs0), 3), round(sum(e[1] for e in errs) / len(errs), 3)]}}
+    if world > 1:
+        dist.destroy_process_group()
+    return out if rank == 0 else None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -377,8 +433,17 @@ def main():
     ap.add_argument("--points", type=int, default=P_DEFAULT)
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", choices=["train_step", "pose_refine"], default="train_step")
+    ap.add_argument("--frames", type=int, default=4, help="pose_refine: query frames per GPU")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    if args.workload == "pose_refine":
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+        out = run_pose_refine(args)
+        if out is not None:
+            print(json.dumps(out))
+        return
 
     if args.impl == "reference":
         from oracle import ref_cuda
