@@ -76,6 +76,109 @@ __device__ __forceinline__ f3 cov2d_ewa(const f3& mean, float focal_x, float foc
     return {cov.c[0][0], cov.c[0][1], cov.c[1][1]};
 }
 
+// One Gaussian.  Returns the number of tiles it touches (0 if culled, degenerate or off-screen)
+// and its tile rectangle.
+__device__ __forceinline__ uint32_t
+preprocess_one(int idx, int D, int M, int C,
+                  const float* __restrict__ means3D,
+                  const float* __restrict__ scales,
+                  const float* __restrict__ rotations,
+                  const float* __restrict__ opacities,
+                  const float* __restrict__ shs,
+                  const float* __restrict__ cov3D_precomp,
+                  const uint8_t* __restrict__ tile_mask,
+                  const float* __restrict__ colors_precomp,
+                  const float* __restrict__ viewmatrix,
+                  const float* __restrict__ projmatrix,
+                  const float* __restrict__ cam_pos,
+                  ViewParams vp, bool prefiltered,
+                  int* __restrict__ radii,
+                  float2* __restrict__ means2D,
+                  float* __restrict__ depths,
+                  float* __restrict__ cov3Ds,
+                  float* __restrict__ rgb,
+                  uint8_t* __restrict__ clamped,
+                  float4* __restrict__ conic_opacity,
+                  uint2& rect_min, uint2& rect_max)
+{
+    // A Gaussian that leaves early keeps radius 0 / 0 tiles and is ignored downstream.
+    radii[idx] = 0;
+
+    f3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
+    f3 p_view = xform_4x3(p_orig, viewmatrix);
+    if (!prefiltered && !in_frustum_ndc(p_orig, projmatrix)) return 0;
+    if (opacities[idx] < 0.0001f) return 0;
+
+    float4 p_hom = xform_4x4(p_orig, projmatrix);
+    float p_w = 1.0f / (p_hom.w + 0.0000001f);
+    f3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
+
+    const float* cov3D;
+    if (cov3D_precomp != nullptr) {
+        cov3D = cov3D_precomp + idx * 6;
+    } else {
+        f3 s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+        float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        cov3d_from_scale_rot(s, vp.scale_modifier, q, cov3Ds + idx * 6);
+        cov3D = cov3Ds + idx * 6;
+    }
+
+    f3 cov = cov2d_ewa(p_orig, vp.focal_x, vp.focal_y, vp.tan_fovx, vp.tan_fovy, cov3D, viewmatrix);
+
+    float det = (cov.x * cov.z - cov.y * cov.y);
+    if (det <= 0.0f || cov.x <= 0.0f || cov.z <= 0.0f) {
+        radii[idx] = -1;  // degenerate footprint: pruned with zero gradients
+        return 0;
+    }
+    float det_inv = 1.f / det;
+    f3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
+
+    float mid = 0.5f * (cov.x + cov.z);
+    float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
+    float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
+    if (lambda1 <= 0.01 || lambda2 <= 0.01 || lambda1 < lambda2 || (lambda1 / lambda2) > 10000.0) {
+        radii[idx] = -1;
+        return 0;
+    }
+    float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+
+    float2 point_image = {ndc_to_pix(p_proj.x, vp.W), ndc_to_pix(p_proj.y, vp.H)};
+    uint2 rmin, rmax;
+    tile_rect(point_image.x, point_image.y, (int)my_radius, vp.grid_x, vp.grid_y, rmin, rmax);
+
+    uint32_t touched = (rmax.y - rmin.y) * (rmax.x - rmin.x);
+    if (touched == 0) return 0;  // off-screen: tiles_touched stays 0, radius stays 0
+
+    if (tile_mask != nullptr) {
+        touched = 0;
+        for (uint32_t y = rmin.y; y < rmax.y; y++)
+            for (uint32_t x = rmin.x; x < rmax.x; x++)
+                if (tile_mask[y * vp.grid_x + x]) touched += 1;
+        if (touched == 0) return 0;
+    }
+    rect_min = rmin;
+    rect_max = rmax;
+
+    conic_opacity[idx] = {conic.x, conic.y, conic.z, opacities[idx]};
+
+    if (colors_precomp == nullptr) {
+        f3 campos = {cam_pos[0], cam_pos[1], cam_pos[2]};
+        f3 result = sh_to_rgb(idx, D, M, p_orig, campos, shs, clamped);
+        rgb[idx * C + 0] = result.x;
+        rgb[idx * C + 1] = result.y;
+        rgb[idx * C + 2] = result.z;
+    }
+
+    depths[idx] = p_view.z;
+    radii[idx] = my_radius;
+    means2D[idx] = point_image;
+    return touched;
+}
+
+
+// K1.  One thread per Gaussian; afterwards the pairs of every tile are counted for the tile-bucketed
+// binning (one counter per 128-byte line).  A Gaussian covering up to 8 tiles adds its own counts;
+// one covering more (near or very flat splats cover thousands) is counted by its whole warp.
 __global__ void __launch_bounds__(256)
 preprocess_kernel(int P, int D, int M, int C,
                   const float* __restrict__ means3D,
@@ -100,89 +203,36 @@ preprocess_kernel(int P, int D, int M, int C,
                   uint32_t* __restrict__ tiles_touched,
                   uint32_t* __restrict__ tile_counts)
 {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    if (idx >= P) return;
-
-    // A Gaussian that leaves early keeps radius 0 / 0 tiles and is ignored downstream.
-    radii[idx] = 0;
-    tiles_touched[idx] = 0;
-
-    f3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
-    f3 p_view = xform_4x3(p_orig, viewmatrix);
-    if (!prefiltered && !in_frustum_ndc(p_orig, projmatrix)) return;
-    if (opacities[idx] < 0.0001f) return;
-
-    float4 p_hom = xform_4x4(p_orig, projmatrix);
-    float p_w = 1.0f / (p_hom.w + 0.0000001f);
-    f3 p_proj = {p_hom.x * p_w, p_hom.y * p_w, p_hom.z * p_w};
-
-    const float* cov3D;
-    if (cov3D_precomp != nullptr) {
-        cov3D = cov3D_precomp + idx * 6;
-    } else {
-        f3 s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
-        float4 q = reinterpret_cast<const float4*>(rotations)[idx];
-        cov3d_from_scale_rot(s, vp.scale_modifier, q, cov3Ds + idx * 6);
-        cov3D = cov3Ds + idx * 6;
+    constexpr uint32_t SOLO_MAX = 8;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
+    uint32_t touched = 0;
+    if (idx < P) {
+        touched = preprocess_one(idx, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
+                                 colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, means2D,
+                                 depths, cov3Ds, rgb, clamped, conic_opacity, rmin, rmax);
+        tiles_touched[idx] = touched;
     }
+    if (tile_counts == nullptr) return;
 
-    f3 cov = cov2d_ewa(p_orig, vp.focal_x, vp.focal_y, vp.tan_fovx, vp.tan_fovy, cov3D, viewmatrix);
-
-    float det = (cov.x * cov.z - cov.y * cov.y);
-    if (det <= 0.0f || cov.x <= 0.0f || cov.z <= 0.0f) {
-        radii[idx] = -1;  // degenerate footprint: pruned with zero gradients
-        return;
-    }
-    float det_inv = 1.f / det;
-    f3 conic = {cov.z * det_inv, -cov.y * det_inv, cov.x * det_inv};
-
-    float mid = 0.5f * (cov.x + cov.z);
-    float lambda1 = mid + sqrt(max(0.1f, mid * mid - det));
-    float lambda2 = mid - sqrt(max(0.1f, mid * mid - det));
-    if (lambda1 <= 0.01 || lambda2 <= 0.01 || lambda1 < lambda2 || (lambda1 / lambda2) > 10000.0) {
-        radii[idx] = -1;
-        return;
-    }
-    float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
-
-    float2 point_image = {ndc_to_pix(p_proj.x, vp.W), ndc_to_pix(p_proj.y, vp.H)};
-    uint2 rmin, rmax;
-    tile_rect(point_image.x, point_image.y, (int)my_radius, vp.grid_x, vp.grid_y, rmin, rmax);
-
-    uint32_t touched = (rmax.y - rmin.y) * (rmax.x - rmin.x);
-    if (touched == 0) return;  // off-screen: tiles_touched stays 0, radius stays 0
-
-    if (tile_mask != nullptr) {
-        touched = 0;
+    auto count = [&](uint32_t t) {
+        if (tile_mask == nullptr || tile_mask[t]) atomicAdd(&tile_counts[(size_t)t * TILE_COUNTER_STRIDE], 1u);
+    };
+    const uint32_t area = touched ? (rmax.x - rmin.x) * (rmax.y - rmin.y) : 0u;
+    if (area > 0 && area <= SOLO_MAX) {
         for (uint32_t y = rmin.y; y < rmax.y; y++)
-            for (uint32_t x = rmin.x; x < rmax.x; x++)
-                if (tile_mask[y * vp.grid_x + x]) touched += 1;
-        if (touched == 0) return;
+            for (uint32_t x = rmin.x; x < rmax.x; x++) count(y * vp.grid_x + x);
     }
-    tiles_touched[idx] = touched;
-
-    // Per-tile pair counts for the tile-bucketed binning (one counter per 128-byte line).
-    if (tile_counts != nullptr) {
-        for (uint32_t y = rmin.y; y < rmax.y; y++)
-            for (uint32_t x = rmin.x; x < rmax.x; x++) {
-                const uint32_t t = y * vp.grid_x + x;
-                if (tile_mask == nullptr || tile_mask[t]) atomicAdd(&tile_counts[(size_t)t * TILE_COUNTER_STRIDE], 1u);
-            }
+    unsigned big = __ballot_sync(0xffffffffu, area > SOLO_MAX);
+    while (big) {
+        const int src = __ffs(big) - 1;
+        big &= big - 1;
+        const uint32_t x0 = __shfl_sync(0xffffffffu, rmin.x, src), y0 = __shfl_sync(0xffffffffu, rmin.y, src);
+        const uint32_t w = __shfl_sync(0xffffffffu, rmax.x, src) - x0;
+        const uint32_t n = __shfl_sync(0xffffffffu, area, src);
+        for (uint32_t k = lane; k < n; k += 32) count((y0 + k / w) * vp.grid_x + x0 + k % w);
     }
-
-    conic_opacity[idx] = {conic.x, conic.y, conic.z, opacities[idx]};
-
-    if (colors_precomp == nullptr) {
-        f3 campos = {cam_pos[0], cam_pos[1], cam_pos[2]};
-        f3 result = sh_to_rgb(idx, D, M, p_orig, campos, shs, clamped);
-        rgb[idx * C + 0] = result.x;
-        rgb[idx * C + 1] = result.y;
-        rgb[idx * C + 2] = result.z;
-    }
-
-    depths[idx] = p_view.z;
-    radii[idx] = my_radius;
-    means2D[idx] = point_image;
 }
 
 __global__ void __launch_bounds__(256)
