@@ -1,23 +1,37 @@
 // splatloc_b200/csrc/blend_bwd.cu
 //
 // K7  backward alpha blending (reference: renderCUDA in
-//     cuda_rasterizer/backward.cu:1018-1209).  Same per-pixel recurrences and
-//     per-term arithmetic as the reference, walked back to front over the first
-//     n_contrib entries of the tile's list; what changes is how the 9 + C
-//     per-Gaussian partial gradients leave the CTA.
+//     cuda_rasterizer/backward.cu:1018-1209).  Same per-pixel recurrences as the
+//     reference, walked back to front over the first n_contrib entries of the
+//     tile's list; what changes is how the 9 + C per-Gaussian partial gradients
+//     are summed over pixels and leave the CTA.
 //
 //     The reference issues 9 + C global float atomics per blended
 //     (pixel, Gaussian) pair.  Here a warp owns an 8x4 pixel patch and streams
 //     the tile's PairRecords back to front on its own (blend_common.cuh; same
 //     chunked survivor pipeline as the forward, starting at the patch's largest
-//     n_contrib); for every
-//     Gaussian that at least one of its 32 pixels blends, the partials are
-//     reduced across the warp with a 16-shuffle transpose-reduction (16 values,
-//     halving the live set at each of the 5 butterfly levels) and the 9 + C sums
-//     leave the warp as one `red.global.add.f32` per value, issued by 9 + C
-//     different lanes.  Warps none of whose pixels blend the Gaussian skip it on
-//     a ballot.  Global atomic traffic drops from (9+C) per blended pixel pair
-//     to at most 8 x (9+C) per (tile, Gaussian) pair.
+//     n_contrib).  The work on a Gaussian is split in two phases with the lanes
+//     changing roles:
+//
+//     pixel phase (lane = pixel): evaluate alpha exactly as the forward did,
+//       advance the pixel's recurrences (T, accum_rec/red/rea) and reduce
+//       everything the pixel contributes to the Gaussian's gradients to two
+//       scalars,  w = alpha * T  and  a = G * dL/dalpha;  Gaussians no pixel of
+//       the patch blends are dropped on a ballot.  (w, a) of all 32 pixels go
+//       to a row of a warp-private shared tile;
+//     Gaussian phase (lane = Gaussian x half patch), once BWD_ROWS rows are
+//       filled: every gradient is linear in (w, a) with coefficients that depend
+//       only on the pixel offset (dx, dy) and on per-Gaussian constants,
+//           dL/dcolour = sum w dL/dpix      dL/ddepth  = sum w dL/dpix_depth
+//           dL/dmean2D = -o (W/2, H/2) . sum a Q d,     |.| likewise
+//           dL/dconic  = -o/2 sum a (dx^2, dx dy, dy^2) dL/dopacity = sum a
+//       so a lane walks 16 pixels of its row with plain FMAs into registers --
+//       no cross-lane reduction per Gaussian -- the two halves are combined with
+//       one shuffle per value and 9 + C `red.global.add.f32` leave per Gaussian.
+//
+//     Global atomic traffic drops from (9+C) per blended pixel pair to at most
+//     8 x (9+C) per (tile, Gaussian) pair, and the pixel sums cost ~25 instead of
+//     ~60 (shuffle butterfly) warp instructions per Gaussian.
 //
 //     Channel rule kept from the fork: channels >= 3 do not feed dL/dalpha
 //     (backward.cu:1153-1154) but do receive colour gradients.
@@ -29,51 +43,23 @@ namespace sl {
 namespace {
 
 constexpr unsigned FULL = 0xffffffffu;
+constexpr int BWD_ROWS = 16;      // Gaussians per Gaussian-phase batch (x 2 half patches = 32 lanes)
+constexpr int BWD_STRIDE = 33;    // row pitch of the (w, a) tiles in floats: conflict-free both ways
+#ifndef SL_BWD_MIN_CTAS
+#define SL_BWD_MIN_CTAS 4         // register budget 128; measured 206 / 211 / 214 us at 4 / 5 / 6 CTAs per SM
+#endif
 
-// Sum 16 per-lane values across the warp.  On return lane L holds in the result the
-// warp-wide total of value (L >> 1).
-__device__ __forceinline__ float warp_transpose_reduce16(float (&v)[16], int lane)
+__device__ __forceinline__ float lds32(uint32_t a)
 {
-    {
-        const bool up = lane & 16;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) {
-            const float send = up ? v[k] : v[k + 8];
-            const float keep = up ? v[k + 8] : v[k];
-            v[k] = keep + __shfl_xor_sync(FULL, send, 16);
-        }
-    }
-    {
-        const bool up = lane & 8;
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            const float send = up ? v[k] : v[k + 4];
-            const float keep = up ? v[k + 4] : v[k];
-            v[k] = keep + __shfl_xor_sync(FULL, send, 8);
-        }
-    }
-    {
-        const bool up = lane & 4;
-#pragma unroll
-        for (int k = 0; k < 2; ++k) {
-            const float send = up ? v[k] : v[k + 2];
-            const float keep = up ? v[k + 2] : v[k];
-            v[k] = keep + __shfl_xor_sync(FULL, send, 4);
-        }
-    }
-    {
-        const bool up = lane & 2;
-        const float send = up ? v[0] : v[1];
-        const float keep = up ? v[1] : v[0];
-        v[0] = keep + __shfl_xor_sync(FULL, send, 2);
-    }
-    return v[0] + __shfl_xor_sync(FULL, v[0], 1);
+    float v;
+    asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+    return v;
 }
 
 }  // namespace
 
 template <int C>
-__global__ void __launch_bounds__(BLEND_THREADS)
+__global__ void __launch_bounds__(BLEND_THREADS, SL_BWD_MIN_CTAS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const PairRecord* __restrict__ records, const uint8_t* __restrict__ masks,
                       int W, int H, int grid_x, const float* __restrict__ bg,
@@ -89,6 +75,11 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 {
     __shared__ PairRecord s_rec[BLEND_WARPS][BLEND_CHUNK];
     __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];
+    __shared__ float s_w[BLEND_WARPS][BWD_ROWS * BWD_STRIDE];          // alpha * T per (row, pixel)
+    __shared__ float s_a[BLEND_WARPS][BWD_ROWS * BWD_STRIDE];          // G * dL/dalpha per (row, pixel)
+    __shared__ __align__(16) float4 s_grec[BLEND_WARPS][BWD_ROWS][2];  // {x, y, Qxx, Qxy}, {Qyy, o, id, -}
+    __shared__ __align__(16) float4 s_dpix[BLEND_WARPS][32];           // dL/dpix, channels 0..3, per pixel
+    __shared__ float s_ddep[BLEND_WARPS][32];                          // dL/dpix_depth per pixel
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int tile = tile_order[blockIdx.x / BLEND_SUBS];
@@ -99,6 +90,9 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const uint32_t pix_id = (uint32_t)W * py + px;
     const float pixf_x = (float)px, pixf_y = (float)py;
     const uint32_t rec_a = smem_addr(&s_rec[warp][0]), lane_a = smem_addr(&s_lane[warp][0]);
+    const uint32_t w_a = smem_addr(&s_w[warp][0]), a_a = smem_addr(&s_a[warp][0]);
+    const uint32_t grec_a = smem_addr(&s_grec[warp][0][0]);
+    const uint32_t dpix_a = smem_addr(&s_dpix[warp][0]), ddep_a = smem_addr(&s_ddep[warp][0]);
     const unsigned lt = (1u << lane) - 1u;
 
     const uint2 range = ranges[tile];
@@ -130,27 +124,6 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const float ddelx_dx = 0.5 * W;
     const float ddely_dy = 0.5 * H;
 
-    // Which output this lane flushes after a warp reduction: value index lane >> 1.
-    //   0..C-1 colour | C depth | C+1,C+2 mean2D x,y | C+3,C+4 |mean2D| x,y |
-    //   C+5..C+7 conic xx,xy,yy | C+8 opacity
-    float* flush_base = nullptr;
-    uint32_t flush_stride = 0;
-    {
-        const int v = lane >> 1;
-        if ((lane & 1) == 0) {
-            if (v < C) { flush_base = dL_dcolor + v; flush_stride = C; }
-            else if (v == C) { flush_base = dL_ddepth; flush_stride = 1; }
-            else if (v == C + 1) { flush_base = dL_dmean2D; flush_stride = 3; }
-            else if (v == C + 2) { flush_base = dL_dmean2D + 1; flush_stride = 3; }
-            else if (v == C + 3) { flush_base = dL_dabsmean2D; flush_stride = 3; }
-            else if (v == C + 4) { flush_base = dL_dabsmean2D + 1; flush_stride = 3; }
-            else if (v == C + 5) { flush_base = dL_dconic; flush_stride = 4; }
-            else if (v == C + 6) { flush_base = dL_dconic + 1; flush_stride = 4; }
-            else if (v == C + 7) { flush_base = dL_dconic + 3; flush_stride = 4; }
-            else if (v == C + 8) { flush_base = dL_dopacity; flush_stride = 1; }
-        }
-    }
-
     // Entries at list positions >= the patch's largest n_contrib are never blended by it:
     // the walk starts there (positions are 0-based here, like the reference's `contributor`).
     int warp_last = last_contributor;
@@ -158,10 +131,85 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     for (int o = 16; o > 0; o >>= 1) warp_last = max(warp_last, __shfl_xor_sync(FULL, warp_last, o));
     if (warp_last == 0) return;
 
-    // Back-propagate through the `cnt` records parked in the warp's buffer; `top_pos` is the list
-    // position of the chunk's entry 0 (entries run towards the front of the list).
-    auto backprop_parked = [&](int cnt, int top_pos) {
-        for (int k = 0; k < cnt; ++k) {
+    // per-pixel image gradients, read by every lane in the Gaussian phase
+    s_dpix[warp][lane] = make_float4(dL_dpixel[0], dL_dpixel[1], dL_dpixel[2], C > 3 ? dL_dpixel[C - 1] : 0.f);
+    s_ddep[warp][lane] = dL_dpixel_depth;
+
+    // Gaussian phase over the n (<= BWD_ROWS) filled rows.  Lane = (row k, half patch h): 16 pixels each.
+    auto gaussian_phase = [&](int n) {
+        __syncwarp();
+        const int k = lane & (BWD_ROWS - 1), half = lane >> 4;
+        const float4 ga = lds128(grec_a + (uint32_t)k * 32u), gb = lds128(grec_a + (uint32_t)k * 32u + 16u);
+        const float gx = ga.x, gy = ga.y, qxx = ga.z, qxy = ga.w, qyy = gb.x;
+        const uint32_t row_w = w_a + (uint32_t)(k * BWD_STRIDE + half * 16) * 4u;
+        const uint32_t row_a = a_a + (uint32_t)(k * BWD_STRIDE + half * 16) * 4u;
+        const uint32_t dp = dpix_a + (uint32_t)half * 256u, dd = ddep_a + (uint32_t)half * 64u;
+        const float x0f = pg.wx0, y0f = pg.wy0 + (float)(2 * half);
+        float sc[C];
+#pragma unroll
+        for (int ch = 0; ch < C; ++ch) sc[ch] = 0.f;
+        float sd = 0.f, sgx = 0.f, sgy = 0.f, sax = 0.f, say = 0.f, sxx = 0.f, sxy = 0.f, syy = 0.f, sa = 0.f;
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+            const float w = lds32(row_w + 4u * j), a = lds32(row_a + 4u * j);
+            const float4 dpx = lds128(dp + 16u * j);
+            const float ddp = lds32(dd + 4u * j);
+            const float dx = gx - (x0f + (float)(j & 7));
+            const float dy = gy - (y0f + (float)(j >> 3));
+            const float c4[4] = {dpx.x, dpx.y, dpx.z, dpx.w};
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) sc[ch] = fmaf(w, c4[ch], sc[ch]);
+            sd = fmaf(w, ddp, sd);
+            const float adx = a * dx, ady = a * dy;
+            sxx = fmaf(adx, dx, sxx);
+            sxy = fmaf(adx, dy, sxy);
+            syy = fmaf(ady, dy, syy);
+            const float ex = fmaf(adx, qxx, ady * qxy);    // a (Q d).x
+            const float ey = fmaf(ady, qyy, adx * qxy);    // a (Q d).y
+            sgx += ex;
+            sgy += ey;
+            sax += fabsf(ex);
+            say += fabsf(ey);
+            sa += a;
+        }
+#pragma unroll
+        for (int ch = 0; ch < C; ++ch) sc[ch] += __shfl_xor_sync(FULL, sc[ch], 16);
+        sd += __shfl_xor_sync(FULL, sd, 16);
+        sgx += __shfl_xor_sync(FULL, sgx, 16);
+        sgy += __shfl_xor_sync(FULL, sgy, 16);
+        sax += __shfl_xor_sync(FULL, sax, 16);
+        say += __shfl_xor_sync(FULL, say, 16);
+        sxx += __shfl_xor_sync(FULL, sxx, 16);
+        sxy += __shfl_xor_sync(FULL, sxy, 16);
+        syy += __shfl_xor_sync(FULL, syy, 16);
+        sa += __shfl_xor_sync(FULL, sa, 16);
+        if (half == 0 && k < n) {
+            const float o = gb.y;
+            const uint32_t gid = (uint32_t)__float_as_int(gb.z);
+#pragma unroll
+            for (int ch = 0; ch < C; ++ch) atomicAdd(dL_dcolor + gid * C + ch, sc[ch]);
+            atomicAdd(dL_ddepth + gid, sd);
+            const float kx = o * ddelx_dx, ky = o * ddely_dy, kc = -0.5f * o;
+            atomicAdd(dL_dmean2D + gid * 3u, -kx * sgx);
+            atomicAdd(dL_dmean2D + gid * 3u + 1u, -ky * sgy);
+            atomicAdd(dL_dabsmean2D + gid * 3u, kx * sax);
+            atomicAdd(dL_dabsmean2D + gid * 3u + 1u, ky * say);
+            atomicAdd(dL_dconic + gid * 4u, kc * sxx);
+            atomicAdd(dL_dconic + gid * 4u + 1u, kc * sxy);
+            atomicAdd(dL_dconic + gid * 4u + 3u, kc * syy);
+            atomicAdd(dL_dopacity + gid, sa);
+        }
+        __syncwarp();
+    };
+
+    int rows = 0;
+
+    // Pixel phase over the `cnt` records parked in the warp's buffer; `top_pos` is the list position
+    // of the chunk's entry 0 (entries run towards the front of the list).
+    auto pixel_phase = [&](int cnt, int top_pos, bool final) {
+        for (int k = 0;; ++k) {
+            bool flush = final && rows > 0;      // after the last record: whatever rows are left
+            if (k < cnt) {
             const uint32_t ra = rec_a + (uint32_t)k * (uint32_t)sizeof(PairRecord);
             const int pos = top_pos - (int)lds_u8(lane_a + k);
             const float4 xyd = lds128(ra);
@@ -177,10 +225,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
             const bool blend = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
             if (!__any_sync(FULL, blend)) continue;
 
-            float v[16];
-#pragma unroll
-            for (int q = 0; q < 16; ++q) v[q] = 0.f;
-
+            float w = 0.f, a = 0.f;
             if (blend) {
                 // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha); 1 - alpha is in
                 // [0.01, 1], so MUFU.RCP plus one Newton step is within an ulp of the reference's division
@@ -189,7 +234,7 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(om));
                 inv = __fmaf_rn(__fmaf_rn(-om, inv, 1.f), inv, inv);
                 T = T * inv;
-                const float w = alpha * T;
+                w = alpha * T;
                 float dL_dalpha = 0.0f;
                 const float4 f = lds128(ra + 32);
                 const float c4[4] = {f.x, f.y, f.z, f.w};
@@ -198,15 +243,12 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                     const float c = c4[ch];
                     accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
                     last_color[ch] = c;
-                    const float dL_dchannel = dL_dpixel[ch];
-                    if (ch <= 2) dL_dalpha += (c - accum_rec[ch]) * dL_dchannel;   // channels >= 3 are masked out
-                    v[ch] = w * dL_dchannel;
+                    if (ch <= 2) dL_dalpha += (c - accum_rec[ch]) * dL_dpixel[ch];   // channels >= 3 are masked out
                 }
                 const float dep = xyd.z;
                 accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
                 last_depth = dep;
                 dL_dalpha += (dep - accum_red) * dL_dpixel_depth;
-                v[C] = w * dL_dpixel_depth;
 
                 accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
                 dL_dalpha += (1 - accum_rea) * dL_dpixel_alpha;
@@ -214,29 +256,21 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 dL_dalpha *= T;
                 last_alpha = alpha;
                 dL_dalpha += neg_Tfinal_bg * inv;
-
-                const float dL_dG = co.w * dL_dalpha;
-                const float gdx = G * dx;
-                const float gdy = G * dy;
-                const float dG_ddelx = -gdx * co.x - gdy * co.y;
-                const float dG_ddely = -gdy * co.z - gdx * co.y;
-                const float gx = dL_dG * dG_ddelx * ddelx_dx;
-                const float gy = dL_dG * dG_ddely * ddely_dy;
-                v[C + 1] = gx;
-                v[C + 2] = gy;
-                v[C + 3] = fabsf(gx);
-                v[C + 4] = fabsf(gy);
-                v[C + 5] = -0.5f * gdx * dx * dL_dG;
-                v[C + 6] = -0.5f * gdx * dy * dL_dG;
-                v[C + 7] = -0.5f * gdy * dy * dL_dG;
-                v[C + 8] = G * dL_dalpha;
+                a = G * dL_dalpha;
             }
-
-            const float total_v = warp_transpose_reduce16(v, lane);
-            if (flush_base != nullptr) {
-                const int gid = __float_as_int(xyd.w);
-                atomicAdd(flush_base + (uint32_t)gid * (uint32_t)flush_stride, total_v);
+            s_w[warp][rows * BWD_STRIDE + lane] = w;
+            s_a[warp][rows * BWD_STRIDE + lane] = a;
+            if (lane == 0) {
+                s_grec[warp][rows][0] = make_float4(xyd.x, xyd.y, co.x, co.y);
+                s_grec[warp][rows][1] = make_float4(co.z, co.w, xyd.w, 0.f);
             }
+            flush = (++rows == BWD_ROWS);
+            }
+            if (flush) {
+                gaussian_phase(rows);
+                rows = 0;
+            }
+            if (k >= cnt) break;
         }
     };
 
@@ -244,7 +278,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     const int start = lo + warp_last - 1;                 // global index of the first entry to visit
     uint32_t m_next = (start - lane >= lo) ? masks[start - lane] : 0u;
 
-    for (int t = start; t >= lo; t -= BLEND_CHUNK) {
+    for (int t = start;; t -= BLEND_CHUNK) {
+        const bool more = t >= lo;                        // one extra pass drains the last parked chunk
         const uint32_t m = m_next;
         const bool bit = (t - lane >= lo) && ((m >> patch) & 1u);
         float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = r0, r2 = r0;
@@ -256,7 +291,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         }
         m_next = (t - BLEND_CHUNK - lane >= lo) ? masks[t - BLEND_CHUNK - lane] : 0u;
 
-        backprop_parked(parked, parked_top);
+        pixel_phase(parked, parked_top, !more);
+        if (!more) break;
 
         __syncwarp();
         const unsigned b = __ballot_sync(0xffffffffu, bit);
@@ -272,7 +308,6 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
         parked = __popc(b);
         parked_top = t - lo;
     }
-    backprop_parked(parked, parked_top);
 }
 
 int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
