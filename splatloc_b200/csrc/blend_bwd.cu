@@ -102,24 +102,24 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     float T = T_final;
     const int last_contributor = inside ? n_contrib[pix_id] : 0;
 
-    float accum_rec[C];
-    float last_color[C];
     float dL_dpixel[C];
 #pragma unroll
-    for (int ch = 0; ch < C; ++ch) {
-        accum_rec[ch] = 0.f;
-        last_color[ch] = 0.f;
-        dL_dpixel[ch] = inside ? dL_dpix[(size_t)ch * H * W + pix_id] : 0.f;
-    }
-    float accum_red = 0.f, accum_rea = 0.f;
+    for (int ch = 0; ch < C; ++ch) dL_dpixel[ch] = inside ? dL_dpix[(size_t)ch * H * W + pix_id] : 0.f;
     const float dL_dpixel_depth = inside ? dL_dpix_depth[pix_id] : 0.f;
     const float dL_dpixel_alpha = inside ? dL_dpix_alpha[pix_id] : 0.f;
-    float last_alpha = 0.f, last_depth = 0.f;
 
+    // The reference carries one recurrence per output (accum_rec[ch], accum_red, accum_rea:
+    // backward.cu:1139-1170), each the blend of everything behind the current Gaussian normalised
+    // by the transmittance after it, and forms dL/dalpha = T sum_ch (c_ch - accum_ch) dL/dpix_ch
+    // - T_final / (1 - alpha) bg . dL/dpix.  With  d_i = dL/dpix . (colour_i, depth_i, 1)  and
+    // T_i accum_i = (sum_{j behind i} w_j c_j) / (1 - alpha_i)  that is the same as
+    //     dL/dalpha_i = T_i d_i - behind_i / (1 - alpha_i),
+    //     behind_i = T_final bg . dL/dpix + sum_{j behind i} w_j d_j,   w_j = alpha_j T_j,
+    // one scalar recurrence with the same cancellation structure (both terms scale with T_i).
     float bg_dot_dpixel = 0.f;
 #pragma unroll
     for (int ch = 0; ch < C; ++ch) bg_dot_dpixel += bg[ch] * dL_dpixel[ch];
-    const float neg_Tfinal_bg = -T_final * bg_dot_dpixel;
+    float behind = T_final * bg_dot_dpixel;
 
     const float ddelx_dx = 0.5 * W;
     const float ddely_dy = 0.5 * H;
@@ -235,27 +235,14 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                 inv = __fmaf_rn(__fmaf_rn(-om, inv, 1.f), inv, inv);
                 T = T * inv;
                 w = alpha * T;
-                float dL_dalpha = 0.0f;
+                // d = dL/dpix . (colour, depth, 1) of this Gaussian; channels >= 3 are masked out
                 const float4 f = lds128(ra + 32);
-                const float c4[4] = {f.x, f.y, f.z, f.w};
-#pragma unroll
-                for (int ch = 0; ch < C; ++ch) {
-                    const float c = c4[ch];
-                    accum_rec[ch] = last_alpha * last_color[ch] + (1.f - last_alpha) * accum_rec[ch];
-                    last_color[ch] = c;
-                    if (ch <= 2) dL_dalpha += (c - accum_rec[ch]) * dL_dpixel[ch];   // channels >= 3 are masked out
-                }
-                const float dep = xyd.z;
-                accum_red = last_alpha * last_depth + (1.f - last_alpha) * accum_red;
-                last_depth = dep;
-                dL_dalpha += (dep - accum_red) * dL_dpixel_depth;
-
-                accum_rea = last_alpha + (1.f - last_alpha) * accum_rea;
-                dL_dalpha += (1 - accum_rea) * dL_dpixel_alpha;
-
-                dL_dalpha *= T;
-                last_alpha = alpha;
-                dL_dalpha += neg_Tfinal_bg * inv;
+                float d = fmaf(xyd.z, dL_dpixel_depth, dL_dpixel_alpha);
+                d = fmaf(f.x, dL_dpixel[0], d);
+                d = fmaf(f.y, dL_dpixel[1], d);
+                d = fmaf(f.z, dL_dpixel[2], d);
+                const float dL_dalpha = fmaf(T, d, -(behind * inv));
+                behind = fmaf(w, d, behind);
                 a = G * dL_dalpha;
             }
             s_w[warp][rows * BWD_STRIDE + lane] = w;
