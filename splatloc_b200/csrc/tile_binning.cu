@@ -22,6 +22,10 @@
 
 namespace sl {
 
+#ifndef SL_SORT_MIN_CTAS
+#define SL_SORT_MIN_CTAS 3        // resident 256-thread sort CTAs per SM the register budget is set for
+#endif
+
 // ------------------------------------------------------------------ 2. per-tile scan (one CTA)
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
@@ -160,6 +164,35 @@ scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __r
 // element w * 32E + 32 r + l.  Compare-exchange distances below 32 are warp shuffles, distances
 // 32 .. 16E stay inside a thread's registers, and only the few distances that cross warps go
 // through shared memory (6 of the 55 steps at N = 1024) -- the rest of the network needs no barrier.
+// take_min ? min(a, b) : max(a, b) for distinct 64-bit keys: one compare, one predicate xor, one
+// select (the C++ form compiles to both < and > compares and two predicated selects per half).
+__device__ __forceinline__ unsigned long long pick64(unsigned long long a, unsigned long long b, int take_max)
+{
+    unsigned long long r;
+    asm("{\n\t.reg .pred p, q;\n\t"
+        "setp.lt.u64 p, %1, %2;\n\t"
+        "setp.ne.s32 q, %3, 0;\n\t"
+        "xor.pred p, p, q;\n\t"
+        "selp.b64 %0, %1, %2, p;\n\t}"
+        : "=l"(r) : "l"(a), "l"(b), "r"(take_max));
+    return r;
+}
+
+// (x, y) -> (min, max), or (max, min) when `descending`: one compare for both selects.
+__device__ __forceinline__ void order64(unsigned long long& x, unsigned long long& y, int descending)
+{
+    unsigned long long lo, hi;
+    asm("{\n\t.reg .pred p, q;\n\t"
+        "setp.gt.u64 p, %2, %3;\n\t"
+        "setp.ne.s32 q, %4, 0;\n\t"
+        "xor.pred p, p, q;\n\t"
+        "selp.b64 %0, %3, %2, p;\n\t"
+        "selp.b64 %1, %2, %3, p;\n\t}"
+        : "=&l"(lo), "=l"(hi) : "l"(x), "l"(y), "r"(descending));
+    x = lo;
+    y = hi;
+}
+
 template <int E, int THREADS>
 __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], unsigned long long* smem, int tid)
 {
@@ -179,8 +212,7 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
                 for (int r = 0; r < E; ++r) {
                     const int g = wbase + 32 * r;
                     const unsigned long long other = smem[g ^ j];
-                    const bool take_min = ((g & j) == 0) == ((g & k) == 0);
-                    key[r] = ((key[r] < other) == take_min) ? key[r] : other;
+                    key[r] = pick64(key[r], other, ((g & j) == 0) != ((g & k) == 0));
                 }
             } else if (j >= 32) {
 #pragma unroll
@@ -189,12 +221,7 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
 #pragma unroll
                         for (int r = 0; r < E; ++r) {
                             if ((r & dr) == 0) {
-                                const bool up = ((wbase + 32 * r) & k) == 0;
-                                const unsigned long long x = key[r], y = key[r | dr];
-                                if ((x > y) == up) {
-                                    key[r] = y;
-                                    key[r | dr] = x;
-                                }
+                                order64(key[r], key[r | dr], ((wbase + 32 * r) & k) != 0);
                             }
                         }
                     }
@@ -203,8 +230,7 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
 #pragma unroll
                 for (int r = 0; r < E; ++r) {
                     const unsigned long long other = __shfl_xor_sync(0xffffffffu, key[r], j);
-                    const bool take_min = ((lane & j) == 0) == (((wbase + 32 * r) & k) == 0);
-                    key[r] = ((key[r] < other) == take_min) ? key[r] : other;
+                    key[r] = pick64(key[r], other, ((lane & j) == 0) != (((wbase + 32 * r) & k) == 0));
                 }
             }
         }
@@ -265,7 +291,7 @@ __device__ __forceinline__ void sort_and_emit_tile(
 // One CTA per tile of `tiles[blockIdx.x]`; handles segments with min_len < n <= 16 * THREADS and
 // picks the network size from n.
 template <int C, int THREADS>
-__global__ void __launch_bounds__(THREADS)
+__global__ void __launch_bounds__(THREADS, THREADS == 256 ? SL_SORT_MIN_CTAS : 1)
 tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tiles, int grid_x, uint32_t min_len,
                  const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
