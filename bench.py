@@ -103,8 +103,11 @@ def algorithmic_bytes(P, V, R, N, Tn, C, M_sh=0):
     return {
         "preprocess": P * (44 + 12 * M_sh) + 8 * P + 52 * V,
         "tile_scan": 8 * Tn + 8 * Tn,
-        "emit_pairs": 16 * V + 4 * P + 12 * R,
-        "sort_pairs": 24 * R + (28 + 4 * C) * R + (33 + 4 * C) * R,
+        # depth-ordered emit (default): compaction + 4 digit passes over V (depth bits, id) entries, then
+        # every pair written once (sorted key, id, their "unsorted" twins, 48-byte record, mask byte)
+        "depth_sort": 8 * P + 12 * V + 4 * 24 * V,
+        "emit_pairs": (4 + 12 + 28 + 4 * C) * V + (24 + 49) * R,
+        "sort_pairs": 24 * R + (28 + 4 * C) * R + (33 + 4 * C) * R,        # tile-bucket / radix paths only
         "pair_records": (12 + 28 + 4 * C) * R + (33 + 4 * C) * R,     # radix fallback only
         "blend_forward": (33 + 4 * C) * R + (12 + 4 * C) * N,
         "blend_backward": (33 + 4 * C) * R + (16 + 4 * C) * N + (36 + 4 * C) * R,
@@ -328,15 +331,15 @@ def run_gpu(args, impl):
         for name, (tot, calls) in prof.items():
             if calls:
                 ms = tot / calls
-                stages[name] = {"ms": round(ms, 4), "alg_MB": round(alg[name] / 1e6, 2),
-                                "GBps": round(alg[name] / (ms * 1e-3) / 1e9, 1)}
+                stages[name] = {"ms": round(ms, 4), "alg_MB": round(alg.get(name, 0) / 1e6, 2),
+                                "GBps": round(alg.get(name, 0) / (ms * 1e-3) / 1e9, 1)}
         top = max(stages, key=lambda k: stages[k]["ms"])
         ach = stages[top]["GBps"]
         out["roofline"] = {"kernel": top, "bound": "hbm", "achieved": ach, "peak": peak, "unit": "GB/s",
                            "frac": round(ach / peak, 4), "traffic": measured_traffic(top), "peak_source": how,
                            "note": "blend kernels are FP32/SFU/atomic-bound; see profiles/ for pipe utilisation",
-                           "step_alg_MB": round(sum(alg.values()) / 1e6, 1),
-                           "step_frac": round(sum(alg.values()) / (ms_step * 1e-3) / 1e9 / peak, 4)}
+                           "step_alg_MB": round(sum(alg.get(n, 0) for n in stages) / 1e6, 1),
+                           "step_frac": round(sum(alg.get(n, 0) for n in stages) / (ms_step * 1e-3) / 1e9 / peak, 4)}
         out["stages"] = stages
         if rank == 0 and not args.no_cpu_baseline:
             out["cpu_baseline"] = cpu_baseline(budget_s=args.cpu_budget)

@@ -185,10 +185,14 @@ int sl_knn_static(int P, const float* points, float* mean_dists, void* stream);
 /* Number of this library's kernels launched by the process so far. */
 long long sl_launch_count(void);
 
-/* Binning strategy of sl_forward: 0 (default) = per-tile counting sort + in-CTA segment sort,
- * falling back to the global radix sort only when a tile's list is too long for one CTA;
- * 1 = always the global radix sort (the reference's pipeline shape).  Both produce identical
- * sorted lists; the switch exists so tests can cover the fallback. */
+/* Binning strategy of sl_forward (no reference counterpart; all strategies produce the reference's
+ * sorted lists bit for bit, the switch exists so tests can cover each of them):
+ *   0 = the library's default (currently 2);
+ *   1 = prefix sum, Gaussian-major emit and one global radix sort (the reference's pipeline shape);
+ *   2 = pairs scattered into per-tile segments, each segment sorted in shared memory by one CTA
+ *       (falls back to 1 when a tile's list is too long for one CTA);
+ *   3 = the visible Gaussians are sorted once by depth and every pair is written straight to its
+ *       final list position (falls back to 2 when the tile grid is too large). */
 void sl_set_binning_mode(int mode);
 
 /* Per-stage device timing with CUDA events recorded on the caller's stream

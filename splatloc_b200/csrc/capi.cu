@@ -46,12 +46,12 @@ int check_stage(bool debug, cudaStream_t stream, const char* what)
 // (sl_profile_enable / sl_profile_read).  Off by default; when off the hot path
 // records nothing.
 enum Stage {
-    ST_PREPROCESS = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD, ST_PREPROCESS_BWD,
-    ST_COUNT
+    ST_PREPROCESS = 0, ST_SCAN, ST_DEPTH_SORT, ST_EMIT, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD,
+    ST_PREPROCESS_BWD, ST_COUNT
 };
 static const char* const kStageNames[ST_COUNT] = {
-    "preprocess", "tile_scan", "emit_pairs", "sort_pairs", "pair_records", "blend_forward", "blend_backward",
-    "preprocess_backward"};
+    "preprocess", "tile_scan", "depth_sort", "emit_pairs", "sort_pairs", "pair_records", "blend_forward",
+    "blend_backward", "preprocess_backward"};
 
 struct Profiler {
     bool enabled = false;
@@ -63,7 +63,8 @@ struct Profiler {
 };
 static Profiler g_prof;
 static std::atomic<long long> g_launches{0};
-static std::atomic<int> g_force_radix{0};   // sl_set_binning_mode(): 1 = always take the radix-sort path
+static std::atomic<int> g_binning_mode{0};  // sl_set_binning_mode(): 0 default, 1 radix sort, 2 tile buckets, 3 ordered emit
+constexpr int kDefaultBinningMode = 2;
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -144,7 +145,10 @@ void sl_profile_enable(int on)
     }
 }
 
-void sl_set_binning_mode(int mode) { g_force_radix.store(mode == 1 ? 1 : 0, std::memory_order_relaxed); }
+void sl_set_binning_mode(int mode)
+{
+    g_binning_mode.store(mode >= 1 && mode <= 3 ? mode : 0, std::memory_order_relaxed);
+}
 
 int sl_profile_stage_count(void) { return ST_COUNT; }
 
@@ -274,7 +278,8 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
 
     {
         StageTimer t(ST_SCAN, stream);
-        rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles, stream);
+        rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles,
+                              geom.block_vis, (int)geom.pre_blocks, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile scan");
@@ -289,15 +294,44 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     }
     const int R = (int)info.num_pairs;
 
-    char* bin_chunk = binning_alloc(binning_ctx, sl_binning_bytes(R));
+    // Binning, three interchangeable paths that produce the same sorted arrays:
+    //   3 depth-ordered emit (ordered_binning.cu): sort the visible Gaussians once, write
+    //     every pair straight to its final list position;
+    //   2 tile buckets (tile_binning.cu): scatter pairs into their tile's segment, sort each segment
+    //     in shared memory -- taken when the tile grid is too large for the ordered emit's masks;
+    //   1 the reference's own pipeline shape -- prefix sum, Gaussian-major emit, global radix sort --
+    //     taken when a tile's list exceeds what one CTA sorts in shared memory.
+    int mode = g_binning_mode.load(std::memory_order_relaxed);
+    if (mode == 0) mode = kDefaultBinningMode;
+    const int V = (int)info.num_visible;
+    const int ordered_block = ordered_block_size(n_tiles);
+    const bool ordered_path = mode == 3 && ordered_block != 0;
+    const bool radix_path = !ordered_path && (info.n_huge > 0 || mode == 1);
+
+    const size_t bin_bytes = ordered_path ? required_bytes<BinningState>((size_t)R, (size_t)V, (size_t)n_tiles,
+                                                                         (size_t)ordered_block)
+                                          : sl_binning_bytes(R);
+    char* bin_chunk = binning_alloc(binning_ctx, bin_bytes);
     if (!bin_chunk) { set_error("sl_forward: binning allocation failed"); return SL_ERR_ALLOC; }
-    BinningState bin = BinningState::from_chunk(bin_chunk, R);
+    BinningState bin = ordered_path ? BinningState::from_chunk(bin_chunk, R, V, n_tiles, ordered_block)
+                                    : BinningState::from_chunk(bin_chunk, R);
     const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
 
-    // Default: tile-bucketed binning (tile_binning.cu).  Fallback when a tile's list exceeds what one
-    // CTA sorts in shared memory (or on request, for tests): the reference's own pipeline shape --
-    // prefix sum, Gaussian-major emit, global radix sort -- which produces the same sorted arrays.
-    const bool radix_path = info.n_huge > 0 || g_force_radix.load(std::memory_order_relaxed) != 0;
+    if (R > 0 && ordered_path) {
+        {
+            StageTimer t(ST_DEPTH_SORT, stream);
+            rc = launch_depth_sort(P, V, geom, bin, stream);
+        }
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "depth sort");
+        {
+            StageTimer t(ST_EMIT, stream);
+            rc = launch_ordered_emit(V, C, ordered_block, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges,
+                                     features, bin, stream);
+        }
+        if (rc) return rc;
+        SL_STAGE(dbg, stream, "ordered emit");
+    } else
     if (R > 0 && !radix_path) {
         {
             StageTimer t(ST_EMIT, stream);

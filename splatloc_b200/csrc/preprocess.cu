@@ -179,7 +179,7 @@ preprocess_one(int idx, int D, int M, int C,
 // K1.  One thread per Gaussian; afterwards the pairs of every tile are counted for the tile-bucketed
 // binning (one counter per 128-byte line).  A Gaussian covering up to 8 tiles adds its own counts;
 // one covering more (near or very flat splats cover thousands) is counted by its whole warp.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(PREPROCESS_THREADS)
 preprocess_kernel(int P, int D, int M, int C,
                   const float* __restrict__ means3D,
                   const float* __restrict__ scales,
@@ -201,7 +201,8 @@ preprocess_kernel(int P, int D, int M, int C,
                   uint8_t* __restrict__ clamped,
                   float4* __restrict__ conic_opacity,
                   uint32_t* __restrict__ tiles_touched,
-                  uint32_t* __restrict__ tile_counts)
+                  uint32_t* __restrict__ tile_counts,
+                  uint32_t* __restrict__ block_vis)
 {
     constexpr uint32_t SOLO_MAX = 8;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -215,6 +216,10 @@ preprocess_kernel(int P, int D, int M, int C,
         tiles_touched[idx] = touched;
     }
     if (tile_counts == nullptr) return;
+
+    // Gaussians of this CTA that reach the binning stage (their stable compaction is ordered_binning.cu's input)
+    const int n_vis = __syncthreads_count(touched != 0);
+    if (threadIdx.x == 0) block_vis[blockIdx.x] = (uint32_t)n_vis;
 
     auto count = [&](uint32_t t) {
         if (tile_mask == nullptr || tile_mask[t]) atomicAdd(&tile_counts[(size_t)t * TILE_COUNTER_STRIDE], 1u);
@@ -252,10 +257,10 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
                       uint32_t* tile_counts, cudaStream_t stream)
 {
-    preprocess_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
+    preprocess_kernel<<<ceil_div(P, PREPROCESS_THREADS), PREPROCESS_THREADS, 0, stream>>>(
         P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
         colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, g.means2D, g.depths,
-        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts); count_launch();
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts, g.block_vis); count_launch();
     return 0;
 }
 

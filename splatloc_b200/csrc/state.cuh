@@ -22,12 +22,17 @@ constexpr int TILE_COUNTER_STRIDE = 32;      // u32 words between per-tile count
 constexpr int TILE_SORT_SMALL = 4096;        // pairs a 256-thread CTA sorts (16 keys per thread, 32 KB of smem)
 constexpr int TILE_SORT_LARGE = 16384;       // pairs a 1024-thread CTA sorts in 128 KB of shared memory
 
-// What the host reads back after the per-tile scan (one 16-byte copy).
+constexpr int PREPROCESS_THREADS = 256;      // CTA size of preprocess (and of the visible-Gaussian compaction)
+constexpr int ORDERED_MASK_BYTES = 160 * 1024;  // shared memory the ordered emit spends on its (warp, tile) masks
+
+// What the host reads back after the per-tile scan (one 32-byte copy).
 struct BinInfo {
     uint32_t num_pairs;      // R
     uint32_t n_large;        // tiles with more than TILE_SORT_SMALL pairs
     uint32_t n_huge;         // tiles with more than TILE_SORT_LARGE pairs (-> radix-sort fallback)
     uint32_t max_pairs;      // longest tile list
+    uint32_t num_visible;    // V: Gaussians that touch at least one tile
+    uint32_t pad[3];
 };
 
 template <typename T>
@@ -52,7 +57,9 @@ struct GeomState {
     // --- own scratch ---
     unsigned long long* scan_desc;  // [scan_blocks] decoupled look-back descriptors
     uint32_t* counters;             // [8] dynamic block tickets etc.
+    uint32_t* block_vis;            // [pre_blocks] visible Gaussians per preprocess CTA, then their exclusive scan
     size_t scan_blocks;
+    size_t pre_blocks;
 
     static GeomState from_chunk(char*& chunk, size_t P)
     {
@@ -69,6 +76,8 @@ struct GeomState {
         g.scan_blocks = (P + SCAN_ITEMS_PER_BLOCK - 1) / SCAN_ITEMS_PER_BLOCK;
         carve(chunk, g.scan_desc, g.scan_blocks + 1);
         carve(chunk, g.counters, 8);
+        g.pre_blocks = (P + PREPROCESS_THREADS - 1) / PREPROCESS_THREADS;
+        carve(chunk, g.block_vis, g.pre_blocks + 1);
         return g;
     }
 };
@@ -138,8 +147,18 @@ struct BinningState {
     PairRecord* records;     // [R] per sorted pair: everything the blend kernels read, gathered once
     uint8_t* masks;          // [R] bit w: the pair can reach the w-th 8x4 patch of its tile
     SortScratch sort;
+    // --- depth-ordered emit (ordered_binning.cu); present when the chunk was sized with V > 0 ---
+    uint64_t* vis_keys_in;   // [V] depth bits of the visible Gaussians in id order (sort input)
+    uint32_t* vis_ids_in;    // [V] their ids
+    uint64_t* vis_keys;      // [V] the same, sorted
+    uint32_t* vis_ids;       // [V] ids in (depth bits, id) order
+    uint16_t* block_hist;    // [rows * Tn] pairs of each block of sorted Gaussians in each tile
+    uint32_t* block_base;    // [rows * Tn] list position of the block's first pair in each tile
+    SortScratch vis_sort;
+    size_t rows;
 
-    static BinningState from_chunk(char*& chunk, size_t R)
+    // `V`, `Tn`, `block`: visible Gaussians, tiles and Gaussians per ordered-emit CTA (0: no ordered emit)
+    static BinningState from_chunk(char*& chunk, size_t R, size_t V = 0, size_t Tn = 0, size_t block = 0)
     {
         BinningState b;
         carve(chunk, b.point_list, R);
@@ -149,6 +168,24 @@ struct BinningState {
         carve(chunk, b.records, R);
         carve(chunk, b.masks, R + 64);   // slack: the blend kernels prefetch one 32-entry chunk ahead
         b.sort = SortScratch::from_chunk(chunk, R);
+        b.rows = block ? (V + block - 1) / block : 0;
+        if (V != 0 && block != 0) {
+            carve(chunk, b.vis_keys_in, V);
+            carve(chunk, b.vis_ids_in, V);
+            carve(chunk, b.vis_keys, V);
+            carve(chunk, b.vis_ids, V);
+            carve(chunk, b.block_hist, b.rows * Tn);
+            carve(chunk, b.block_base, b.rows * Tn);
+            b.vis_sort = SortScratch::from_chunk(chunk, V);
+        } else {
+            b.vis_keys_in = nullptr;
+            b.vis_ids_in = nullptr;
+            b.vis_keys = nullptr;
+            b.vis_ids = nullptr;
+            b.block_hist = nullptr;
+            b.block_base = nullptr;
+            b.vis_sort = SortScratch();
+        }
         return b;
     }
 };

@@ -29,13 +29,44 @@ namespace sl {
 // ------------------------------------------------------------------ 2. per-tile scan (one CTA)
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
-                 uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles)
+                 uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles,
+                 uint32_t* block_vis, int n_blocks)
 {
     constexpr int NT = 1024;
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_hist[NT];
     __shared__ uint32_t s_carry, s_max, s_large, s_huge;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    if (blockIdx.x == 1) {
+        // second CTA, in parallel: exclusive scan (in place) of the visible-Gaussian counts of the
+        // preprocess CTAs -- where each of them compacts its Gaussians to (ordered_binning.cu)
+        if (tid == 0) s_carry = 0;
+        __syncthreads();
+        for (int base = 0; base < n_blocks; base += NT) {
+            const int b = base + tid;
+            const uint32_t c = (b < n_blocks) ? block_vis[b] : 0u;
+            uint32_t incl = c;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
+                if (lane >= o) incl += v;
+            }
+            if (lane == 31) s_warp[warp] = incl;
+            __syncthreads();
+            uint32_t off = s_carry;
+            for (int w = 0; w < warp; ++w) off += s_warp[w];
+            if (b < n_blocks) block_vis[b] = off + incl - c;
+            __syncthreads();
+            if (tid == NT - 1) s_carry = off + incl;
+            __syncthreads();
+        }
+        if (tid == 0) {
+            block_vis[n_blocks] = s_carry;
+            info->num_visible = s_carry;
+        }
+        return;
+    }
     if (tid == 0) { s_carry = 0; s_max = 0; s_large = 0; s_huge = 0; }
     s_hist[tid] = 0;
     __syncthreads();
@@ -316,9 +347,10 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 }
 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, cudaStream_t stream)
+                     int n_tiles, uint32_t* block_vis, int n_blocks, cudaStream_t stream)
 {
-    tile_scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles);
+    tile_scan_kernel<<<2, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles, block_vis,
+                                             n_blocks);
     count_launch();
     return 0;
 }

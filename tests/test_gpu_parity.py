@@ -36,11 +36,14 @@ CASES = [
 ]
 
 
-@pytest.fixture(params=["tile_binning", "radix_fallback"])
+BINNING_MODES = {"ordered_emit": 3, "radix_fallback": 1, "tile_buckets": 2}
+
+
+@pytest.fixture(params=list(BINNING_MODES))
 def binning_mode(request):
-    """Both binning strategies of sl_forward must give the reference's sorted lists."""
+    """All three binning strategies of sl_forward must give the reference's sorted lists."""
     from splatloc_b200 import _capi
-    _capi.load().sl_set_binning_mode(1 if request.param == "radix_fallback" else 0)
+    _capi.load().sl_set_binning_mode(BINNING_MODES[request.param])
     yield request.param
     _capi.load().sl_set_binning_mode(0)
 
@@ -58,10 +61,21 @@ def test_matches_reference_cuda(case, binning_mode):
     assert not bad, "\n".join(bad)
 
 
-def test_long_tile_lists_take_the_large_and_fallback_sorts():
-    """Many Gaussians stacked on a few tiles: segments beyond 4096 pairs use the 1024-thread segment
-    sort, beyond 16384 the radix fallback; all must still match the reference bit for bit."""
+@pytest.mark.parametrize("mode", ["ordered_emit", "tile_buckets"])
+def test_long_tile_lists(mode):
+    """Many Gaussians stacked on a few tiles.  Tile buckets: segments beyond 4096 pairs use the
+    1024-thread segment sort, beyond 16384 the radix fallback; the ordered emit has no such limits.
+    All must still match the reference bit for bit."""
+    from splatloc_b200 import _capi
     ref, ours = _ref(), _ours()
+    _capi.load().sl_set_binning_mode(BINNING_MODES[mode])
+    try:
+        _long_tile_lists(ref, ours)
+    finally:
+        _capi.load().sl_set_binning_mode(0)
+
+
+def _long_tile_lists(ref, ours):
     for P, spread in ((60000, 0.15), (120000, 0.05)):
         d = H.scene_inputs(P, 21, size=(128, 96))
         cam = d["cam"]
