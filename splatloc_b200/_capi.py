@@ -104,6 +104,8 @@ def load() -> C.CDLL:
             fn = getattr(lib, name)  # AttributeError if the symbol is not exported
             fn.restype = res
             fn.argtypes = args
+        if os.environ.get("SPLATLOC_B200_BINNING"):      # tuning experiments: see sl_set_binning_mode
+            lib.sl_set_binning_mode(int(os.environ["SPLATLOC_B200_BINNING"]))
         _lib = lib
     return _lib
 

@@ -9,7 +9,7 @@
 // The mask byte holds the axis-aligned bounding box test of that ellipse, half-widths
 //     hx = sqrt(2 ln(255 o) * Qyy / det Q),  hy = sqrt(2 ln(255 o) * Qxx / det Q);
 // refined, for the patches the box touches, by the exact minimum of d^T Q d over the patch
-// rectangle (patch_reached) -- everything padded by 0.2-0.4 % + 0.05 px and >= 2e-5 in power
+// rectangle (patch_mask) -- everything padded by 0.2-0.4 % + 0.05 px and >= 2e-5 in power
 // units, far more than any float32 / ex2.approx error.  A warp reads 32 mask bytes per step, ballots the survivors, fetches only their records
 // into a warp-private shared buffer (while it blends the previous chunk) and evaluates those with
 // the reference's exact arithmetic.  The test is conservative and list positions are kept, so
@@ -53,31 +53,10 @@ __device__ __forceinline__ PatchGeom patch_geom(int tile, int grid_x, int warp, 
     return g;
 }
 
-// Exact refinement of the reach mask for ONE patch: can d^T Q d drop to `limit` (2 ln(255 o), padded)
-// anywhere on the patch rectangle [wx0, wx1] x [wy0, wy1]?  The form is convex with its minimum at the Gaussian's centre,
-// so if the centre is outside the rectangle the minimum lies on an edge facing the centre (at most
-// two), where it is the clamped vertex of a 1-D parabola.
-__device__ __forceinline__ bool patch_reached(float cx, float cy, const float4& co, float limit,
-                                              float wx0, float wx1, float wy0, float wy1)
-{
-    const float x0 = wx0 - 0.05f - cx, x1 = wx1 + 0.05f - cx;   // rectangle relative to the centre
-    const float y0 = wy0 - 0.05f - cy, y1 = wy1 + 0.05f - cy;
-    const bool in_x = x0 <= 0.f && x1 >= 0.f, in_y = y0 <= 0.f && y1 >= 0.f;
-    if (in_x && in_y) return true;
-    float best = 3.4e38f;
-    if (!in_x) {
-        const float u = x0 > 0.f ? x0 : x1;                                  // the edge facing the centre
-        const float v = fminf(fmaxf(__fdividef(-co.y * u, co.z), y0), y1);
-        best = co.x * u * u + 2.0f * co.y * u * v + co.z * v * v;
-    }
-    if (!in_y) {
-        const float v = y0 > 0.f ? y0 : y1;
-        const float u = fminf(fmaxf(__fdividef(-co.y * v, co.x), x0), x1);
-        best = fminf(best, co.x * u * u + 2.0f * co.y * u * v + co.z * v * v);
-    }
-    return !(best > limit);
-}
-
+// Exact refinement of the reach mask: can d^T Q d drop to `limit` (2 ln(255 o), padded) anywhere on
+// a patch rectangle (padded by 0.05 px)?  The form is convex with its minimum at the Gaussian's
+// centre, so if the centre is outside the rectangle the minimum lies on an edge facing the centre (at
+// most two), where it is the clamped vertex of a 1-D parabola.
 // Bit w of the result: the Gaussian may reach a pixel of warp w's 8x4 patch.
 __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4& co, int tile_x0, int tile_y0)
 {
@@ -108,17 +87,44 @@ __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4&
     for (int r = 0; r < 4; ++r)
         if (rows & (1u << r)) m |= cols << (2 * r);
 
-    // exact test for the patches the box touches (typically 2-4 of them)
+    if (m == 0u) return 0u;
+
+    // Exact test for all 8 patches in straight-line code: the per-column and
+    // per-row terms are shared, and there is no data-dependent loop for the warp to diverge on.
     const float limit = t2 * 1.004f + 1e-4f;
-    const float ux = cx - (float)tile_x0, uy = cy - (float)tile_y0;
-    uint32_t cand = m;
-    while (cand) {
-        const int w = __ffs(cand) - 1;
-        cand &= cand - 1;
-        const float wx0 = (float)((w & 1) * 8), wy0 = (float)((w >> 1) * 4);
-        if (!patch_reached(ux, uy, co, limit, wx0, wx0 + 7.f, wy0, wy0 + 3.f)) m &= ~(1u << w);
+    const float ux = cx - (float)tile_x0, uy = cy - (float)tile_y0;      // centre in tile coordinates
+    const float rcx = __frcp_rn(co.x), rcz = __frcp_rn(co.z);
+    const float two_b = 2.0f * co.y;
+    float cx0[2], cx1[2], ue[2], tx[2], ax[2];
+    bool in_x[2];
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        cx0[c] = (float)(8 * c) - 0.05f - ux;             // patch column relative to the centre
+        cx1[c] = cx0[c] + 7.1f;
+        in_x[c] = cx0[c] <= 0.f && cx1[c] >= 0.f;
+        ue[c] = cx0[c] > 0.f ? cx0[c] : cx1[c];           // the vertical edge facing the centre
+        tx[c] = -co.y * ue[c] * rcz;                      // vertex of the parabola along that edge
+        ax[c] = co.x * ue[c] * ue[c];
     }
-    return m;
+    uint32_t exact = 0u;
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+        const float y0 = (float)(4 * r) - 0.05f - uy, y1 = y0 + 3.1f;
+        const bool in_y = y0 <= 0.f && y1 >= 0.f;
+        const float ve = y0 > 0.f ? y0 : y1;              // the horizontal edge facing the centre
+        const float ty = -co.y * ve * rcx;
+        const float cy2 = co.z * ve * ve;
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+            const float v = fminf(fmaxf(tx[c], y0), y1);
+            const float best_x = in_x[c] ? 3.4e38f : ax[c] + (two_b * ue[c] + co.z * v) * v;
+            const float u = fminf(fmaxf(ty, cx0[c]), cx1[c]);
+            const float best_y = in_y ? 3.4e38f : cy2 + (two_b * ve + co.x * u) * u;
+            const bool reached = (in_x[c] && in_y) || !(fminf(best_x, best_y) > limit);
+            exact |= (reached ? 1u : 0u) << (2 * r + c);
+        }
+    }
+    return m & exact;
 }
 
 // Shared-space (32-bit) addressing done by hand: with generic pointers the compiler re-derives the

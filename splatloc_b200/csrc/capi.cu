@@ -266,12 +266,16 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     // Per-tile pair counters (one 128-byte line each), filled by preprocess.
     SL_CUDA(cudaMemsetAsync(img.tile_counts, 0, (size_t)n_tiles * TILE_COUNTER_STRIDE * sizeof(uint32_t), stream),
             "tile counter memset");
+    SL_CUDA(cudaMemsetAsync(img.bin_info, 0, sizeof(BinInfo), stream), "bin info memset");
+    int mode = g_binning_mode.load(std::memory_order_relaxed);
+    if (mode == 0) mode = kDefaultBinningMode;
+    const bool want_ordered = mode == 3 && ordered_supported(n_tiles);
     int rc;
     {
         StageTimer t(ST_PREPROCESS, stream);
         rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
                                colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered != 0, radii,
-                               geom, img.tile_counts, stream);
+                               geom, img.tile_counts, want_ordered ? &img.bin_info->rect_tiles : nullptr, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess");
@@ -279,7 +283,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     {
         StageTimer t(ST_SCAN, stream);
         rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles,
-                              geom.block_vis, (int)geom.pre_blocks, stream);
+                              want_ordered ? geom.block_vis : nullptr, (int)geom.pre_blocks, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile scan");
@@ -301,32 +305,30 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     //     in shared memory -- taken when the tile grid is too large for the ordered emit's masks;
     //   1 the reference's own pipeline shape -- prefix sum, Gaussian-major emit, global radix sort --
     //     taken when a tile's list exceeds what one CTA sorts in shared memory.
-    int mode = g_binning_mode.load(std::memory_order_relaxed);
-    if (mode == 0) mode = kDefaultBinningMode;
     const int V = (int)info.num_visible;
-    const int ordered_block = ordered_block_size(n_tiles);
-    const bool ordered_path = mode == 3 && ordered_block != 0;
+    const bool ordered_path = want_ordered;
+    const size_t ordered_blocks = ordered_path ? (size_t)ordered_rows(info.rect_tiles) : 0;
     const bool radix_path = !ordered_path && (info.n_huge > 0 || mode == 1);
 
     const size_t bin_bytes = ordered_path ? required_bytes<BinningState>((size_t)R, (size_t)V, (size_t)n_tiles,
-                                                                         (size_t)ordered_block)
+                                                                         ordered_blocks)
                                           : sl_binning_bytes(R);
     char* bin_chunk = binning_alloc(binning_ctx, bin_bytes);
     if (!bin_chunk) { set_error("sl_forward: binning allocation failed"); return SL_ERR_ALLOC; }
-    BinningState bin = ordered_path ? BinningState::from_chunk(bin_chunk, R, V, n_tiles, ordered_block)
+    BinningState bin = ordered_path ? BinningState::from_chunk(bin_chunk, R, V, n_tiles, ordered_blocks)
                                     : BinningState::from_chunk(bin_chunk, R);
     const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
 
     if (R > 0 && ordered_path) {
         {
             StageTimer t(ST_DEPTH_SORT, stream);
-            rc = launch_depth_sort(P, V, geom, bin, stream);
+            rc = launch_depth_sort(P, V, geom, radii, vp.grid_x, vp.grid_y, bin, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "depth sort");
         {
             StageTimer t(ST_EMIT, stream);
-            rc = launch_ordered_emit(V, C, ordered_block, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges,
+            rc = launch_ordered_emit(V, info.rect_tiles, C, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges,
                                      features, bin, stream);
         }
         if (rc) return rc;

@@ -20,7 +20,7 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
                       const float* viewmatrix, const float* projmatrix, const float* cam_pos,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      uint32_t* tile_counts, cudaStream_t stream);
+                      uint32_t* tile_counts, uint32_t* rect_tiles, cudaStream_t stream);
 
 // K10: frustum visibility (reference: checkFrustum, rasterizer_impl.cu:54-66).
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -50,19 +50,25 @@ int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint
                      uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
                      uint8_t* masks, cudaStream_t stream);
 
-// ---- depth-ordered emit (ordered_binning.cu; the default): the visible Gaussians are sorted ONCE by
-// depth and every pair is then written straight to its final list position -- no per-tile sort.
-// `block` = Gaussians per CTA (a multiple of 32, <= 256) chosen by ordered_block_size().
-int ordered_block_size(int n_tiles);   // 0: too many tiles for the shared-memory masks, use another path
-int launch_depth_sort(int P, int V, const GeomState& g, BinningState& bin, cudaStream_t stream);
-int launch_ordered_emit(int V, int C, int block, const GeomState& g, const int* radii, const uint8_t* tile_mask,
-                        int grid_x, int grid_y, const uint2* ranges, const float* features, BinningState& bin,
-                        cudaStream_t stream);
+// ---- depth-ordered emit (ordered_binning.cu): the visible Gaussians are sorted ONCE by depth and every
+// pair is then written straight to its final list position -- no per-tile sort.
+bool ordered_supported(int n_tiles);      // false: too many tiles for the per-CTA counters, use another path
+int ordered_rows(size_t rect_tiles);      // pair blocks (CTAs) for `rect_tiles` rectangle tiles
+int launch_depth_sort(int P, int V, const GeomState& g, const int* radii, int grid_x, int grid_y, BinningState& bin,
+                      cudaStream_t stream);
+int launch_ordered_emit(int V, size_t rect_tiles, int C, const GeomState& g, const int* radii,
+                        const uint8_t* tile_mask, int grid_x, int grid_y, const uint2* ranges, const float* features,
+                        BinningState& bin, cudaStream_t stream);
 
 // K4: stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit);
 // result in (keys_out, vals_out); the inputs are preserved.
+// `histograms_ready`: the caller ran sort_prepare() and accumulated the digit histograms itself.
+int sort_prepare(SortScratch& sc, int n, int end_bit, cudaStream_t stream);
 int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
-                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream);
+                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream,
+                      bool histograms_ready = false);
+int launch_inclusive_scan_keys_hi(const uint64_t* keys, uint32_t* out, int n, unsigned long long* desc,
+                                  uint32_t* ticket, cudaStream_t stream);
 
 // Gather, once per frame, everything the blend kernels read for each sorted pair (PairRecord) plus
 // the per-patch reach mask, and write the per-tile ranges (reference: identifyTileRanges).

@@ -202,7 +202,8 @@ preprocess_kernel(int P, int D, int M, int C,
                   float4* __restrict__ conic_opacity,
                   uint32_t* __restrict__ tiles_touched,
                   uint32_t* __restrict__ tile_counts,
-                  uint32_t* __restrict__ block_vis)
+                  uint32_t* __restrict__ block_vis,
+                  uint32_t* __restrict__ rect_tiles)
 {
     constexpr uint32_t SOLO_MAX = 8;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -217,14 +218,22 @@ preprocess_kernel(int P, int D, int M, int C,
     }
     if (tile_counts == nullptr) return;
 
-    // Gaussians of this CTA that reach the binning stage (their stable compaction is ordered_binning.cu's input)
-    const int n_vis = __syncthreads_count(touched != 0);
-    if (threadIdx.x == 0) block_vis[blockIdx.x] = (uint32_t)n_vis;
+    if (block_vis != nullptr) {
+        // depth-ordered emit only: Gaussians of this CTA that reach the binning stage (their stable
+        // compaction is ordered_binning.cu's input)
+        const int n_vis = __syncthreads_count(touched != 0);
+        if (threadIdx.x == 0) block_vis[blockIdx.x] = (uint32_t)n_vis;
+    }
 
     auto count = [&](uint32_t t) {
         if (tile_mask == nullptr || tile_mask[t]) atomicAdd(&tile_counts[(size_t)t * TILE_COUNTER_STRIDE], 1u);
     };
     const uint32_t area = touched ? (rmax.x - rmin.x) * (rmax.y - rmin.y) : 0u;
+    if (block_vis != nullptr) {
+        // all tiles inside the visible Gaussians' rectangles (the pair count unless a tile mask removes some)
+        const uint32_t warp_tiles = __reduce_add_sync(0xffffffffu, area);
+        if (lane == 0 && warp_tiles != 0) atomicAdd(rect_tiles, warp_tiles);
+    }
     if (area > 0 && area <= SOLO_MAX) {
         for (uint32_t y = rmin.y; y < rmax.y; y++)
             for (uint32_t x = rmin.x; x < rmax.x; x++) count(y * vp.grid_x + x);
@@ -255,12 +264,12 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
                       const float* viewmatrix, const float* projmatrix, const float* cam_pos,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      uint32_t* tile_counts, cudaStream_t stream)
+                      uint32_t* tile_counts, uint32_t* rect_tiles, cudaStream_t stream)
 {
     preprocess_kernel<<<ceil_div(P, PREPROCESS_THREADS), PREPROCESS_THREADS, 0, stream>>>(
         P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
         colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, g.means2D, g.depths,
-        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts, g.block_vis); count_launch();
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts, rect_tiles != nullptr ? g.block_vis : nullptr, rect_tiles); count_launch();
     return 0;
 }
 

@@ -52,6 +52,9 @@ __device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v, int lane)
 constexpr unsigned long long SCAN_AGG = 1ull << 32;
 constexpr unsigned long long SCAN_INCL = 2ull << 32;
 
+// KEYS_HI: the addends are the high 32-bit words of an array of u64 (the tile counts that ride on
+// the depth keys of ordered_binning.cu) instead of a plain u32 array.
+template <bool KEYS_HI>
 __global__ void __launch_bounds__(256)
 inclusive_scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
                       unsigned long long* desc, uint32_t* ticket)
@@ -67,7 +70,11 @@ inclusive_scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ ou
     const int base = bid * SCAN_ITEMS_PER_BLOCK + tid * 16;
 
     uint32_t v[16];
-    if (base + 16 <= n && (reinterpret_cast<uintptr_t>(in) & 15) == 0) {
+    if (KEYS_HI) {
+        const uint2* src = reinterpret_cast<const uint2*>(in);
+#pragma unroll
+        for (int k = 0; k < 16; ++k) v[k] = (base + k < n) ? src[base + k].y : 0u;
+    } else if (base + 16 <= n && (reinterpret_cast<uintptr_t>(in) & 15) == 0) {
         const uint4* src = reinterpret_cast<const uint4*>(in + base);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -190,12 +197,13 @@ sort_scan_hist_kernel(uint32_t* __restrict__ hist)
 
 constexpr int SORT_THREADS = 256;
 constexpr int SORT_WARPS = SORT_THREADS / 32;
-constexpr int SORT_ITEMS = SORT_ITEMS_PER_BLOCK / SORT_THREADS;  // 16 per thread
-constexpr int SORT_WARP_ITEMS = SORT_ITEMS * 32;                 // 512 per warp
 
+// A CTA ranks SORT_ITEMS keys per thread: 16 (4096 per CTA) for large inputs, 4 (1024 per CTA) for
+// small ones, where a pass is bounded by the latency of one CTA rather than by bandwidth.
+template <int SORT_ITEMS>
 struct SortSmem {
-    uint64_t keys[SORT_ITEMS_PER_BLOCK];
-    uint32_t vals[SORT_ITEMS_PER_BLOCK];
+    uint64_t keys[SORT_ITEMS * SORT_THREADS];
+    uint32_t vals[SORT_ITEMS * SORT_THREADS];
     uint32_t warp_hist[SORT_WARPS][SORT_RADIX];
     uint32_t bin_excl[SORT_RADIX];
     uint32_t bin_gbase[SORT_RADIX];
@@ -203,13 +211,16 @@ struct SortSmem {
     uint32_t bid;
 };
 
+template <int SORT_ITEMS>
 __global__ void __launch_bounds__(SORT_THREADS)
 sort_pass_kernel(const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ vals_out, int n, int shift,
                  const uint32_t* __restrict__ digit_base, uint32_t* lookback, uint32_t* ticket)
 {
+    constexpr int SORT_ITEMS_PER_BLOCK = SORT_ITEMS * SORT_THREADS;
+    constexpr int SORT_WARP_ITEMS = SORT_ITEMS * 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    SortSmem& s = *reinterpret_cast<SortSmem*>(smem_raw);
+    SortSmem<SORT_ITEMS>& s = *reinterpret_cast<SortSmem<SORT_ITEMS>*>(smem_raw);
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     if (tid == 0) s.bid = atomicAdd(ticket, 1u);
@@ -336,7 +347,19 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned lon
     const int blocks = ceil_div(n, SCAN_ITEMS_PER_BLOCK);
     SL_CUDA(cudaMemsetAsync(desc, 0, (size_t)(blocks + 1) * sizeof(unsigned long long), stream), "scan memset");
     SL_CUDA(cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream), "scan memset");
-    inclusive_scan_kernel<<<blocks, 256, 0, stream>>>(in, out, n, desc, ticket); count_launch();
+    inclusive_scan_kernel<false><<<blocks, 256, 0, stream>>>(in, out, n, desc, ticket); count_launch();
+    return 0;
+}
+
+int launch_inclusive_scan_keys_hi(const uint64_t* keys, uint32_t* out, int n, unsigned long long* desc,
+                                  uint32_t* ticket, cudaStream_t stream)
+{
+    const int blocks = ceil_div(n, SCAN_ITEMS_PER_BLOCK);
+    SL_CUDA(cudaMemsetAsync(desc, 0, (size_t)(blocks + 1) * sizeof(unsigned long long), stream), "scan memset");
+    SL_CUDA(cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream), "scan memset");
+    inclusive_scan_kernel<true><<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(keys), out, n, desc,
+                                                            ticket);
+    count_launch();
     return 0;
 }
 
@@ -347,23 +370,13 @@ size_t SortScratch::bytes(size_t n)
     return reinterpret_cast<size_t>(p) + 128;
 }
 
-int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
-                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream)
+template <int ITEMS>
+static int sort_passes(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out, uint32_t* vals_out,
+                       SortScratch& sc, int n, int passes, cudaStream_t stream)
 {
-    if (n <= 0) return 0;
-    const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
-    if (passes < 1 || passes > SORT_MAX_PASSES) {
-        set_error("sort: %d key bits need 1..%d digit places", end_bit, SORT_MAX_PASSES);
-        return -3;
-    }
-    SL_CUDA(cudaFuncSetAttribute(sort_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int)sizeof(SortSmem)), "sort smem attribute");
-    SL_CUDA(cudaMemsetAsync(sc.histograms, 0, sc.zero_bytes, stream), "sort memset");
-    const int hist_blocks = min(ceil_div(n, 256 * 8), 148 * 8);
-    sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, /*aggregate_from=*/3, sc.histograms); count_launch();
-    sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(sc.histograms); count_launch();
-
-    const int blocks = (int)sc.sort_blocks;
+    SL_CUDA(cudaFuncSetAttribute(sort_pass_kernel<ITEMS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int)sizeof(SortSmem<ITEMS>)), "sort smem attribute");
+    const int blocks = ceil_div(n, ITEMS * SORT_THREADS);
     const uint64_t* kin = keys_in;
     const uint32_t* vin = vals_in;
     for (int p = 0; p < passes; ++p) {
@@ -372,13 +385,46 @@ int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
         const bool to_final = ((passes - 1 - p) % 2) == 0;
         uint64_t* kout = to_final ? keys_out : sc.keys_tmp;
         uint32_t* vout = to_final ? vals_out : sc.vals_tmp;
-        sort_pass_kernel<<<blocks, SORT_THREADS, sizeof(SortSmem), stream>>>(
+        sort_pass_kernel<ITEMS><<<blocks, SORT_THREADS, sizeof(SortSmem<ITEMS>), stream>>>(
             kin, vin, kout, vout, n, p * SORT_RADIX_BITS, sc.histograms + p * SORT_RADIX,
             sc.lookback + (size_t)p * blocks * SORT_RADIX, sc.tickets + p); count_launch();
         kin = kout;
         vin = vout;
     }
     return 0;
+}
+
+int sort_prepare(SortScratch& sc, int n, int end_bit, cudaStream_t stream)
+{
+    const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+    if (passes < 1 || passes > SORT_MAX_PASSES) {
+        set_error("sort: %d key bits need 1..%d digit places", end_bit, SORT_MAX_PASSES);
+        return -3;
+    }
+    // histograms | tickets | look-back words of the digit places in use
+    const int blocks = ceil_div(n, sort_items_per_block(n));
+    const size_t bytes = (size_t)(reinterpret_cast<char*>(sc.lookback) - reinterpret_cast<char*>(sc.histograms)) +
+                         (size_t)passes * blocks * SORT_RADIX * sizeof(uint32_t);
+    SL_CUDA(cudaMemsetAsync(sc.histograms, 0, bytes, stream), "sort memset");
+    return 0;
+}
+
+int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream,
+                      bool histograms_ready)
+{
+    if (n <= 0) return 0;
+    const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
+    if (!histograms_ready) {
+        const int rc = sort_prepare(sc, n, end_bit, stream);
+        if (rc) return rc;
+        const int hist_blocks = min(ceil_div(n, 256 * 8), 148 * 8);
+        sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, /*aggregate_from=*/3, sc.histograms); count_launch();
+    }
+    sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(sc.histograms); count_launch();
+    if (sort_items_per_block(n) == SORT_ITEMS_PER_BLOCK)
+        return sort_passes<SORT_ITEMS_PER_BLOCK / SORT_THREADS>(keys_in, vals_in, keys_out, vals_out, sc, n, passes, stream);
+    return sort_passes<SORT_SMALL_ITEMS_PER_BLOCK / SORT_THREADS>(keys_in, vals_in, keys_out, vals_out, sc, n, passes, stream);
 }
 
 }  // namespace sl

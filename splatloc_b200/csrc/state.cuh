@@ -15,6 +15,12 @@ namespace sl {
 
 constexpr int SCAN_ITEMS_PER_BLOCK = 4096;   // 256 threads x 16 items
 constexpr int SORT_ITEMS_PER_BLOCK = 4096;   // 256 threads x 16 keys
+constexpr int SORT_SMALL_ITEMS_PER_BLOCK = 1024;   // 256 threads x 4 keys: inputs below SORT_SMALL_LIMIT
+constexpr int SORT_SMALL_LIMIT = 1 << 20;
+__host__ __device__ inline int sort_items_per_block(size_t n)
+{
+    return n < (size_t)SORT_SMALL_LIMIT ? SORT_SMALL_ITEMS_PER_BLOCK : SORT_ITEMS_PER_BLOCK;
+}
 constexpr int SORT_RADIX_BITS = 8;
 constexpr int SORT_RADIX = 1 << SORT_RADIX_BITS;
 constexpr int SORT_MAX_PASSES = 8;
@@ -23,7 +29,6 @@ constexpr int TILE_SORT_SMALL = 4096;        // pairs a 256-thread CTA sorts (16
 constexpr int TILE_SORT_LARGE = 16384;       // pairs a 1024-thread CTA sorts in 128 KB of shared memory
 
 constexpr int PREPROCESS_THREADS = 256;      // CTA size of preprocess (and of the visible-Gaussian compaction)
-constexpr int ORDERED_MASK_BYTES = 160 * 1024;  // shared memory the ordered emit spends on its (warp, tile) masks
 
 // What the host reads back after the per-tile scan (one 32-byte copy).
 struct BinInfo {
@@ -32,7 +37,8 @@ struct BinInfo {
     uint32_t n_huge;         // tiles with more than TILE_SORT_LARGE pairs (-> radix-sort fallback)
     uint32_t max_pairs;      // longest tile list
     uint32_t num_visible;    // V: Gaussians that touch at least one tile
-    uint32_t pad[3];
+    uint32_t rect_tiles;     // A: tiles inside their rectangles (= R unless a tile mask removes some)
+    uint32_t pad[2];
 };
 
 template <typename T>
@@ -116,22 +122,20 @@ struct SortScratch {
     uint64_t* keys_tmp;      // [n] ping-pong
     uint32_t* vals_tmp;      // [n]
     uint32_t* histograms;    // [SORT_MAX_PASSES * 256] global digit histograms
-    uint32_t* lookback;      // [SORT_MAX_PASSES * sort_blocks * 256]
     uint32_t* tickets;       // [SORT_MAX_PASSES] dynamic block ids
+    uint32_t* lookback;      // [SORT_MAX_PASSES * sort_blocks * 256]; zeroed per sort, with the two above
     size_t sort_blocks;
-    size_t zero_bytes;       // bytes from `histograms` that must be zeroed per sort
 
     static SortScratch from_chunk(char*& chunk, size_t n)
     {
         SortScratch b;
         carve(chunk, b.keys_tmp, n);
         carve(chunk, b.vals_tmp, n);
-        b.sort_blocks = (n + SORT_ITEMS_PER_BLOCK - 1) / SORT_ITEMS_PER_BLOCK;
+        const size_t per_block = (size_t)sort_items_per_block(n);
+        b.sort_blocks = (n + per_block - 1) / per_block;
         carve(chunk, b.histograms, (size_t)SORT_MAX_PASSES * SORT_RADIX);
-        char* zero_begin = reinterpret_cast<char*>(b.histograms);
-        carve(chunk, b.lookback, (size_t)SORT_MAX_PASSES * b.sort_blocks * SORT_RADIX, 4);
         carve(chunk, b.tickets, SORT_MAX_PASSES, 4);
-        b.zero_bytes = (size_t)(chunk - zero_begin);
+        carve(chunk, b.lookback, (size_t)SORT_MAX_PASSES * b.sort_blocks * SORT_RADIX, 4);
         return b;
     }
     static size_t bytes(size_t n);
@@ -152,13 +156,14 @@ struct BinningState {
     uint32_t* vis_ids_in;    // [V] their ids
     uint64_t* vis_keys;      // [V] the same, sorted
     uint32_t* vis_ids;       // [V] ids in (depth bits, id) order
-    uint16_t* block_hist;    // [rows * Tn] pairs of each block of sorted Gaussians in each tile
+    uint32_t* pair_incl;     // [V] inclusive prefix sum of their tile counts: pair indices, Gaussian-major
+    uint16_t* block_hist;    // [rows * Tn] pairs of each 2048-pair block in each tile
     uint32_t* block_base;    // [rows * Tn] list position of the block's first pair in each tile
     SortScratch vis_sort;
     size_t rows;
 
-    // `V`, `Tn`, `block`: visible Gaussians, tiles and Gaussians per ordered-emit CTA (0: no ordered emit)
-    static BinningState from_chunk(char*& chunk, size_t R, size_t V = 0, size_t Tn = 0, size_t block = 0)
+    // `V`, `Tn`, `rows`: visible Gaussians, tiles and pair blocks of the ordered emit (0: not used)
+    static BinningState from_chunk(char*& chunk, size_t R, size_t V = 0, size_t Tn = 0, size_t rows = 0)
     {
         BinningState b;
         carve(chunk, b.point_list, R);
@@ -168,12 +173,13 @@ struct BinningState {
         carve(chunk, b.records, R);
         carve(chunk, b.masks, R + 64);   // slack: the blend kernels prefetch one 32-entry chunk ahead
         b.sort = SortScratch::from_chunk(chunk, R);
-        b.rows = block ? (V + block - 1) / block : 0;
-        if (V != 0 && block != 0) {
+        b.rows = rows;
+        if (V != 0) {
             carve(chunk, b.vis_keys_in, V);
             carve(chunk, b.vis_ids_in, V);
             carve(chunk, b.vis_keys, V);
             carve(chunk, b.vis_ids, V);
+            carve(chunk, b.pair_incl, V);
             carve(chunk, b.block_hist, b.rows * Tn);
             carve(chunk, b.block_base, b.rows * Tn);
             b.vis_sort = SortScratch::from_chunk(chunk, V);
@@ -182,6 +188,7 @@ struct BinningState {
             b.vis_ids_in = nullptr;
             b.vis_keys = nullptr;
             b.vis_ids = nullptr;
+            b.pair_incl = nullptr;
             b.block_hist = nullptr;
             b.block_base = nullptr;
             b.vis_sort = SortScratch();

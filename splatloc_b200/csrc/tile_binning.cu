@@ -349,8 +349,9 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
                      int n_tiles, uint32_t* block_vis, int n_blocks, cudaStream_t stream)
 {
-    tile_scan_kernel<<<2, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles, block_vis,
-                                             n_blocks);
+    // the second CTA (offsets for the depth-ordered emit) only when that path is selected
+    tile_scan_kernel<<<block_vis != nullptr ? 2 : 1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info,
+                                                                        n_tiles, block_vis, n_blocks);
     count_launch();
     return 0;
 }
