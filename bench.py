@@ -190,8 +190,13 @@ def run_gpu(args, impl):
     leaves = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "colors_precomp", "scales", "rotations")}
     means2D = torch.zeros_like(leaves["means3D"], requires_grad=True)
     cam_host = [(c.viewmatrix.pin_memory(), c.projmatrix.pin_memory(), c.campos.pin_memory()) for c in cams_host]
-    cam_dev = (torch.empty(4, 4, device=dev), torch.empty(4, 4, device=dev), torch.empty(3, device=dev))
-    g_dev = (torch.empty(C, H, W, device=dev), torch.empty(1, H, W, device=dev), torch.empty(1, H, W, device=dev))
+    cam_packed = [torch.cat([t.reshape(-1) for t in c]).pin_memory() for c in cam_host]   # 16 + 16 + 3 floats
+    cam_pack = torch.empty(35, device=dev)
+    cam_dev = (cam_pack[:16].view(4, 4), cam_pack[16:32].view(4, 4), cam_pack[32:35])
+    # upstream gradients travel as one (C + 2, H, W) block: [dL/dcolour | dL/ddepth | dL/dalpha]
+    grads_packed = [torch.cat(g, 0).pin_memory() for g in grads_host]
+    g_pack = torch.empty(C + 2, H, W, device=dev)
+    g_dev = (g_pack[:C], g_pack[C:C + 1], g_pack[C + 1:])
     img_host = (torch.empty(C, H, W).pin_memory(), torch.empty(1, H, W).pin_memory(), torch.empty(1, H, W).pin_memory())
     h2d = sum(t.numel() * 4 for t in cam_dev) + sum(t.numel() * 4 for t in g_dev)
     d2h = sum(t.numel() * 4 for t in img_host)
@@ -204,12 +209,10 @@ def run_gpu(args, impl):
         images leave while the backward runs; everything still completes inside the timed step."""
         k = i % N_CAMERAS
         main = torch.cuda.current_stream(dev)
-        for dst, src in zip(cam_dev, cam_host[k]):
-            dst.copy_(src, non_blocking=True)
+        cam_pack.copy_(cam_packed[k], non_blocking=True)
         copy_stream.wait_stream(main)                  # previous step's consumers of g_dev / img_host are done
         with torch.cuda.stream(copy_stream):
-            for dst, src in zip(g_dev, grads_host[k]):
-                dst.copy_(src, non_blocking=True)
+            g_pack.copy_(grads_packed[k], non_blocking=True)
             ev_grads.record(copy_stream)
         c = cams_host[k]
         rs = Settings(H, W, c.tanfovx, c.tanfovy, bg, 1.0, cam_dev[0], cam_dev[1], 0, cam_dev[2], False, False)

@@ -10,6 +10,7 @@ memory and the current stream only; all computation is in libsplatloc_b200.so.
 from __future__ import annotations
 
 import ctypes as C
+import threading
 
 import torch
 
@@ -39,17 +40,52 @@ def _stream(device) -> int:
 
 class _Chunk:
     """A growable byte tensor handed to the library as an allocation callback
-    (the reference's resizeFunctional, rasterize_points.cu:27-33)."""
+    (the reference's resizeFunctional, rasterize_points.cu:27-33).  The ctypes callback object is
+    created once and reused: `take()` hands the tensor of the finished call to the caller."""
 
-    def __init__(self, device):
-        self.device = device
-        self.tensor = torch.empty(0, dtype=torch.uint8, device=device)
+    def __init__(self):
+        self.device = None
+        self.tensor = None
 
         def _alloc(_ctx, nbytes):
             self.tensor = torch.empty(int(nbytes), dtype=torch.uint8, device=self.device)
             return self.tensor.data_ptr()
 
         self.callback = _capi.ALLOC_FN(_alloc)
+
+    def take(self):
+        t, self.tensor = self.tensor, None
+        return t if t is not None else torch.empty(0, dtype=torch.uint8, device=self.device)
+
+
+_tls = threading.local()
+
+
+def _chunks(device):
+    """This thread's three allocation callbacks (geometry, binning, image), bound to `device`."""
+    c = getattr(_tls, "chunks", None)
+    if c is None:
+        c = _tls.chunks = (_Chunk(), _Chunk(), _Chunk())
+    for x in c:
+        x.device = device
+        x.tensor = None
+    return c
+
+
+class _on_device:
+    """`torch.cuda.device(dev)` only when `dev` is not already current (the common case costs nothing)."""
+
+    def __init__(self, dev):
+        cur = torch.cuda.current_device()
+        self.ctx = None if dev.index is None or dev.index == cur else torch.cuda.device(dev)
+
+    def __enter__(self):
+        if self.ctx is not None:
+            self.ctx.__enter__()
+
+    def __exit__(self, *exc):
+        if self.ctx is not None:
+            self.ctx.__exit__(*exc)
 
 
 def _pad_bg(bg: torch.Tensor, n_ch: int) -> torch.Tensor:
@@ -105,15 +141,13 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             raise RuntimeError(f"tile_mask must have {tiles} elements, got {tile_mask.numel()}")
     M = int(sh.shape[1]) if sh.numel() != 0 else 0
 
-    with torch.cuda.device(dev):
-        f_opts = dict(dtype=torch.float32, device=dev)
-        out_color = torch.empty((n_ch, H, W), **f_opts)
-        out_depth = torch.empty((1, H, W), **f_opts)
-        out_alpha = torch.empty((1, H, W), **f_opts)
+    with _on_device(dev):
+        # colour, depth and alpha are views of one allocation (one device -> host copy moves them all)
+        images = torch.empty((n_ch + 2, H, W), dtype=torch.float32, device=dev)
+        out_color, out_depth, out_alpha = images[:n_ch], images[n_ch:n_ch + 1], images[n_ch + 1:]
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
-        geom, binning, img = _Chunk(dev), _Chunk(dev), _Chunk(dev)
+        geom, binning, img = _chunks(dev)
         n_touched = torch.zeros((P,), dtype=torch.int32, device=dev) if want_n_touched else None
-        rendered = 0
         rc = lib.sl_forward_ext(
             geom.callback, None, binning.callback, None, img.callback, None,
             P, int(degree), M, n_ch,
@@ -123,10 +157,11 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
             _ptr(rotations), _ptr(cov3D_precomp), _ptr(tile_mask),
             _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos),
             float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-            _ptr(out_color), _ptr(out_depth), _ptr(out_alpha), _ptr(radii), _ptr(n_touched),
+            out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(), _ptr(radii), _ptr(n_touched),
             int(bool(debug)), _stream(dev))
+        geom_t, binning_t, img_t = geom.take(), binning.take(), img.take()
         rendered = _capi.check(rc)
-    out = (rendered, out_color, out_depth, out_alpha, radii, geom.tensor, binning.tensor, img.tensor)
+    out = (rendered, out_color, out_depth, out_alpha, radii, geom_t, binning_t, img_t)
     return out + (n_touched,) if want_n_touched else out
 
 
@@ -171,7 +206,7 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     campos = _f32(campos, "campos")
     radii = radii.contiguous()
 
-    with torch.cuda.device(dev):
+    with _on_device(dev):
         (g_mean3D, g_mean2D, g_abs2D, g_color, g_depth, g_conic, g_opac, g_cov3D, g_sh, g_scale,
          g_rot) = _grad_block(P, [3, 3, 3, n_ch, 1, 4, 1, 6, 3 * M, 3, 4], dev)
         g_tau = torch.zeros(6, dtype=torch.float32, device=dev) if want_pose else None
