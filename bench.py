@@ -182,8 +182,11 @@ def run_gpu(args, impl):
             cam.viewmatrix, cam.projmatrix, cam.tanfovx, cam.tanfovy, gc, gd, ga, EMPTY, 0, cam.campos, geom, R,
             binning, img, alpha, False)
         if use_dist:
-            flat = out[0]._base if out[0]._base is not None else out[0]
-            dist.all_reduce(flat)   # multi-view step: sum of per-Gaussian gradients over the views
+            # multi-view step: sum over the views of the gradients the optimiser consumes (means3D, opacity,
+            # scales, rotations, colours: the leading span of the packed block; the screen-space
+            # statistics and chain intermediates that follow are per-view quantities)
+            flat = out[0]._base
+            dist.all_reduce(flat[:flat.trainable_numel])
         return R, radii
 
     # ---- e2e: public autograd API, per-view inputs from pinned host memory, images read back
@@ -318,7 +321,7 @@ def run_gpu(args, impl):
         "impl": impl,
         "config": {"workload": WORKLOAD, "gaussians": P, "channels": C, "image": [W, H], "views_per_gpu_per_step": 1,
                    "visible": V, "pairs": R, "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
-                   "parallelism": f"views sharded over {n_ranks} GPU(s)" + (", NCCL all-reduce of the packed gradient block" if use_dist else "")},
+                   "parallelism": f"views sharded over {n_ranks} GPU(s)" + (", NCCL all-reduce of the trainable-gradient span of the packed block (means3D, opacity, scales, rotations, colours)" if use_dist else "")},
         "e2e": {"value": round(e2e_value, 3), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": "GaussianRasterizer autograd fwd+bwd; camera + upstream pixel gradients from pinned host memory, "
                        "images read back (copies on a second stream, inside the timed step); the Gaussian map is "

@@ -166,7 +166,9 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
 
 
 def _grad_block(P: int, widths: list[int], device) -> list[torch.Tensor]:
-    """One zero-filled allocation (one memset) carved into per-gradient blocks."""
+    """One zero-filled allocation (one memset) carved into per-gradient blocks.  The base tensor
+    (`block._base`) carries `trainable_numel`: the length of its leading span that holds the
+    gradients of the trainable inputs (means3D, opacity, scales, rotations, colours / SH)."""
     sizes = [(P * w + 3) // 4 * 4 for w in widths]  # keep every block 16-byte aligned
     flat = torch.zeros(sum(sizes), dtype=torch.float32, device=device)
     out, off = [], 0
@@ -207,8 +209,13 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     radii = radii.contiguous()
 
     with _on_device(dev):
-        (g_mean3D, g_mean2D, g_abs2D, g_color, g_depth, g_conic, g_opac, g_cov3D, g_sh, g_scale,
-         g_rot) = _grad_block(P, [3, 3, 3, n_ch, 1, 4, 1, 6, 3 * M, 3, 4], dev)
+        # what an optimiser consumes first (one contiguous span for a multi-GPU all-reduce), then the
+        # per-view densification statistics, then the intermediates of the chain
+        (g_mean3D, g_opac, g_scale, g_rot, g_color, g_sh, g_mean2D, g_abs2D, g_depth, g_conic,
+         g_cov3D) = _grad_block(P, [3, 1, 3, 4, n_ch, 3 * M, 3, 3, 1, 4, 6], dev)
+        flat = g_mean3D._base
+        flat.trainable_numel = (flat.numel() if cov3D_precomp.numel() != 0
+                                else g_mean2D.storage_offset() - flat.storage_offset())
         g_tau = torch.zeros(6, dtype=torch.float32, device=dev) if want_pose else None
         if P != 0:
             rc = lib.sl_backward_ext(
