@@ -433,6 +433,74 @@ def run_pose_refine(args):
     return out if rank == 0 else None
 
 
+def run_mapping_loss(args):
+    """Secondary workload (not the default bench line): the per-view mapping loss
+    and its gradient seed on one 640x480, C = 4 view.  `--impl ours`: sl_mapping_loss through
+    splatloc_b200.mapping_loss (one kernel forward, one scaling multiply backward); `--impl reference`:
+    the reference's formulas (utils/utils.py:55-82, train_gaussians.py:38-42) as the PyTorch ops it
+    runs, on the same GPU.  Metric: loss fwd+bwd Mpix/s, L2 flushed between steps."""
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    H, W, C = 480, 640, 4
+    g = torch.Generator().manual_seed(3)
+    image = torch.rand((C, H, W), generator=g)
+    image[3] = 4.0 * torch.randn((H, W), generator=g)
+    depth = 0.5 + 4.0 * torch.rand((1, H, W), generator=g)
+    gt_image = (image[:3] + 0.1 * torch.randn((3, H, W), generator=g)).clamp(0, 1).to(dev)
+    gt_depth = (depth[0] + 0.05 * torch.randn((H, W), generator=g)).to(dev)
+    gt_kp = (torch.rand((H, W), generator=g) < 0.03).float().to(dev)
+    image, depth = image.to(dev).requires_grad_(True), depth.to(dev).requires_grad_(True)
+    a = torch.tensor([0.05], device=dev, requires_grad=True)
+    b = torch.tensor([-0.01], device=dev, requires_grad=True)
+    flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=dev)
+
+    if args.impl == "ours":
+        from splatloc_b200.mapping_loss import fused_mapping_loss
+
+        def loss_fn():
+            return fused_mapping_loss(image, depth, gt_image, gt_depth, gt_kp, a, b, 0.01, False)
+    else:
+        def loss_fn():
+            m_rgb = (gt_image.sum(dim=0) > 0.01).view(*depth.shape)
+            m_d = (gt_depth[None] > 0.01).view(*depth.shape)
+            l1_rgb = torch.abs((torch.exp(a) * image[:3] + b) * m_rgb - gt_image * m_rgb)
+            l1_depth = torch.abs(depth * m_d - gt_depth[None] * m_d)
+            kp = torch.nn.functional.binary_cross_entropy(torch.sigmoid(image[-1].view(-1)), gt_kp.view(-1), reduction="mean")
+            return l1_rgb.mean() + l1_depth.mean() + kp
+
+    def step():
+        for t in (image, depth, a, b):
+            t.grad = None
+        loss_fn().backward()
+
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for e0, e1 in ev:
+        flush.zero_()
+        e0.record()
+        step()
+        e1.record()
+    torch.cuda.synchronize()
+    ms = sum(x.elapsed_time(y) for x, y in ev) / args.steps
+    N = H * W
+    alg = (C + 1 + 3 + 1 + 1 + C + 1) * 4 * N          # reads + gradient writes of the fused forward
+    peak, how = measured_peaks()
+    out = {"metric": "mapping-loss fwd+bwd Mpix/s at 640x480", "value": round(N / (ms * 1e-3) / 1e6, 2), "unit": "Mpix/s",
+           "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms, 5), "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "impl": args.impl,
+           "config": {"workload": "mapping_loss_640x480_c4", "image": [W, H], "channels": C,
+                      "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
+                      "note": "SURVEY 8(f) row 2; time includes the autograd call overhead of both arms"}}
+    if args.impl == "ours":
+        out["roofline"] = {"kernel": "mapping_loss", "bound": "hbm", "achieved": round(alg / (ms * 1e-3) / 1e9, 1), "peak": peak,
+                           "unit": "GB/s", "frac": round(alg / (ms * 1e-3) / 1e9 / peak, 4), "traffic": None, "peak_source": how,
+                           "note": "whole fwd+bwd step over one kernel's algorithmic bytes: a 3 us kernel inside ~60 us of "
+                                   "launch and autograd latency"}
+    return out
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -442,10 +510,16 @@ def main():
     ap.add_argument("--points", type=int, default=P_DEFAULT)
     ap.add_argument("--cpu-budget", type=float, default=20.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", choices=["train_step", "pose_refine"], default="train_step")
+    ap.add_argument("--workload", choices=["train_step", "pose_refine", "mapping_loss"], default="train_step")
     ap.add_argument("--frames", type=int, default=4, help="pose_refine: query frames per GPU")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
+    if args.workload == "mapping_loss":
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+        if env_int("RANK", 0) == 0:
+            print(json.dumps(run_mapping_loss(args)))
+        return
     if args.workload == "pose_refine":
         if not torch.cuda.is_available():
             raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")

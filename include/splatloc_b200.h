@@ -179,6 +179,30 @@ int sl_knn(int P, const float* points, float* mean_dists,
 #define SL_KNN_STATIC_MAX_POINTS 65536
 int sl_knn_static(int P, const float* points, float* mean_dists, void* stream);
 
+/* ---- per-view mapping loss and its gradient seed ---------------------
+ * Replaces, for one rendered view, the reference's
+ *   get_loss_mapping(config, image, depth, viewpoint, opacity, initialization)   utils/utils.py:55-82
+ *   get_loss_marker(config, pred, gt)                                            train_gaussians.py:38-42
+ * as the mapping loop sums them (train_gaussians.py:215-216):
+ *   loss = mean |(exp(a) * rgb + b) * m_rgb - gt_rgb * m_rgb| + mean |depth * m_d - gt_depth * m_d|
+ *        + mean BCE(sigmoid(kp_logit), gt_kp),
+ *   m_rgb = gt_rgb.sum(0) > rgb_boundary_threshold,  m_d = gt_depth > 0.01,
+ * and writes d loss / d image, d loss / d depth in the same pass over the pixels.
+ *   image     (channels, H, W): the rasterizer's colour output; channels 0..2 are rgb and, when
+ *             gt_kp != NULL, channel channels-1 is the key-point logit (render()'s "kp_prob")
+ *   depth     (1, H, W); gt_image (3, H, W); gt_depth (H, W); gt_kp (H, W) or NULL (no key-point term)
+ *   exposure_a, exposure_b: device pointers to the camera's exposure parameters (one float each; NULL = 0)
+ *   initialization != 0: the exposure affine is skipped (utils.py:56-57)
+ *   out[6] (device): loss, colour term, depth term, key-point term, d loss / d exposure_a, d loss / d exposure_b
+ *   workspace: sl_mapping_loss_workspace_bytes() bytes of device memory, zero-filled before its first
+ *             use (the kernel leaves it ready for the next call); one per concurrently running call.
+ * Sums are accumulated in double and reduced in a fixed order: results are run-to-run identical. */
+size_t sl_mapping_loss_workspace_bytes(void);
+int sl_mapping_loss(int width, int height, int channels, const float* image, const float* depth,
+                    const float* gt_image, const float* gt_depth, const float* gt_kp, const float* exposure_a,
+                    const float* exposure_b, float rgb_boundary_threshold, int initialization, float* dL_dimage,
+                    float* dL_ddepth, float* out, void* workspace, void* stream);
+
 /* ---- instrumentation (no counterpart in the reference, which has no tracing,
  * SURVEY.md section 5) ------------------------------------------------------ */
 

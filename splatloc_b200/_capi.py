@@ -80,6 +80,13 @@ SIGNATURES = {
     "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),
     "sl_knn_static": (C.c_int, [C.c_int, _F, _F, C.c_void_p]),
+    "sl_mapping_loss_workspace_bytes": (C.c_size_t, []),
+    "sl_mapping_loss": (C.c_int, [
+        C.c_int, C.c_int, C.c_int,                   # width, height, channels
+        _F, _F, _F, _F, _F,                          # image, depth, gt_image, gt_depth, gt_kp
+        _F, _F, C.c_float, C.c_int,                  # exposure_a, exposure_b, rgb_boundary_threshold, initialization
+        _F, _F, _F, _F, C.c_void_p,                  # dL_dimage, dL_ddepth, out, workspace, stream
+    ]),
     "sl_launch_count": (C.c_longlong, []),
     "sl_set_binning_mode": (None, [C.c_int]),
     "sl_profile_enable": (None, [C.c_int]),

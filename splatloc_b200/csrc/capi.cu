@@ -133,6 +133,26 @@ const char* sl_version(void) { return "splatloc_b200 0.1 sm_100a"; }
 
 const char* sl_last_error(void) { return last_error(); }
 
+size_t sl_mapping_loss_workspace_bytes(void) { return mapping_loss_workspace_bytes(); }
+
+int sl_mapping_loss(int width, int height, int channels, const float* image, const float* depth,
+                    const float* gt_image, const float* gt_depth, const float* gt_kp, const float* exposure_a,
+                    const float* exposure_b, float rgb_boundary_threshold, int initialization, float* dL_dimage,
+                    float* dL_ddepth, float* out, void* workspace, void* stream_)
+{
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (width <= 0 || height <= 0) { set_error("sl_mapping_loss: empty image %d x %d", width, height); return SL_ERR_ARGUMENT; }
+    if (!image || !depth || !gt_image || !gt_depth || !dL_dimage || !dL_ddepth || !out || !workspace) {
+        set_error("sl_mapping_loss: null pointer argument");
+        return SL_ERR_ARGUMENT;
+    }
+    int rc = launch_mapping_loss(width, height, channels, image, depth, gt_image, gt_depth, gt_kp, exposure_a, exposure_b,
+                                 rgb_boundary_threshold, initialization != 0, dL_dimage, dL_ddepth, out,
+                                 static_cast<char*>(workspace), stream);
+    if (rc) return rc;
+    return check_stage(false, stream, "mapping loss");
+}
+
 long long sl_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 void sl_profile_enable(int on)

@@ -104,4 +104,12 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
 size_t knn_scratch_bytes(int P);
 int launch_knn(int P, const float* points, float* mean_dists, char* scratch, cudaStream_t stream);
 
+// per-view mapping loss + gradient seed (reference: utils/utils.py:55-82,
+// train_gaussians.py:38-42).  `workspace` holds mapping_loss_workspace_bytes() bytes, zero before first use.
+size_t mapping_loss_workspace_bytes();
+int launch_mapping_loss(int W, int H, int C, const float* image, const float* depth, const float* gt_image,
+                        const float* gt_depth, const float* gt_kp, const float* exposure_a, const float* exposure_b,
+                        float rgb_threshold, bool initialization, float* dL_dimage, float* dL_ddepth, float* out,
+                        char* workspace, cudaStream_t stream);
+
 }  // namespace sl
