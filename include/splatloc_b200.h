@@ -135,6 +135,29 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                    float tan_fovx, float tan_fovy, int prefiltered,
                    float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
                    int debug, void* stream);
+/* sl_forward_nosync = sl_forward_ext without the reference's one blocking read of the pair count
+ * (rasterizer_impl.cu:522; no reference counterpart): the caller states how many (tile, Gaussian)
+ * pairs the binning chunk may hold, the chunk is requested with sl_binning_bytes(max_pairs) before
+ * anything runs, and nothing in the call waits for the device -- so a forward + backward step can be
+ * captured in a CUDA graph and replayed with no host work between its kernels.
+ *   returns max_pairs: pass THAT as R to sl_backward[_ext] (it locates the chunk's arrays).
+ *   status [1] (device int, required): 0 after the call's work has run, or 1 if the frame had more
+ *     than max_pairs pairs or a tile with more than 4096 of them.  Then colour / depth / alpha are
+ *     background-only, n_contrib is 0 and the backward yields zero gradients: check the word when
+ *     convenient and redo the frame with sl_forward_ext or a larger max_pairs.
+ * Always uses the tile-bucket binning (sl_set_binning_mode does not apply).  debug is not available. */
+int sl_forward_nosync(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                      sl_alloc_fn binning_alloc, void* binning_ctx,
+                      sl_alloc_fn image_alloc, void* image_ctx,
+                      int P, int D, int M, int C,
+                      const float* background, int width, int height,
+                      const float* means3D, const float* shs, const float* colors_precomp,
+                      const float* opacities, const float* scales, float scale_modifier,
+                      const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                      float tan_fovx, float tan_fovy, int prefiltered,
+                      float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                      int max_pairs, int* status, void* stream);
 int sl_backward_ext(int P, int D, int M, int R, int C,
                     const float* background, int width, int height,
                     const float* means3D, const float* shs, const float* colors_precomp,

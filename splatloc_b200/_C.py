@@ -108,9 +108,13 @@ def _channels(colors: torch.Tensor) -> int:
 
 def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations, scale_modifier,
                         cov3D_precomp, tile_mask, viewmatrix, projmatrix, tan_fovx, tan_fovy,
-                        image_height, image_width, sh, degree, campos, prefiltered, debug, want_n_touched=False):
+                        image_height, image_width, sh, degree, campos, prefiltered, debug, want_n_touched=False,
+                        max_pairs=None):
     """-> (num_rendered, color, depth, alpha, radii, geomBuffer, binningBuffer, imgBuffer)
-    [+ n_touched (P,) int32 as a 9th element when `want_n_touched` -- an extension, see sl_forward_ext]."""
+    [+ n_touched (P,) int32 when `want_n_touched` -- an extension, see sl_forward_ext]
+    [+ status (1,) int32 on the device when `max_pairs` is given -- sl_forward_nosync: no host
+       synchronisation (CUDA-graph capturable), `num_rendered` is then `max_pairs`, and status becomes 1
+       if the frame did not fit (outputs are background-only in that case)]."""
     if means3D.dim() != 2 or means3D.shape[1] != 3:
         raise RuntimeError("means3D must have dimensions (num_points, 3)")
     lib = _capi.load()
@@ -148,21 +152,29 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
         radii = torch.empty((P,), dtype=torch.int32, device=dev)
         geom, binning, img = _chunks(dev)
         n_touched = torch.zeros((P,), dtype=torch.int32, device=dev) if want_n_touched else None
-        rc = lib.sl_forward_ext(
-            geom.callback, None, binning.callback, None, img.callback, None,
-            P, int(degree), M, n_ch,
-            _ptr(background), W, H,
-            _ptr(means3D), _ptr(sh), _ptr(colors),
-            _ptr(opacity), _ptr(scales), float(scale_modifier),
-            _ptr(rotations), _ptr(cov3D_precomp), _ptr(tile_mask),
-            _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos),
-            float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
-            out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(), _ptr(radii), _ptr(n_touched),
-            int(bool(debug)), _stream(dev))
+        common = (geom.callback, None, binning.callback, None, img.callback, None,
+                  P, int(degree), M, n_ch,
+                  _ptr(background), W, H,
+                  _ptr(means3D), _ptr(sh), _ptr(colors),
+                  _ptr(opacity), _ptr(scales), float(scale_modifier),
+                  _ptr(rotations), _ptr(cov3D_precomp), _ptr(tile_mask),
+                  _ptr(viewmatrix), _ptr(projmatrix), _ptr(campos),
+                  float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+                  out_color.data_ptr(), out_depth.data_ptr(), out_alpha.data_ptr(), _ptr(radii), _ptr(n_touched))
+        status = None
+        if max_pairs is None:
+            rc = lib.sl_forward_ext(*common, int(bool(debug)), _stream(dev))
+        else:
+            status = torch.empty(1, dtype=torch.int32, device=dev)
+            rc = lib.sl_forward_nosync(*common, int(max_pairs), status.data_ptr(), _stream(dev))
         geom_t, binning_t, img_t = geom.take(), binning.take(), img.take()
         rendered = _capi.check(rc)
     out = (rendered, out_color, out_depth, out_alpha, radii, geom_t, binning_t, img_t)
-    return out + (n_touched,) if want_n_touched else out
+    if want_n_touched:
+        out = out + (n_touched,)
+    if status is not None:
+        out = out + (status,)
+    return out
 
 
 def _grad_block(P: int, widths: list[int], device) -> list[torch.Tensor]:

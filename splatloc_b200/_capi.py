@@ -62,6 +62,18 @@ SIGNATURES = {
         _F, _F, _F, _F, _F,                          # out_color, out_depth, out_alpha, radii, n_touched
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
+    "sl_forward_nosync": (C.c_int, [
+        ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p,
+        C.c_int, C.c_int, C.c_int, C.c_int,          # P, D, M, C
+        _F, C.c_int, C.c_int,                        # background, width, height
+        _F, _F, _F,                                  # means3D, shs, colors_precomp
+        _F, _F, C.c_float,                           # opacities, scales, scale_modifier
+        _F, _F, _F,                                  # rotations, cov3D_precomp, tile_mask
+        _F, _F, _F,                                  # viewmatrix, projmatrix, cam_pos
+        C.c_float, C.c_float, C.c_int,               # tan_fovx, tan_fovy, prefiltered
+        _F, _F, _F, _F, _F,                          # out_color, out_depth, out_alpha, radii, n_touched
+        C.c_int, _F, C.c_void_p,                     # max_pairs, status, stream
+    ]),
     "sl_backward_ext": (C.c_int, [
         C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # P, D, M, R, C
         _F, C.c_int, C.c_int,                        # background, width, height

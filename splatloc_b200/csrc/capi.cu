@@ -219,20 +219,23 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                           prefiltered, out_color, out_depth, out_alpha, radii, nullptr, debug, stream_);
 }
 
-int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
-                   sl_alloc_fn binning_alloc, void* binning_ctx,
-                   sl_alloc_fn image_alloc, void* image_ctx,
-                   int P, int D, int M, int C,
-                   const float* background, int width, int height,
-                   const float* means3D, const float* shs, const float* colors_precomp,
-                   const float* opacities, const float* scales, float scale_modifier,
-                   const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
-                   const float* viewmatrix, const float* projmatrix, const float* cam_pos,
-                   float tan_fovx, float tan_fovy, int prefiltered,
-                   float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
-                   int debug, void* stream_)
+// `max_pairs` < 0: the reference's protocol -- read R back, size the binning chunk exactly.
+// `max_pairs` >= 0 (sl_forward_nosync): the caller's capacity; no host synchronisation at all.
+static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                        sl_alloc_fn binning_alloc, void* binning_ctx,
+                        sl_alloc_fn image_alloc, void* image_ctx,
+                        int P, int D, int M, int C,
+                        const float* background, int width, int height,
+                        const float* means3D, const float* shs, const float* colors_precomp,
+                        const float* opacities, const float* scales, float scale_modifier,
+                        const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                        const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                        float tan_fovx, float tan_fovy, int prefiltered,
+                        float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                        int debug, void* stream_, int max_pairs, int* status)
 {
     g_error[0] = 0;
+    const bool nosync = max_pairs >= 0;
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool dbg = debug != 0;
     if (P < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4)) {
@@ -251,6 +254,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         SL_CUDA(cudaMemsetAsync(out_color, 0, N * C * sizeof(float), stream), "forward memset");
         SL_CUDA(cudaMemsetAsync(out_depth, 0, N * sizeof(float), stream), "forward memset");
         SL_CUDA(cudaMemsetAsync(out_alpha, 0, N * sizeof(float), stream), "forward memset");
+        if (status != nullptr) SL_CUDA(cudaMemsetAsync(status, 0, sizeof(int), stream), "forward memset");
         return 0;
     }
     if (n_touched != nullptr) SL_CUDA(cudaMemsetAsync(n_touched, 0, (size_t)P * sizeof(int), stream), "n_touched memset");
@@ -289,6 +293,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     SL_CUDA(cudaMemsetAsync(img.bin_info, 0, sizeof(BinInfo), stream), "bin info memset");
     int mode = g_binning_mode.load(std::memory_order_relaxed);
     if (mode == 0) mode = kDefaultBinningMode;
+    if (nosync) mode = 2;   // the only binning path whose launches do not depend on R
     const bool want_ordered = mode == 3 && ordered_supported(n_tiles);
     int rc;
     {
@@ -303,15 +308,26 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     {
         StageTimer t(ST_SCAN, stream);
         rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles,
-                              want_ordered ? geom.block_vis : nullptr, (int)geom.pre_blocks, stream);
+                              want_ordered ? geom.block_vis : nullptr, (int)geom.pre_blocks,
+                              nosync ? (uint32_t)max_pairs : 0xffffffffu,
+                              nosync ? (uint32_t)TILE_SORT_SMALL : 0xffffffffu, status, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile scan");
 
     // The binning chunk is sized by R, which only the device knows: one blocking read.
     BinInfo info;
-    SL_CUDA(cudaMemcpyAsync(&info, img.bin_info, sizeof(BinInfo), cudaMemcpyDeviceToHost, stream), "read R");
-    SL_CUDA(cudaStreamSynchronize(stream), "read R");
+    if (nosync) {
+        // No read-back: the chunk holds `max_pairs` pairs; tile_scan_kernel has flagged the frame on the
+        // device if it needs more (or has a tile list beyond the 256-thread segment sort), in which
+        // case the remaining stages do nothing.  Launch shapes below assume the worst admissible case.
+        memset(&info, 0, sizeof(info));
+        info.num_pairs = (uint32_t)max_pairs;
+        info.max_pairs = (uint32_t)TILE_SORT_SMALL;
+    } else {
+        SL_CUDA(cudaMemcpyAsync(&info, img.bin_info, sizeof(BinInfo), cudaMemcpyDeviceToHost, stream), "read R");
+        SL_CUDA(cudaStreamSynchronize(stream), "read R");
+    }
     if (info.num_pairs >= (1u << 30)) {
         set_error("sl_forward: %u (tile, Gaussian) pairs exceed the 2^30 limit", info.num_pairs);
         return SL_ERR_CAPACITY;
@@ -358,7 +374,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         {
             StageTimer t(ST_EMIT, stream);
             rc = launch_scatter_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges, img.tile_counts,
-                                      bin.point_list_keys_unsorted, bin.point_list_unsorted, stream);
+                                      bin.point_list_keys_unsorted, bin.point_list_unsorted, img.bin_info, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "scatter pairs");
@@ -366,7 +382,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
             StageTimer t(ST_SORT, stream);
             rc = launch_tile_sort(C, info, img.ranges, img.tile_order, img.large_tiles, n_tiles, vp.grid_x, bin.point_list_keys_unsorted,
                                   bin.point_list_unsorted, bin.point_list_keys, bin.point_list, geom, features,
-                                  bin.records, bin.masks, stream);
+                                  bin.records, bin.masks, img.bin_info, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "tile sort");
@@ -404,6 +420,49 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend forward");
     return R;
+}
+
+int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                   sl_alloc_fn binning_alloc, void* binning_ctx,
+                   sl_alloc_fn image_alloc, void* image_ctx,
+                   int P, int D, int M, int C,
+                   const float* background, int width, int height,
+                   const float* means3D, const float* shs, const float* colors_precomp,
+                   const float* opacities, const float* scales, float scale_modifier,
+                   const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                   const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                   float tan_fovx, float tan_fovy, int prefiltered,
+                   float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                   int debug, void* stream_)
+{
+    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, C,
+                        background, width, height, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
+                        rotations, cov3D_precomp, tile_mask, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
+                        prefiltered, out_color, out_depth, out_alpha, radii, n_touched, debug, stream_, -1, nullptr);
+}
+
+int sl_forward_nosync(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                      sl_alloc_fn binning_alloc, void* binning_ctx,
+                      sl_alloc_fn image_alloc, void* image_ctx,
+                      int P, int D, int M, int C,
+                      const float* background, int width, int height,
+                      const float* means3D, const float* shs, const float* colors_precomp,
+                      const float* opacities, const float* scales, float scale_modifier,
+                      const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                      float tan_fovx, float tan_fovy, int prefiltered,
+                      float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                      int max_pairs, int* status, void* stream_)
+{
+    if (max_pairs < 0 || status == nullptr) {
+        set_error("sl_forward_nosync: max_pairs >= 0 and a device status word are required");
+        return SL_ERR_ARGUMENT;
+    }
+    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, C,
+                        background, width, height, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
+                        rotations, cov3D_precomp, tile_mask, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
+                        prefiltered, out_color, out_depth, out_alpha, radii, n_touched, /*debug=*/0, stream_, max_pairs,
+                        status);
 }
 
 int sl_backward(int P, int D, int M, int R, int C,

@@ -40,15 +40,16 @@ int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t
 // and each segment is sorted on (depth bits, Gaussian id) in shared memory by one CTA, which also
 // writes the PairRecords and masks.  The result equals the stable global sort on (tile | depth).
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, uint32_t* block_vis, int n_blocks, cudaStream_t stream);
+                     int n_tiles, uint32_t* block_vis, int n_blocks, uint32_t max_pairs, uint32_t max_tile_pairs,
+                     int* status, cudaStream_t stream);
 int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask, int grid_x,
                          int grid_y, const uint2* ranges, uint32_t* cursors, uint64_t* keys, uint32_t* vals,
-                         cudaStream_t stream);
+                         const BinInfo* dev_info, cudaStream_t stream);
 int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
                      const uint32_t* large_tiles, int n_tiles,
                      int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                      uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
-                     uint8_t* masks, cudaStream_t stream);
+                     uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream);
 
 // ---- depth-ordered emit (ordered_binning.cu): the visible Gaussians are sorted ONCE by depth and every
 // pair is then written straight to its final list position -- no per-tile sort.

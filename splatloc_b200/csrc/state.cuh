@@ -38,7 +38,8 @@ struct BinInfo {
     uint32_t max_pairs;      // longest tile list
     uint32_t num_visible;    // V: Gaussians that touch at least one tile
     uint32_t rect_tiles;     // A: tiles inside their rectangles (= R unless a tile mask removes some)
-    uint32_t pad[2];
+    uint32_t overflow;       // no-readback mode: R or a tile's list exceeds what the caller provided for
+    uint32_t pad[1];
 };
 
 template <typename T>

@@ -30,7 +30,7 @@ namespace sl {
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
                  uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles,
-                 uint32_t* block_vis, int n_blocks)
+                 uint32_t* block_vis, int n_blocks, uint32_t max_pairs, uint32_t max_tile_pairs, int* status)
 {
     constexpr int NT = 1024;
     __shared__ uint32_t s_warp[32];
@@ -108,11 +108,16 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
         atomicAdd(&s_huge, n_huge);
     }
     __syncthreads();
+    // No-readback mode (sl_forward_nosync): the host sized the binning chunk without knowing R.  If
+    // the frame does not fit, every later stage of this frame does nothing and the caller is told.
+    const bool overflow = s_carry > max_pairs || s_max > max_tile_pairs;
     if (tid == 0) {
         info->num_pairs = s_carry;
         info->n_large = s_large;
         info->n_huge = s_huge;
         info->max_pairs = s_max;
+        info->overflow = overflow ? 1u : 0u;
+        if (status != nullptr) *status = overflow ? 1 : 0;
     }
 
     // launch order: counting sort of the tiles by list length, longest first
@@ -140,6 +145,10 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
         const uint32_t len = ranges[t].y - ranges[t].x;
         order[atomicAdd(&s_hist[NT - 1 - len / width], 1u)] = t;
     }
+    if (overflow) {
+        __syncthreads();
+        for (int t = tid; t < n_tiles; t += NT) ranges[t] = make_uint2(0u, 0u);   // nothing is drawn
+    }
 }
 
 // ------------------------------------------------------------------ 3. scatter pairs into tile segments
@@ -151,9 +160,10 @@ scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __r
                      const uint32_t* __restrict__ tiles_touched, const int* __restrict__ radii,
                      const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y,
                      const uint2* __restrict__ ranges, uint32_t* cursors,
-                     uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
+                     uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, const BinInfo* __restrict__ info)
 {
     constexpr uint32_t SOLO_MAX = 8;
+    if (info->overflow) return;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
@@ -328,9 +338,10 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
                  const float2* __restrict__ means2D, const float* __restrict__ depths,
                  const float4* __restrict__ conic_opacity, const float* __restrict__ features,
-                 PairRecord* __restrict__ records, uint8_t* __restrict__ masks)
+                 PairRecord* __restrict__ records, uint8_t* __restrict__ masks, const BinInfo* __restrict__ dev_info)
 {
     extern __shared__ __align__(16) unsigned long long s_key[];
+    if (dev_info->overflow) return;
     const uint32_t tile = tiles[blockIdx.x];
     const uint2 range = ranges[tile];
     const uint32_t n = range.y - range.x;
@@ -347,21 +358,24 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 }
 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, uint32_t* block_vis, int n_blocks, cudaStream_t stream)
+                     int n_tiles, uint32_t* block_vis, int n_blocks, uint32_t max_pairs, uint32_t max_tile_pairs,
+                     int* status, cudaStream_t stream)
 {
     // the second CTA (offsets for the depth-ordered emit) only when that path is selected
     tile_scan_kernel<<<block_vis != nullptr ? 2 : 1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info,
-                                                                        n_tiles, block_vis, n_blocks);
+                                                                        n_tiles, block_vis, n_blocks, max_pairs,
+                                                                        max_tile_pairs, status);
     count_launch();
     return 0;
 }
 
 int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask, int grid_x,
                          int grid_y, const uint2* ranges, uint32_t* cursors, uint64_t* keys, uint32_t* vals,
-                         cudaStream_t stream)
+                         const BinInfo* dev_info, cudaStream_t stream)
 {
     scatter_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.tiles_touched, radii,
-                                                               tile_mask, grid_x, grid_y, ranges, cursors, keys, vals);
+                                                               tile_mask, grid_x, grid_y, ranges, cursors, keys, vals,
+                                                               dev_info);
     count_launch();
     return 0;
 }
@@ -371,7 +385,7 @@ static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const ui
                               const uint32_t* large_tiles, int n_tiles,
                               int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                               uint32_t* point_list, const GeomState& g, const float* features,
-                              PairRecord* records, uint8_t* masks, cudaStream_t stream)
+                              PairRecord* records, uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream)
 {
     // Long segments (work list written by tile_scan_kernel) get a 1024-thread CTA with 128 KB of
     // shared memory each; the 256-thread launch covers all tiles and skips those.
@@ -382,7 +396,7 @@ static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const ui
                 "tile sort smem attribute");
         tile_sort_kernel<C, T><<<(int)info.n_large, T, smem, stream>>>(
             ranges, large_tiles, grid_x, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list, g.means2D,
-            g.depths, g.conic_opacity, features, records, masks);
+            g.depths, g.conic_opacity, features, records, masks, dev_info);
         count_launch();
     }
     constexpr int T = 256;
@@ -392,7 +406,7 @@ static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const ui
     while (pad < longest) pad <<= 1;
     tile_sort_kernel<C, T><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
         ranges, tile_order, grid_x, 0u, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
-        features, records, masks);
+        features, records, masks, dev_info);
     count_launch();
     return 0;
 }
@@ -401,13 +415,13 @@ int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint
                      const uint32_t* large_tiles, int n_tiles,
                      int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                      uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
-                     uint8_t* masks, cudaStream_t stream)
+                     uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream)
 {
     if (C == 4)
         return tile_sort_launches<4>(info, ranges, tile_order, large_tiles, n_tiles, grid_x, keys_in, vals_in, keys_out, point_list,
-                                     g, features, records, masks, stream);
+                                     g, features, records, masks, dev_info, stream);
     return tile_sort_launches<3>(info, ranges, tile_order, large_tiles, n_tiles, grid_x, keys_in, vals_in, keys_out, point_list, g,
-                                 features, records, masks, stream);
+                                 features, records, masks, dev_info, stream);
 }
 
 }  // namespace sl

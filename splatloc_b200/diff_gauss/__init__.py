@@ -63,13 +63,17 @@ def _call_with_snapshot(fn, args, debug, dump_path, what):
 class _RasterizeGaussians(torch.autograd.Function):
     @staticmethod
     def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                cov3Ds_precomp, tile_mask, raster_settings, theta=None, rho=None, want_n_touched=False):
+                cov3Ds_precomp, tile_mask, raster_settings, theta=None, rho=None, want_n_touched=False,
+                max_pairs=None, status_out=None):
         rs = raster_settings
         fw_args = (rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier,
                    cov3Ds_precomp, tile_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy,
                    rs.image_height, rs.image_width, sh, rs.sh_degree, rs.campos, rs.prefiltered, rs.debug)
-        res = _call_with_snapshot(_C.rasterize_gaussians, fw_args + (want_n_touched,), rs.debug, _DUMP_FW, "forward")
+        res = _call_with_snapshot(_C.rasterize_gaussians, fw_args + (want_n_touched, max_pairs), rs.debug, _DUMP_FW,
+                                  "forward")
         (num_rendered, color, depth, alpha, radii, geom, binning, img) = res[:8]
+        if max_pairs is not None and status_out is not None:
+            status_out.append(res[-1])     # device int32: 1 if the frame did not fit `max_pairs`
 
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
@@ -102,13 +106,15 @@ class _RasterizeGaussians(torch.autograd.Function):
         means2D.absgrad = g_abs2D
         # one gradient per forward input; tile_mask and the settings have none
         return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, None,
-                g_theta, g_rho, None)
+                g_theta, g_rho, None, None, None)
 
 
 def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                        cov3Ds_precomp, tile_mask, raster_settings, theta=None, rho=None, want_n_touched=False):
+                        cov3Ds_precomp, tile_mask, raster_settings, theta=None, rho=None, want_n_touched=False,
+                        max_pairs=None, status_out=None):
     return _RasterizeGaussians.apply(means3D, means2D, sh, colors_precomp, opacities, scales, rotations,
-                                     cov3Ds_precomp, tile_mask, raster_settings, theta, rho, want_n_touched)
+                                     cov3Ds_precomp, tile_mask, raster_settings, theta, rho, want_n_touched,
+                                     max_pairs, status_out)
 
 
 def mark_visible(positions: torch.Tensor, viewmatrix: torch.Tensor, projmatrix: torch.Tensor):
@@ -122,12 +128,21 @@ class GaussianRasterizer(nn.Module):
       * `theta=` / `rho=` (3-vectors, MonoGS's `cam_rot_delta` / `cam_trans_delta`): placeholders whose
         values are taken as zero; after backward their `.grad` holds dL/dtheta, dL/drho for the left
         perturbation W2C' = Exp(rho, theta) W2C of `viewmatrix` (and of `projmatrix`, `campos`);
-      * `return_n_touched=True` at construction: forward returns a 5th tensor, n_touched (P,) int32."""
+      * `return_n_touched=True` at construction: forward returns a 5th tensor, n_touched (P,) int32.
+    A third option changes how, not what: `max_pairs=N` (sl_forward_nosync) sizes the binning scratch
+    for N (tile, Gaussian) pairs up front instead of reading the pair count back from the device, so
+    the call never blocks the host and a forward + backward step can be captured in a CUDA graph
+    (`splatloc_b200.graphs`).  After each forward `self.overflow` is a (1,) int32 device tensor: 1 if
+    the frame needed more than N pairs (or a tile more than 4096), in which case the outputs are
+    background-only and the gradients zero -- check it when convenient and redo that frame."""
 
-    def __init__(self, raster_settings: GaussianRasterizationSettings, return_n_touched: bool = False):
+    def __init__(self, raster_settings: GaussianRasterizationSettings, return_n_touched: bool = False,
+                 max_pairs: int | None = None):
         super().__init__()
         self.raster_settings = raster_settings
         self.return_n_touched = return_n_touched
+        self.max_pairs = max_pairs
+        self.overflow = None
 
     def markVisible(self, positions):
         rs = self.raster_settings
@@ -153,9 +168,12 @@ class GaussianRasterizer(nn.Module):
         if tile_mask.dtype != torch.bool:
             tile_mask = tile_mask.bool()
 
-        return rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
-                                   cov3D_precomp, tile_mask, self.raster_settings, theta, rho,
-                                   self.return_n_touched)
+        status = []
+        out = rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                  cov3D_precomp, tile_mask, self.raster_settings, theta, rho,
+                                  self.return_n_touched, self.max_pairs, status)
+        self.overflow = status[0] if status else None
+        return out
 
 
 # ------------------------------------------------------------------ scratch-buffer views
