@@ -238,6 +238,53 @@ def run_gpu(args, impl):
                 dist.all_reduce(t.grad)
         main.wait_event(ev_imgs)                       # the step ends when its images are on the host
 
+    # ---- e2e, this library: the same step captured once in a CUDA graph (splatloc_b200.graphs) --
+    # possible because sl_forward_nosync needs no read-back of the pair count -- and replayed with one
+    # launch per step.  Per step and inside the timed region: the camera and this step's upstream
+    # gradients come from pinned host memory (the gradients of step i + 1 are sent on a copy stream
+    # while step i runs, then moved into the graph's input by a device copy), the images are copied to
+    # pinned host memory inside the graph, overlapped with the backward.
+    graphed = None
+    if impl == "ours" and not os.environ.get("BENCH_E2E_EAGER"):
+        from splatloc_b200.graphs import GraphedViewStep
+        max_R = 0
+        for i in range(N_CAMERAS):
+            max_R = max(max_R, step_resident(i)[0])
+        img_host_packed = torch.empty(C + 2, H, W).pin_memory()
+        c0 = cams_host[0]
+        graphed = GraphedViewStep(leaves, H, W, c0.tanfovx, c0.tanfovy, bg, max_pairs=int(1.25 * max_R) + 4096,
+                                  host_images=img_host_packed)
+        stage = [torch.empty(C + 2, H, W, device=dev) for _ in range(2)]
+        copy_in = torch.cuda.Stream(device=dev)
+        ev_in = [torch.cuda.Event(), torch.cuda.Event()]      # stage[b] holds its step's gradients
+        ev_free = [torch.cuda.Event(), torch.cuda.Event()]    # stage[b] has been consumed
+        pipe = {"sent": None}
+
+        def send_grads(step):
+            b = step % 2
+            with torch.cuda.stream(copy_in):
+                copy_in.wait_event(ev_free[b])
+                stage[b].copy_(grads_packed[step % N_CAMERAS], non_blocking=True)
+                ev_in[b].record(copy_in)
+
+        def step_e2e_graph(i):
+            k, b = i % N_CAMERAS, i % 2
+            main = torch.cuda.current_stream(dev)
+            if pipe["sent"] != i:
+                send_grads(i)
+            graphed.viewmatrix.copy_(cam_host[k][0], non_blocking=True)
+            graphed.projmatrix.copy_(cam_host[k][1], non_blocking=True)
+            graphed.campos.copy_(cam_host[k][2], non_blocking=True)
+            main.wait_event(ev_in[b])
+            graphed.upstream.copy_(stage[b], non_blocking=True)
+            ev_free[b].record(main)
+            send_grads(i + 1)
+            pipe["sent"] = i + 1
+            graphed.replay()
+            if use_dist:
+                for t in leaves.values():
+                    dist.all_reduce(t.grad)
+
     def barrier():
         torch.cuda.synchronize()
         if world > 1 and impl == "ours":
@@ -302,7 +349,11 @@ def run_gpu(args, impl):
     # the warm-up steps launched too; count only the timed ones
     if impl == "ours":
         launches = launches * args.steps // (args.steps + args.warmup)
-    e2e_ms, _, _ = timed(step_e2e, args.steps, args.warmup)
+    e2e_ms, _, _ = timed(step_e2e_graph if graphed is not None else step_e2e, args.steps, args.warmup)
+    e2e_eager_ms = None
+    if graphed is not None:
+        assert int(graphed.overflow) == 0, "bench: the graphed step's pair capacity was exceeded"
+        e2e_eager_ms, _, _ = timed(step_e2e, args.steps, args.warmup)
     # per-stage device times: same steps again with the library's event timers on (kept apart from
     # the headline loop because reading the events back blocks the host between stages)
     _, _, prof = timed(step_resident, max(5, args.steps // 2), 1, profile=True)
@@ -323,13 +374,21 @@ def run_gpu(args, impl):
                    "visible": V, "pairs": R, "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
                    "parallelism": f"views sharded over {n_ranks} GPU(s)" + (", NCCL all-reduce of the trainable-gradient span of the packed block (means3D, opacity, scales, rotations, colours)" if use_dist else "")},
         "e2e": {"value": round(e2e_value, 3), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "api": "GaussianRasterizer autograd fwd+bwd; camera + upstream pixel gradients from pinned host memory, "
-                       "images read back (copies on a second stream, inside the timed step); the Gaussian map is "
-                       "resident state"},
+                "api": ("splatloc_b200.graphs.GraphedViewStep: the GaussianRasterizer autograd fwd+bwd (max_pairs / "
+                        "sl_forward_nosync: no pair-count read-back) captured once in a CUDA graph, one replay per step; "
+                        "camera + upstream pixel gradients from pinned host memory (step i+1's gradients are sent on a copy "
+                        "stream while step i runs), images copied to pinned host memory inside the graph; the Gaussian map "
+                        "is resident state") if graphed is not None else
+                       ("GaussianRasterizer autograd fwd+bwd; camera + upstream pixel gradients from pinned host memory, "
+                        "images read back (copies on a second stream, inside the timed step); the Gaussian map is "
+                        "resident state")},
         "gpu_launches": int(launches),
         "clocks": clocks,
         "wall_s": round(wall, 3),
     }
+    if e2e_eager_ms is not None:
+        # the same step without graph capture (eager autograd calls, reading the pair count back each step)
+        out["e2e"]["eager_value"] = round(N * n_ranks / (e2e_eager_ms / args.steps * 1e-3) / 1e6, 3)
     if impl == "ours":
         peak, how = measured_peaks()
         alg = algorithmic_bytes(P, V, R, N, Tn, C)
