@@ -282,8 +282,21 @@ def run_gpu(args, impl):
             pipe["sent"] = i + 1
             graphed.replay()
             if use_dist:
-                for t in leaves.values():
-                    dist.all_reduce(t.grad)
+                dist.all_reduce(graphed.trainable_grads())
+
+        def step_resident_graph(i):
+            """The resident step submitted as one graph replay: camera and upstream gradients are device
+            tensors, copied into the graph's static inputs by device copies."""
+            cam, g3 = cams[i % N_CAMERAS], grads[i % N_CAMERAS]
+            graphed.viewmatrix.copy_(cam.viewmatrix)
+            graphed.projmatrix.copy_(cam.projmatrix)
+            graphed.campos.copy_(cam.campos)
+            graphed.upstream[:C].copy_(g3[0])
+            graphed.upstream[C:C + 1].copy_(g3[1])
+            graphed.upstream[C + 1:].copy_(g3[2])
+            graphed.replay()
+            if use_dist:
+                dist.all_reduce(graphed.trainable_grads())
 
     def barrier():
         torch.cuda.synchronize()
@@ -343,12 +356,19 @@ def run_gpu(args, impl):
         from splatloc_b200 import _capi
         launches0 = _capi.load().sl_launch_count()
     sampler.lines.clear()    # keep only samples taken during the timed region
-    ms_total, wall, _ = timed(step_resident, args.steps, args.warmup)
+    if graphed is not None:
+        # kernels per step, counted on one eager step (a replay launches the same kernels, uncounted)
+        step_resident(0)
+        per_step = _capi.load().sl_launch_count() - launches0
+        ms_total, wall, _ = timed(step_resident_graph, args.steps, args.warmup)
+        launches = per_step * args.steps
+    else:
+        ms_total, wall, _ = timed(step_resident, args.steps, args.warmup)
+        launches = (_capi.load().sl_launch_count() - launches0) if impl == "ours" else 0
+        # the warm-up steps launched too; count only the timed ones
+        if impl == "ours":
+            launches = launches * args.steps // (args.steps + args.warmup)
     clocks = sampler.stop()
-    launches = (_capi.load().sl_launch_count() - launches0) if impl == "ours" else 0
-    # the warm-up steps launched too; count only the timed ones
-    if impl == "ours":
-        launches = launches * args.steps // (args.steps + args.warmup)
     e2e_ms, _, _ = timed(step_e2e_graph if graphed is not None else step_e2e, args.steps, args.warmup)
     e2e_eager_ms = None
     if graphed is not None:
@@ -371,7 +391,9 @@ def run_gpu(args, impl):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "impl": impl,
         "config": {"workload": WORKLOAD, "gaussians": P, "channels": C, "image": [W, H], "views_per_gpu_per_step": 1,
-                   "visible": V, "pairs": R, "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
+                   "visible": V, "pairs": R,
+                   "submission": "one CUDA-graph replay per step (splatloc_b200.graphs)" if graphed is not None else "eager calls",
+                   "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
                    "parallelism": f"views sharded over {n_ranks} GPU(s)" + (", NCCL all-reduce of the trainable-gradient span of the packed block (means3D, opacity, scales, rotations, colours)" if use_dist else "")},
         "e2e": {"value": round(e2e_value, 3), "unit": "Mpix/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "api": ("splatloc_b200.graphs.GraphedViewStep: the GaussianRasterizer autograd fwd+bwd (max_pairs / "

@@ -177,6 +177,12 @@ def rasterize_gaussians(background, means3D, colors, opacity, scales, rotations,
     return out
 
 
+def trainable_grad_numel(P: int, n_ch: int, M: int) -> int:
+    """Length of the leading span of the packed gradient block that holds the gradients of
+    means3D, opacity, scales, rotations and colours / SH (the blocks are 16-byte aligned)."""
+    return sum((P * w + 3) // 4 * 4 for w in (3, 1, 3, 4, n_ch, 3 * M))
+
+
 def _grad_block(P: int, widths: list[int], device) -> list[torch.Tensor]:
     """One zero-filled allocation (one memset) carved into per-gradient blocks.  The base tensor
     (`block._base`) carries `trainable_numel`: the length of its leading span that holds the

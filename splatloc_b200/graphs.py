@@ -100,3 +100,14 @@ class GraphedViewStep:
 
     def replay(self) -> None:
         self.graph.replay()
+
+    def trainable_grads(self) -> torch.Tensor:
+        """The gradients of means3D, opacity, scales, rotations and colours / SH of the last replay as ONE
+        flat tensor (they are the leading blocks of a single allocation): what a multi-GPU step
+        all-reduces.  Requires all of them to be leaves of this step."""
+        from ._C import trainable_grad_numel
+        g = self.params["means3D"].grad
+        shs = self.params.get("shs")
+        M = int(shs.shape[1]) if shs is not None else 0
+        n = trainable_grad_numel(int(g.shape[0]), self.C if shs is None else 3, M)
+        return g.as_strided((n,), (1,), g.storage_offset())
