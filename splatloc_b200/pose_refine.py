@@ -38,9 +38,11 @@ def se3_exp(tau: torch.Tensor) -> torch.Tensor:
     I3 = torch.eye(3, dtype=torch.float64, device=tau.device)
     R = I3 + A * K + B * (K @ K)
     V = I3 + B * K + Cc * (K @ K)
-    top = torch.cat([R, (V @ rho).reshape(3, 1)], 1)
-    bottom = torch.tensor([[0.0, 0.0, 0.0, 1.0]], dtype=torch.float64, device=tau.device)
-    return torch.cat([top, bottom], 0)
+    T = torch.zeros(4, 4, dtype=torch.float64, device=tau.device)   # (no host -> device copy: capturable)
+    T[:3, :3] = R
+    T[:3, 3] = V @ rho
+    T[3, 3].fill_(1.0)
+    return T
 
 
 def pose_error(w2c_a: torch.Tensor, w2c_b: torch.Tensor) -> tuple[float, float]:
@@ -86,6 +88,88 @@ class PoseRefiner:
         return GaussianRasterizer(rs)(means3D=g["means3D"], means2D=self.means2D, opacities=g["opacities"],
                                       colors_precomp=g["colors_precomp"], scales=g["scales"], rotations=g["rotations"],
                                       theta=theta, rho=rho)
+
+    # ------------------------------------------------------------------ one iteration as a CUDA graph
+    def _pair_capacity(self, w2c: torch.Tensor) -> int:
+        """Pairs of the view at `w2c` (one synchronising forward), doubled: room for the pose to move."""
+        from . import _C
+        view, full, campos = self.camera_tensors(w2c)
+        g, e = self.g, torch.Tensor([])
+        R = _C.rasterize_gaussians(self.bg, g["means3D"], g["colors_precomp"], g["opacities"], g["scales"], g["rotations"],
+                                   1.0, e, e.bool(), view, full, self.tanfovx, self.tanfovy, self.H, self.W, e, 0, campos,
+                                   False, False)[0]
+        return 2 * int(R) + 100_000
+
+    def _capture(self, w2c_init, target_color, target_depth, max_iters):
+        dev = self.device
+        st = self._state = {
+            "w2c": w2c_init.double().to(dev).clone(), "m": torch.zeros(6, dtype=torch.float64, device=dev),
+            "v": torch.zeros(6, dtype=torch.float64, device=dev), "t": torch.zeros((), dtype=torch.float64, device=dev),
+            "color": target_color.to(dev).clone(), "depth": target_depth.to(dev).clone(),
+            "losses": torch.zeros(max_iters, device=dev), "i": torch.zeros(1, dtype=torch.long, device=dev),
+            "overflow": torch.zeros(1, dtype=torch.int32, device=dev)}
+        cap = self._pair_capacity(st["w2c"])
+        g = self.g
+
+        def one_iteration():
+            theta = torch.zeros(3, device=dev, requires_grad=True)
+            rho = torch.zeros(3, device=dev, requires_grad=True)
+            view, full, campos = self.camera_tensors(st["w2c"])
+            rs = GaussianRasterizationSettings(self.H, self.W, self.tanfovx, self.tanfovy, self.bg, 1.0, view, full, 0,
+                                               campos, False, False)
+            rast = GaussianRasterizer(rs, max_pairs=cap)
+            color, depth, alpha, _ = rast(means3D=g["means3D"], means2D=self.means2D, opacities=g["opacities"],
+                                          colors_precomp=g["colors_precomp"], scales=g["scales"],
+                                          rotations=g["rotations"], theta=theta, rho=rho)
+            valid = (st["depth"] > 0).float()
+            loss = (color - st["color"]).abs().mean() + self.depth_weight * ((depth - st["depth"]).abs() * valid).mean()
+            loss.backward()
+            grad = torch.cat([rho.grad, theta.grad]).double()
+            st["t"].add_(1.0)
+            st["m"].mul_(0.9).add_(0.1 * grad)
+            st["v"].mul_(0.999).add_(0.001 * grad * grad)
+            m_hat = st["m"] / (1 - torch.pow(0.9, st["t"]))
+            v_hat = st["v"] / (1 - torch.pow(0.999, st["t"]))
+            st["w2c"].copy_(se3_exp(-(self.lr * m_hat / (v_hat.sqrt() + 1e-12))) @ st["w2c"])
+            st["losses"].index_copy_(0, st["i"], loss.detach().reshape(1))
+            st["i"].add_(1)
+            st["overflow"].copy_(torch.maximum(st["overflow"], rast.overflow))
+
+        snapshot = {k: v.clone() for k, v in st.items()}
+        with torch.cuda.device(dev):
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(2):
+                    one_iteration()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            self._graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._graph):
+                one_iteration()
+        for k, v in snapshot.items():
+            st[k].copy_(v)
+        self._graph_iters = max_iters
+
+    def refine_graphed(self, w2c_init: torch.Tensor, target_color: torch.Tensor, target_depth: torch.Tensor, iters: int = 100):
+        """`refine` with the whole iteration -- render (no pair-count read-back), loss, backward, Adam and the
+        SE(3) update -- captured once per refiner in a CUDA graph and replayed `iters` times: no host
+        work between kernels, one synchronisation at the end.  Same update rule, same results up to the
+        order of the atomic sums.  Falls back to `refine` if a frame exceeds the pair capacity chosen at
+        capture (twice the pairs of the first pose)."""
+        if getattr(self, "_graph", None) is None or self._graph_iters < iters:
+            self._capture(w2c_init, target_color, target_depth, iters)
+        st = self._state
+        st["w2c"].copy_(w2c_init.double())
+        st["color"].copy_(target_color)
+        st["depth"].copy_(target_depth)
+        for k in ("m", "v", "t", "losses", "i", "overflow"):
+            st[k].zero_()
+        for _ in range(iters):
+            self._graph.replay()
+        if int(st["overflow"]) != 0:
+            return self.refine(w2c_init, target_color, target_depth, iters)
+        return st["w2c"].clone(), list(st["losses"][:iters].clone())
 
     def refine(self, w2c_init: torch.Tensor, target_color: torch.Tensor, target_depth: torch.Tensor, iters: int = 100):
         """Adam (beta 0.9 / 0.999) on tau, re-linearised at every step.  Returns (w2c, [loss per iteration])."""

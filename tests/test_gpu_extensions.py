@@ -104,3 +104,15 @@ def test_pose_refinement_converges():
     e1 = pose_error(w2c, w2c_gt)
     assert float(losses[-1]) < 0.5 * float(losses[0]), (float(losses[0]), float(losses[-1]))
     assert e1[0] < 0.4 * e0[0] + 1e-4 and e1[1] < 0.4 * e0[1] + 1e-3, (e0, e1)
+
+    # the same refinement with every iteration replayed from one CUDA graph: same trajectory up to the
+    # order of the atomic sums, for this frame and for a second one through the cached graph
+    for seed in (1, 2):
+        start = perturb_pose(w2c_gt, seed=seed)
+        a, la = ref.refine(start, color.detach(), depth.detach(), iters=120)
+        b, lb = ref.refine_graphed(start, color.detach(), depth.detach(), iters=120)
+        assert abs(float(la[0]) - float(lb[0])) <= 1e-5 * abs(float(la[0]))
+        d = pose_error(a, b)
+        assert d[0] < 1e-3 and d[1] < 0.2, d      # 120 Adam steps amplify the summation-order noise
+        eb = pose_error(b, w2c_gt)
+        assert eb[0] < 0.4 * pose_error(start, w2c_gt)[0] + 1e-4, eb
