@@ -428,15 +428,24 @@ def run_gpu(args, impl):
                            "step_alg_MB": round(sum(alg.get(n, 0) for n in stages) / 1e6, 1),
                            "step_frac": round(sum(alg.get(n, 0) for n in stages) / (ms_step * 1e-3) / 1e9 / peak, 4)}
         out["stages"] = stages
-        if rank == 0 and not args.no_cpu_baseline:
+        if rank == 0 and world == 1 and not args.no_cpu_baseline:      # rank 0 at N = 1 only
             out["cpu_baseline"] = cpu_baseline(budget_s=args.cpu_budget)
     else:
         out["cpu_baseline"] = {"value": out["value"], "unit": "Mpix/s", "cores": 0, "kind": "reference",
                                "sample": "full workload; the reference path is CUDA-only, so this arm is the reference's own "
                                          "CUDA rasterizer (oracle/_ref, sm_100a) on the GPU, not host cores"}
     if world > 1:
-        dist.destroy_process_group()
+        finish_distributed(dist)
     return out if rank == 0 else None
+
+
+def finish_distributed(dist):
+    """All ranks are done with their collectives; the process then leaves through os._exit (see main):
+    tearing NCCL communicators and captured graphs down in the interpreter's shutdown has been seen to
+    hang 8-rank jobs after the result was printed."""
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
 
 
 def cpu_baseline(budget_s=20.0):
@@ -512,7 +521,7 @@ def run_pose_refine(args):
                       "mean_trans_err_m": [round(sum(e[0] for e in errs0) / len(errs0), 4), round(sum(e[0] for e in errs) / len(errs), 4)],
                       "mean_rot_err_deg": [round(sum(e[1] for e in errs0) / len(errs0), 3), round(sum(e[1] for e in errs) / len(errs), 3)]}}
     if world > 1:
-        dist.destroy_process_group()
+        finish_distributed(dist)
     return out if rank == 0 else None
 
 
@@ -585,6 +594,9 @@ def run_mapping_loss(args):
 
 
 def main():
+    world = env_int("WORLD_SIZE", 1)
+    if world > 1:     # the ranks share the host cores (scene generation runs on them)
+        torch.set_num_threads(max(1, (os.cpu_count() or world) // world))
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=100)
@@ -626,3 +638,6 @@ def main():
 
 if __name__ == "__main__":
     main()
+    sys.stdout.flush()
+    sys.stderr.flush()
+    os._exit(0)      # skip interpreter / NCCL / CUDA-graph teardown (see finish_distributed)
