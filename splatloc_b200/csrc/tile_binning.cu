@@ -278,117 +278,6 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
     }
 }
 
-#ifdef SL_SORT_COARSE
-// ---- experimental (off by default, NOT yet run on a GPU): 32-bit network + local fix-up -----------
-// The 64-bit network spends two shuffles, two compares and two selects per element and step.  Here
-// the network sorts 32-bit words  (depth bits with the low log2(N) bits replaced by the element's
-// index in the segment): half the work per step.  Elements whose depths agree in the remaining high
-// bits end up adjacent in arbitrary order; each then ranks itself inside its (short) run by the full
-// 64-bit key read back through the index.  Runs longer than COARSE_MAX_RUN make the CTA fall back
-// to the 64-bit network.  Shared memory: N x (8 + 4) bytes.
-constexpr int COARSE_MAX_RUN = 48;
-
-template <int E, int THREADS>
-__device__ __forceinline__ void cta_bitonic_sort32(uint32_t (&key)[E], uint32_t* smem, int tid)
-{
-    constexpr int N = E * THREADS;
-    const int lane = tid & 31;
-    const int wbase = (tid >> 5) * 32 * E + lane;
-#pragma unroll 1
-    for (int k = 2; k <= N; k <<= 1) {
-#pragma unroll 1
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            if (j >= 32 * E) {
-                __syncthreads();
-#pragma unroll
-                for (int r = 0; r < E; ++r) smem[wbase + 32 * r] = key[r];
-                __syncthreads();
-#pragma unroll
-                for (int r = 0; r < E; ++r) {
-                    const int g = wbase + 32 * r;
-                    const uint32_t other = smem[g ^ j];
-                    const bool take_max = ((g & j) == 0) != ((g & k) == 0);
-                    key[r] = take_max ? max(key[r], other) : min(key[r], other);
-                }
-            } else if (j >= 32) {
-#pragma unroll
-                for (int dr = E / 2; dr >= 1; dr >>= 1) {
-                    if (j == 32 * dr) {
-#pragma unroll
-                        for (int r = 0; r < E; ++r) {
-                            if ((r & dr) == 0) {
-                                const bool desc = ((wbase + 32 * r) & k) != 0;
-                                const uint32_t lo = min(key[r], key[r | dr]), hi = max(key[r], key[r | dr]);
-                                key[r] = desc ? hi : lo;
-                                key[r | dr] = desc ? lo : hi;
-                            }
-                        }
-                    }
-                }
-            } else {
-#pragma unroll
-                for (int r = 0; r < E; ++r) {
-                    const uint32_t other = __shfl_xor_sync(0xffffffffu, key[r], j);
-                    const bool take_max = ((lane & j) == 0) != (((wbase + 32 * r) & k) == 0);
-                    key[r] = take_max ? max(key[r], other) : min(key[r], other);
-                }
-            }
-        }
-    }
-}
-
-// In: key[r] = full key of segment element wbase + 32 r (~0 for padding).  Out: key[r] = full key of
-// the element the 32-bit network put at position wbase + 32 r, pos[r] = its final position in the
-// segment.  Returns false (for the whole CTA) if a run was too long; key[] is then unspecified.
-template <int E, int THREADS>
-__device__ __forceinline__ bool coarse_sort(unsigned long long (&key)[E], uint32_t (&pos)[E], unsigned long long* smem,
-                                            int tid)
-{
-    constexpr int N = E * THREADS;
-    constexpr uint32_t IDX = (uint32_t)N - 1u;          // N is a power of two
-    constexpr uint32_t PAD = 0xffffffffu;
-    unsigned long long* s_full = smem;
-    uint32_t* s_ck = reinterpret_cast<uint32_t*>(smem + N);
-    const int lane = tid & 31;
-    const int wbase = (tid >> 5) * 32 * E + lane;
-    uint32_t ck[E];
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
-        const uint32_t g = (uint32_t)(wbase + 32 * r);
-        s_full[g] = key[r];
-        ck[r] = key[r] == ~0ull ? PAD : (((uint32_t)(key[r] >> 32) & ~IDX) | g);
-    }
-    cta_bitonic_sort32<E, THREADS>(ck, s_ck, tid);
-    __syncthreads();
-#pragma unroll
-    for (int r = 0; r < E; ++r) s_ck[wbase + 32 * r] = ck[r];
-    __syncthreads();
-    bool too_long = false;
-#pragma unroll
-    for (int r = 0; r < E; ++r) {
-        const int g = wbase + 32 * r;
-        pos[r] = (uint32_t)g;
-        key[r] = ~0ull;
-        if (ck[r] == PAD) continue;
-        const uint32_t top = ck[r] & ~IDX;
-        const unsigned long long full = s_full[ck[r] & IDX];
-        int left = 0, right = 0, less = 0;
-        for (int j = g - 1; j >= 0 && (s_ck[j] & ~IDX) == top; --j) {      // (padding sorts last: never to the left)
-            less += s_full[s_ck[j] & IDX] < full;
-            if (++left > COARSE_MAX_RUN) { too_long = true; break; }
-        }
-        for (int j = g + 1; j < N && s_ck[j] != PAD && (s_ck[j] & ~IDX) == top; ++j) {
-            less += s_full[s_ck[j] & IDX] < full;
-            if (++right > COARSE_MAX_RUN) { too_long = true; break; }
-        }
-        pos[r] = (uint32_t)(g - left + less);
-        key[r] = full;
-    }
-    return __syncthreads_or(too_long) == 0;
-}
-#endif  // SL_SORT_COARSE
-
 // Sort one tile's segment (n <= E * THREADS pairs) and write every per-pair output.
 template <int C, int E, int THREADS>
 __device__ __forceinline__ void sort_and_emit_tile(
@@ -408,31 +297,13 @@ __device__ __forceinline__ void sort_and_emit_tile(
         const uint32_t g = wbase + 32 * r;
         key[r] = (g < n) ? ((keys_in[range.x + g] << 32) | (unsigned long long)vals_in[range.x + g]) : ~0ull;
     }
-#ifdef SL_SORT_COARSE
-    uint32_t pos[E];
-    if (!coarse_sort<E, THREADS>(key, pos, smem, tid)) {
-#pragma unroll
-        for (int r = 0; r < E; ++r) {
-            const uint32_t g = wbase + 32 * r;
-            pos[r] = g;
-            key[r] = (g < n) ? ((keys_in[range.x + g] << 32) | (unsigned long long)vals_in[range.x + g]) : ~0ull;
-        }
-        cta_bitonic_sort<E, THREADS>(key, smem, tid);
-    }
-#else
     cta_bitonic_sort<E, THREADS>(key, smem, tid);
-#endif
 
     const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
 #pragma unroll
     for (int r = 0; r < E; ++r) {
-#ifdef SL_SORT_COARSE
-        const uint32_t g = pos[r];
-        if (key[r] != ~0ull) {
-#else
         const uint32_t g = wbase + 32 * r;
         if (g < n) {
-#endif
             const unsigned long long k = key[r];
             const uint32_t id = (uint32_t)k;
             const uint32_t slot = range.x + g;
@@ -509,12 +380,6 @@ int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint
     return 0;
 }
 
-#ifdef SL_SORT_COARSE
-constexpr size_t SORT_SMEM_PER_KEY = sizeof(unsigned long long) + sizeof(uint32_t);
-#else
-constexpr size_t SORT_SMEM_PER_KEY = sizeof(unsigned long long);
-#endif
-
 template <int C>
 static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
                               const uint32_t* large_tiles, int n_tiles,
@@ -526,7 +391,7 @@ static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const ui
     // shared memory each; the 256-thread launch covers all tiles and skips those.
     if (info.n_large > 0) {
         constexpr int T = 1024;
-        const size_t smem = (size_t)TILE_SORT_LARGE * SORT_SMEM_PER_KEY;
+        const size_t smem = (size_t)TILE_SORT_LARGE * sizeof(unsigned long long);
         SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 "tile sort smem attribute");
         tile_sort_kernel<C, T><<<(int)info.n_large, T, smem, stream>>>(
@@ -539,7 +404,7 @@ static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const ui
     const uint32_t longest = info.max_pairs < (uint32_t)TILE_SORT_SMALL ? info.max_pairs : (uint32_t)TILE_SORT_SMALL;
     uint32_t pad = T;
     while (pad < longest) pad <<= 1;
-    tile_sort_kernel<C, T><<<n_tiles, T, (size_t)pad * SORT_SMEM_PER_KEY, stream>>>(
+    tile_sort_kernel<C, T><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
         ranges, tile_order, grid_x, 0u, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
         features, records, masks, dev_info);
     count_launch();
