@@ -46,10 +46,24 @@ const char* sl_last_error(void);
  * Replaces CudaRasterizer::required<GeometryState|BinningState|ImageState>
  * (DGR/cuda_rasterizer/rasterizer_impl.h:66-81).  The leading fields of each
  * chunk keep the reference layout (rasterizer_impl.cu:393-431), so
- * diff_gauss.interpret_{geom,binning,img}Buffer read them unchanged. */
+ * diff_gauss.interpret_{geom,binning,img}Buffer read them unchanged.
+ *
+ * Which fields of the chunks hold defined data after sl_forward (for debug tooling that reads them
+ * through interpret_*Buffer):
+ *   always:  geometry  depths, means2D, conic_opacity, tiles_touched (and cov3D / rgb / clamped when
+ *            they are computed), for Gaussians with radii > 0;
+ *            binning   point_list, point_list_keys (sorted);   image  ranges, n_contrib;
+ *   binning mode 1 only (sl_set_binning_mode): geometry point_offsets, and point_list_unsorted /
+ *            point_list_keys_unsorted in the reference's Gaussian-major emission order.  In the default
+ *            mode point_offsets is never written and the two "unsorted" arrays are grouped by tile;
+ *   no-read-back calls (sl_forward_nosync, sl_forward_batch with max_pairs >= 0): only the first R
+ *            entries of the binning arrays are filled; the rest up to max_pairs is undefined.
+ * The *_batch forms size the geometry and image chunks of a call that renders n_views cameras. */
 size_t sl_geometry_bytes(int P);
 size_t sl_binning_bytes(int R);
 size_t sl_image_bytes(int width, int height);
+size_t sl_geometry_bytes_batch(int P, int n_views);
+size_t sl_image_bytes_batch(int width, int height, int n_views);
 
 /* Forward rasterization.  Replaces CudaRasterizer::Rasterizer::forward
  * (DGR/cuda_rasterizer/rasterizer.h:134-159, rasterizer_impl.cu:435-582), which
@@ -142,7 +156,8 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
  * captured in a CUDA graph and replayed with no host work between its kernels.
  *   returns max_pairs: pass THAT as R to sl_backward[_ext] (it locates the chunk's arrays).
  *   status [1] (device int, required): 0 after the call's work has run, or 1 if the frame had more
- *     than max_pairs pairs or a tile with more than 4096 of them.  Then colour / depth / alpha are
+ *     than max_pairs pairs, a tile with more than 16384 of them, or more than 256 tiles with more than
+ *     4096.  Then colour / depth / alpha are
  *     background-only, n_contrib is 0 and the backward yields zero gradients: check the word when
  *     convenient and redo the frame with sl_forward_ext or a larger max_pairs.
  * Always uses the tile-bucket binning (sl_set_binning_mode does not apply).  debug is not available. */
@@ -171,6 +186,58 @@ int sl_backward_ext(int P, int D, int M, int R, int C,
                     float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
                     float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                     int debug, void* stream);
+
+/* ---- several cameras per call (no reference counterpart: the reference renders one camera per call
+ * and its callers loop, train_gaussians.py:195-229; the vestigial per-camera pose deltas are
+ * utils/camera_utils.py:141-143,179-180).  n_views cameras of ONE image size and field of view are
+ * rendered against the same Gaussians by the same seven launches a single view takes: tiles are
+ * numbered view-major (global tile = view * tiles_per_view + tile; the sorted keys carry the global
+ * number), one pair list holds all views.  Every per-view result is bit-identical to what the
+ * single-view call returns for that camera.
+ *
+ * sl_forward_batch: viewmatrices / projmatrices [n_views, 16], cam_positions [n_views, 3];
+ *   out_color [n_views, C, H, W], out_depth / out_alpha [n_views, H, W], radii [n_views, P] (may be NULL),
+ *   n_touched [n_views, P] | NULL; tile_mask (one, applied to every view) | NULL.
+ *   max_pairs < 0: read the total pair count back once (like sl_forward; status may be NULL, debug applies);
+ *   max_pairs >= 0: no read-back, capacity for all views together, status as in sl_forward_nosync.
+ *   Chunk sizes: sl_geometry_bytes_batch, sl_image_bytes_batch, sl_binning_bytes(total pairs).
+ *   Returns the total pair count (or max_pairs): pass it as R to sl_backward_batch.
+ *
+ * sl_backward_batch: dL_dpix [n_views, C, H, W], dL_dpix_depth / dL_dpix_alpha / accum_alphas [n_views, H, W].
+ *   Outputs, all ZERO on entry.  Per view (screen-space statistics and chain intermediates):
+ *     dL_dmean2D, dL_dabsmean2D [n_views, P, 3]   dL_dconic [n_views, P, 4]   dL_ddepth [n_views, P]
+ *     dL_dtau [n_views, 6] | NULL
+ *     dL_dcolor: [P, C] summed over the views with colors_precomp; [n_views, P, 3] with shs (a view's
+ *                colour gradient feeds that view's SH backward)
+ *   Summed over the views (what an optimiser consumes; each stored once, no atomics across views):
+ *     dL_dopacity [P]  dL_dmean3D [P, 3]  dL_dcov3D [P, 6]  dL_dsh [P, M, 3]  dL_dscale [P, 3]  dL_drot [P, 4]
+ *   dL_dmean3D == NULL: only dL_dtau is wanted (pose refinement against a fixed map); then dL_dcov3D,
+ *     dL_dsh, dL_dscale and dL_drot are not written and may be NULL. */
+int sl_forward_batch(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                     sl_alloc_fn binning_alloc, void* binning_ctx,
+                     sl_alloc_fn image_alloc, void* image_ctx,
+                     int n_views, int P, int D, int M, int C,
+                     const float* background, int width, int height,
+                     const float* means3D, const float* shs, const float* colors_precomp,
+                     const float* opacities, const float* scales, float scale_modifier,
+                     const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                     const float* viewmatrices, const float* projmatrices, const float* cam_positions,
+                     float tan_fovx, float tan_fovy, int prefiltered,
+                     float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                     int max_pairs, int* status, int debug, void* stream);
+int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
+                      const float* background, int width, int height,
+                      const float* means3D, const float* shs, const float* colors_precomp,
+                      const float* scales, float scale_modifier, const float* rotations,
+                      const float* cov3D_precomp, const float* viewmatrices, const float* projmatrices,
+                      const float* cam_positions, float tan_fovx, float tan_fovy, const int* radii,
+                      char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                      const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                      const float* dL_dpix_alpha,
+                      float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                      float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                      float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                      int debug, void* stream);
 
 /* Frustum visibility, present[i] in {0,1}.  Replaces
  * CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:71-76,
@@ -232,14 +299,14 @@ int sl_mapping_loss(int width, int height, int channels, const float* image, con
 /* Number of this library's kernels launched by the process so far. */
 long long sl_launch_count(void);
 
-/* Binning strategy of sl_forward (no reference counterpart; all strategies produce the reference's
- * sorted lists bit for bit, the switch exists so tests can cover each of them):
+/* Binning strategy of sl_forward (no reference counterpart; both strategies produce the reference's
+ * sorted lists bit for bit, the switch exists so tests can cover each of them).  The setting is
+ * PROCESS-WIDE: it changes the frames of every thread that calls sl_forward afterwards.
  *   0 = the library's default (currently 2);
  *   1 = prefix sum, Gaussian-major emit and one global radix sort (the reference's pipeline shape);
- *   2 = pairs scattered into per-tile segments, each segment sorted in shared memory by one CTA
- *       (falls back to 1 when a tile's list is too long for one CTA);
- *   3 = the visible Gaussians are sorted once by depth and every pair is written straight to its
- *       final list position (falls back to 2 when the tile grid is too large). */
+ *   2 = pairs scattered into per-tile segments, each segment sorted by one CTA with a bitonic network
+ *       held in registers (warp shuffles; shared memory only for the cross-warp steps); falls back to
+ *       1 when a tile's list is longer than the 16384 pairs one CTA sorts. */
 void sl_set_binning_mode(int mode);
 
 /* Per-stage device timing with CUDA events recorded on the caller's stream
@@ -247,7 +314,9 @@ void sl_set_binning_mode(int mode);
  * and starts accumulation, sl_profile_enable(0) stops it.  sl_profile_read
  * synchronises on the last recorded events and fills, for stage i <
  * sl_profile_stage_count(), the accumulated milliseconds and number of timed
- * calls.  Host-blocking; not for use inside latency-critical loops. */
+ * calls.  Host-blocking; not for use inside latency-critical loops.  The profiler is one
+ * process-wide object guarded by a mutex: enable it from one thread, for calls on ONE device
+ * (the device that is current at sl_profile_enable(1)); calls on other devices are not timed. */
 void sl_profile_enable(int on);
 int sl_profile_stage_count(void);
 const char* sl_profile_stage_name(int stage);

@@ -256,6 +256,161 @@ def rasterize_gaussians_backward(background, means3D, radii, colors, scales, rot
     return out + (g_tau,) if want_pose else out
 
 
+def rasterize_gaussians_batch(background, means3D, colors, opacity, scales, rotations, scale_modifier,
+                              cov3D_precomp, tile_mask, viewmatrices, projmatrices, tan_fovx, tan_fovy,
+                              image_height, image_width, sh, degree, campos, prefiltered, debug,
+                              want_n_touched=False, max_pairs=None):
+    """Several cameras in one call (sl_forward_batch; the reference renders one camera per call and its
+    callers loop, train_gaussians.py:195-229).  Arguments as `rasterize_gaussians`, except
+    `viewmatrices`, `projmatrices` (V, 4, 4) and `campos` (V, 3): V cameras of one image size.
+    -> (num_rendered over all views, color (V, C, H, W), depth (V, 1, H, W), alpha (V, 1, H, W),
+        radii (V, P), geomBuffer, binningBuffer, imgBuffer) [+ n_touched (V, P)] [+ status (1,)]
+    Each view's results are bit-identical to the single-view call's."""
+    if means3D.dim() != 2 or means3D.shape[1] != 3:
+        raise RuntimeError("means3D must have dimensions (num_points, 3)")
+    if viewmatrices.dim() != 3 or projmatrices.shape != viewmatrices.shape or tuple(viewmatrices.shape[1:]) != (4, 4):
+        raise RuntimeError("viewmatrices and projmatrices must have dimensions (num_views, 4, 4)")
+    lib = _capi.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (the rasterizer has no CPU path)")
+    dev = means3D.device
+    V, P, H, W = int(viewmatrices.shape[0]), int(means3D.shape[0]), int(image_height), int(image_width)
+    if V < 1 or campos.numel() != 3 * V:
+        raise RuntimeError(f"campos must have dimensions ({V}, 3)")
+
+    means3D = _f32(means3D, "means3D")
+    colors = _f32(colors, "colors_precomp")
+    opacity = _f32(opacity, "opacities")
+    scales = _f32(scales, "scales")
+    rotations = _f32(rotations, "rotations")
+    cov3D_precomp = _f32(cov3D_precomp, "cov3D_precomp")
+    sh = _f32(sh, "shs")
+    viewmatrices = _f32(viewmatrices, "viewmatrices")
+    projmatrices = _f32(projmatrices, "projmatrices")
+    campos = _f32(campos, "campos")
+    n_ch = _channels(colors)
+    background = _pad_bg(_f32(background, "bg"), n_ch)
+    if tile_mask is not None and tile_mask.numel() != 0:
+        if not tile_mask.is_cuda:
+            raise RuntimeError("tile_mask must be a CUDA tensor")
+        tile_mask = tile_mask.to(torch.bool).contiguous()
+        tiles = ((H + 15) // 16) * ((W + 15) // 16)
+        if tile_mask.numel() != tiles:
+            raise RuntimeError(f"tile_mask must have {tiles} elements, got {tile_mask.numel()}")
+    M = int(sh.shape[1]) if sh.numel() != 0 else 0
+
+    with _on_device(dev):
+        # one allocation [colour of all views | depth | alpha]: one device -> host copy moves them all
+        N = H * W
+        images = torch.empty(V * (n_ch + 2) * N, dtype=torch.float32, device=dev)
+        color = images[:V * n_ch * N].view(V, n_ch, H, W)
+        depth = images[V * n_ch * N:V * (n_ch + 1) * N].view(V, 1, H, W)
+        alpha = images[V * (n_ch + 1) * N:].view(V, 1, H, W)
+        radii = torch.empty((V, P), dtype=torch.int32, device=dev)
+        geom, binning, img = _chunks(dev)
+        n_touched = torch.zeros((V, P), dtype=torch.int32, device=dev) if want_n_touched else None
+        status = torch.empty(1, dtype=torch.int32, device=dev) if max_pairs is not None else None
+        rc = lib.sl_forward_batch(
+            geom.callback, None, binning.callback, None, img.callback, None,
+            V, P, int(degree), M, n_ch, _ptr(background), W, H,
+            _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(opacity), _ptr(scales), float(scale_modifier),
+            _ptr(rotations), _ptr(cov3D_precomp), _ptr(tile_mask),
+            _ptr(viewmatrices), _ptr(projmatrices), _ptr(campos),
+            float(tan_fovx), float(tan_fovy), int(bool(prefiltered)),
+            color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), _ptr(radii), _ptr(n_touched),
+            -1 if max_pairs is None else int(max_pairs), _ptr(status), int(bool(debug)), _stream(dev))
+        geom_t, binning_t, img_t = geom.take(), binning.take(), img.take()
+        rendered = _capi.check(rc)
+    out = (rendered, color, depth, alpha, radii, geom_t, binning_t, img_t)
+    if want_n_touched:
+        out = out + (n_touched,)
+    if status is not None:
+        out = out + (status,)
+    return out
+
+
+def _carve(flat: torch.Tensor, counts: list[int]) -> list[torch.Tensor]:
+    """Consecutive 16-byte-aligned slices of `flat` with the given element counts."""
+    out, off = [], 0
+    for n in counts:
+        out.append(flat[off:off + n])
+        off += (n + 3) // 4 * 4
+    return out
+
+
+def rasterize_gaussians_backward_batch(background, means3D, radii, colors, scales, rotations, scale_modifier,
+                                       cov3D_precomp, viewmatrices, projmatrices, tan_fovx, tan_fovy,
+                                       dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
+                                       geomBuffer, R, binningBuffer, imageBuffer, out_alpha, debug,
+                                       want_pose=False, pose_only=False):
+    """Backward of `rasterize_gaussians_batch` (sl_backward_batch).  Upstream gradients are (V, C, H, W),
+    (V, 1, H, W), (V, 1, H, W).
+    -> (dL_dabsmeans2D (V, P, 3), dL_dmeans2D (V, P, 3), dL_dcolors, dL_dopacity (P, 1), dL_dmeans3D (P, 3),
+        dL_dcov3D (P, 6), dL_dsh (P, M, 3), dL_dscales (P, 3), dL_drotations (P, 4)) [+ dL_dtau (V, 6)]
+    The per-Gaussian gradients are summed over the views; dL_dcolors is (P, C) (summed) with precomputed
+    colours and (V, P, 3) with SH.  `pose_only`: only dL_dtau is computed (a fixed map); the per-Gaussian
+    gradients come back as None."""
+    lib = _capi.load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    V, n_ch, H, W = (int(x) for x in dL_dout_color.shape)
+    M = int(sh.shape[1]) if sh.numel() != 0 else 0
+    with_sh = M != 0
+
+    means3D = _f32(means3D, "means3D")
+    colors = _f32(colors, "colors_precomp")
+    scales = _f32(scales, "scales")
+    rotations = _f32(rotations, "rotations")
+    cov3D_precomp = _f32(cov3D_precomp, "cov3D_precomp")
+    sh = _f32(sh, "shs")
+    dL_dout_color = _f32(dL_dout_color, "dL_dout_color")
+    dL_dout_depth = _f32(dL_dout_depth, "dL_dout_depth")
+    dL_dout_alpha = _f32(dL_dout_alpha, "dL_dout_alpha")
+    out_alpha = _f32(out_alpha, "out_alpha")
+    background = _pad_bg(_f32(background, "bg"), n_ch)
+    viewmatrices = _f32(viewmatrices, "viewmatrices")
+    projmatrices = _f32(projmatrices, "projmatrices")
+    campos = _f32(campos, "campos")
+    radii = radii.contiguous()
+    want_pose = want_pose or pose_only
+
+    with _on_device(dev):
+        # summed over the views, what an optimiser consumes first (one contiguous span for a multi-GPU
+        # all-reduce); then the per-view statistics and chain intermediates
+        n_color_sum = 0 if with_sh else P * n_ch
+        counts = [P * 3, P, P * 3, P * 4, n_color_sum, P * 3 * M, P * 6,
+                  V * P * 3, V * P * 3, V * P, V * P * 4, V * P * 3 if with_sh else 0]
+        if pose_only:       # nothing per Gaussian leaves the last stage
+            counts[0] = counts[2] = counts[3] = counts[5] = counts[6] = 0
+        flat = torch.zeros(sum((n + 3) // 4 * 4 for n in counts), dtype=torch.float32, device=dev)
+        (g_mean3D, g_opac, g_scale, g_rot, g_color_sum, g_sh, g_cov3D, g_mean2D, g_abs2D, g_depth, g_conic,
+         g_color_view) = _carve(flat, counts)
+        flat.trainable_numel = (flat.numel() if cov3D_precomp.numel() != 0
+                                else g_cov3D.storage_offset() - flat.storage_offset())
+        g_color = g_color_view if with_sh else g_color_sum
+        g_tau = torch.zeros((V, 6), dtype=torch.float32, device=dev) if want_pose else None
+        if P != 0:
+            rc = lib.sl_backward_batch(
+                V, P, int(degree), M, int(R), n_ch, _ptr(background), W, H,
+                _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(scales), float(scale_modifier), _ptr(rotations),
+                _ptr(cov3D_precomp), _ptr(viewmatrices), _ptr(projmatrices), _ptr(campos),
+                float(tan_fovx), float(tan_fovy), _ptr(radii),
+                _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
+                _ptr(out_alpha), _ptr(dL_dout_color), _ptr(dL_dout_depth), _ptr(dL_dout_alpha),
+                g_mean2D.data_ptr(), g_abs2D.data_ptr(), g_conic.data_ptr(), g_opac.data_ptr(),
+                g_color.data_ptr(), g_depth.data_ptr(), _ptr(g_mean3D), _ptr(g_cov3D),
+                _ptr(g_sh), _ptr(g_scale), _ptr(g_rot), _ptr(g_tau),
+                int(bool(debug)), _stream(dev))
+            _capi.check(rc)
+    colors_out = g_color.view(V, P, 3) if with_sh else g_color.view(P, n_ch)
+    if pose_only:
+        out = (g_abs2D.view(V, P, 3), g_mean2D.view(V, P, 3), colors_out, g_opac.view(P, 1), None, None, None, None, None)
+    else:
+        out = (g_abs2D.view(V, P, 3), g_mean2D.view(V, P, 3), colors_out, g_opac.view(P, 1), g_mean3D.view(P, 3),
+               g_cov3D.view(P, 6), g_sh.view(P, M, 3), g_scale.view(P, 3), g_rot.view(P, 4))
+    return out + (g_tau,) if want_pose else out
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """-> bool tensor (P,): inside the padded view frustum."""
     lib = _capi.load()

@@ -24,6 +24,8 @@ SIGNATURES = {
     "sl_geometry_bytes": (C.c_size_t, [C.c_int]),
     "sl_binning_bytes": (C.c_size_t, [C.c_int]),
     "sl_image_bytes": (C.c_size_t, [C.c_int, C.c_int]),
+    "sl_geometry_bytes_batch": (C.c_size_t, [C.c_int, C.c_int]),
+    "sl_image_bytes_batch": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
     "sl_forward": (C.c_int, [
         ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p,
         C.c_int, C.c_int, C.c_int, C.c_int,          # P, D, M, C
@@ -81,6 +83,32 @@ SIGNATURES = {
         _F, C.c_float, _F,                           # scales, scale_modifier, rotations
         _F, _F, _F,                                  # cov3D_precomp, viewmatrix, projmatrix
         _F, C.c_float, C.c_float, _F,                # campos, tan_fovx, tan_fovy, radii
+        _F, _F, _F,                                  # geometry, binning, image chunks
+        _F, _F, _F, _F,                              # accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha
+        _F, _F, _F, _F,                              # dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity
+        _F, _F, _F, _F,                              # dL_dcolor, dL_ddepth, dL_dmean3D, dL_dcov3D
+        _F, _F, _F, _F,                              # dL_dsh, dL_dscale, dL_drot, dL_dtau
+        C.c_int, C.c_void_p,                         # debug, stream
+    ]),
+    "sl_forward_batch": (C.c_int, [
+        ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p,
+        C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # n_views, P, D, M, C
+        _F, C.c_int, C.c_int,                        # background, width, height
+        _F, _F, _F,                                  # means3D, shs, colors_precomp
+        _F, _F, C.c_float,                           # opacities, scales, scale_modifier
+        _F, _F, _F,                                  # rotations, cov3D_precomp, tile_mask
+        _F, _F, _F,                                  # viewmatrices, projmatrices, cam_positions
+        C.c_float, C.c_float, C.c_int,               # tan_fovx, tan_fovy, prefiltered
+        _F, _F, _F, _F, _F,                          # out_color, out_depth, out_alpha, radii, n_touched
+        C.c_int, _F, C.c_int, C.c_void_p,            # max_pairs, status, debug, stream
+    ]),
+    "sl_backward_batch": (C.c_int, [
+        C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # n_views, P, D, M, R, C
+        _F, C.c_int, C.c_int,                        # background, width, height
+        _F, _F, _F,                                  # means3D, shs, colors_precomp
+        _F, C.c_float, _F,                           # scales, scale_modifier, rotations
+        _F, _F, _F,                                  # cov3D_precomp, viewmatrices, projmatrices
+        _F, C.c_float, C.c_float, _F,                # cam_positions, tan_fovx, tan_fovy, radii
         _F, _F, _F,                                  # geometry, binning, image chunks
         _F, _F, _F, _F,                              # accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha
         _F, _F, _F, _F,                              # dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity

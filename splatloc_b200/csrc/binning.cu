@@ -16,26 +16,30 @@ namespace sl {
 __global__ void __launch_bounds__(256)
 emit_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                   const uint32_t* __restrict__ offsets, const int* __restrict__ radii,
-                  const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y,
+                  const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y, int tiles_per_view,
                   uint64_t* __restrict__ keys, uint32_t* __restrict__ vals)
 {
-    int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= P) return;
-    const int r = radii[idx];
+    // blockIdx.y: the view.  The prefix sum runs over all (view, Gaussian) entries, view-major.
+    const size_t v = (size_t)blockIdx.y * P + idx;
+    const int r = radii[v];
     if (r <= 0) return;
 
-    uint32_t off = (idx == 0) ? 0 : offsets[idx - 1];
-    const uint32_t end = offsets[idx];
+    uint32_t off = (v == 0) ? 0 : offsets[v - 1];
+    const uint32_t end = offsets[v];
     if (off == end) return;  // visible radius but nothing to emit (masked out)
-    const float2 xy = means2D[idx];
+    const float2 xy = means2D[v];
     uint2 rmin, rmax;
     tile_rect(xy.x, xy.y, r, grid_x, grid_y, rmin, rmax);
-    const uint64_t depth_bits = __float_as_uint(depths[idx]);
+    const uint64_t depth_bits = __float_as_uint(depths[v]);
+    const uint64_t tile0 = (uint64_t)blockIdx.y * tiles_per_view;
 
     for (uint32_t y = rmin.y; y < rmax.y; y++) {
         for (uint32_t x = rmin.x; x < rmax.x; x++) {
             uint64_t key = y * grid_x + x;
             if (tile_mask != nullptr && !tile_mask[key]) continue;
+            key += tile0;
             key <<= 32;
             key |= depth_bits;
             keys[off] = key;
@@ -51,11 +55,11 @@ emit_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __rest
 // per-Gaussian arrays or point_list again: they stream `records` / `masks` linearly.
 template <int C>
 __global__ void __launch_bounds__(256)
-build_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
+build_records_kernel(int R, int P, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
                      const float2* __restrict__ means2D, const float* __restrict__ depths,
                      const float4* __restrict__ conic_opacity, const float* __restrict__ features,
-                     int grid_x, PairRecord* __restrict__ records, uint8_t* __restrict__ masks,
-                     uint2* __restrict__ ranges)
+                     size_t feature_view_stride, int grid_x, int tiles_per_view,
+                     PairRecord* __restrict__ records, uint8_t* __restrict__ masks, uint2* __restrict__ ranges)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= R) return;
@@ -71,9 +75,12 @@ build_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* _
     }
     if (i == R - 1) ranges[tile].y = R;
 
+    const uint32_t view = tile / (uint32_t)tiles_per_view, local_tile = tile - view * (uint32_t)tiles_per_view;
     const int id = point_list[i];
-    const float2 xy = means2D[id];
-    const float4 co = conic_opacity[id];
+    const size_t v = (size_t)view * P + id;
+    const float2 xy = means2D[v];
+    const float4 co = conic_opacity[v];
+    features += view * feature_view_stride;
     float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
     if (C == 4) {
         f = reinterpret_cast<const float4*>(features)[id];
@@ -83,36 +90,38 @@ build_records_kernel(int R, const uint64_t* __restrict__ keys, const uint32_t* _
         if (C > 2) f.z = features[id * C + 2];
     }
     PairRecord rec;
-    rec.xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float(id));
+    rec.xyd = make_float4(xy.x, xy.y, depths[v], __int_as_float(id));
     rec.co = co;
     rec.col = f;
     records[i] = rec;
-    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+    const int tile_x0 = (local_tile % grid_x) * SL_TILE_X, tile_y0 = (local_tile / grid_x) * SL_TILE_Y;
     masks[i] = (uint8_t)patch_mask(xy.x, xy.y, co, tile_x0, tile_y0);
 }
 
-int launch_build_records(int R, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
-                         const GeomState& g, const float* features, int grid_x, int n_tiles,
-                         PairRecord* records, uint8_t* masks, uint2* ranges, cudaStream_t stream)
+int launch_build_records(int R, int P, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
+                         const GeomState& g, const float* features, size_t feature_view_stride,
+                         const ViewParams& vp, PairRecord* records, uint8_t* masks, uint2* ranges,
+                         cudaStream_t stream)
 {
-    SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)n_tiles * sizeof(uint2), stream), "ranges memset");
+    SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)vp.tiles * vp.views * sizeof(uint2), stream), "ranges memset");
     if (R > 0) {
         if (C == 4)
-            build_records_kernel<4><<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, point_list, g.means2D, g.depths,
-                g.conic_opacity, features, grid_x, records, masks, ranges);
+            build_records_kernel<4><<<ceil_div(R, 256), 256, 0, stream>>>(R, P, sorted_keys, point_list, g.means2D,
+                g.depths, g.conic_opacity, features, feature_view_stride, vp.grid_x, vp.tiles, records, masks, ranges);
         else
-            build_records_kernel<3><<<ceil_div(R, 256), 256, 0, stream>>>(R, sorted_keys, point_list, g.means2D, g.depths,
-                g.conic_opacity, features, grid_x, records, masks, ranges);
+            build_records_kernel<3><<<ceil_div(R, 256), 256, 0, stream>>>(R, P, sorted_keys, point_list, g.means2D,
+                g.depths, g.conic_opacity, features, feature_view_stride, vp.grid_x, vp.tiles, records, masks, ranges);
         count_launch();
     }
     return 0;
 }
 
 int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
-                      int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream)
+                      const ViewParams& vp, uint64_t* keys, uint32_t* vals, cudaStream_t stream)
 {
-    emit_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii,
-                                                            tile_mask, grid_x, grid_y, keys, vals); count_launch();
+    const dim3 grid(ceil_div(P, 256), vp.views);
+    emit_pairs_kernel<<<grid, 256, 0, stream>>>(P, g.means2D, g.depths, g.point_offsets, radii, tile_mask, vp.grid_x,
+                                                vp.grid_y, vp.tiles, keys, vals); count_launch();
     return 0;
 }
 

@@ -62,16 +62,17 @@ template <int C>
 __global__ void __launch_bounds__(BLEND_THREADS, SL_BWD_MIN_CTAS)
 blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                       const PairRecord* __restrict__ records, const uint8_t* __restrict__ masks,
-                      int W, int H, int grid_x, const float* __restrict__ bg,
+                      int W, int H, int grid_x, int tiles_per_view, int P, const float* __restrict__ bg,
                       const float* __restrict__ out_alpha, const uint32_t* __restrict__ n_contrib,
                       const float* __restrict__ dL_dpix, const float* __restrict__ dL_dpix_depth,
                       const float* __restrict__ dL_dpix_alpha,
-                      float* __restrict__ dL_dmean2D,     // (P,3)
-                      float* __restrict__ dL_dabsmean2D,  // (P,3)
-                      float* __restrict__ dL_dconic,      // (P,4)
-                      float* __restrict__ dL_dopacity,    // (P,1)
-                      float* __restrict__ dL_dcolor,      // (P,C)
-                      float* __restrict__ dL_ddepth)      // (P,1)
+                      float* __restrict__ dL_dmean2D,     // (views,P,3)
+                      float* __restrict__ dL_dabsmean2D,  // (views,P,3)
+                      float* __restrict__ dL_dconic,      // (views,P,4)
+                      float* __restrict__ dL_dopacity,    // (P,1): summed over the views
+                      float* __restrict__ dL_dcolor,      // (P,C) + view * color_view_stride
+                      size_t color_view_stride,
+                      float* __restrict__ dL_ddepth)      // (views,P,1)
 {
     __shared__ PairRecord s_rec[BLEND_WARPS][BLEND_CHUNK];
     __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];
@@ -82,9 +83,23 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     __shared__ float s_ddep[BLEND_WARPS][32];                          // dL/dpix_depth per pixel
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = tile_order[blockIdx.x / BLEND_SUBS];
+    const int tile = tile_order[blockIdx.x / BLEND_SUBS];          // global (view-major) tile number
+    const int view = tile / tiles_per_view;
     const int patch = (blockIdx.x % BLEND_SUBS) * BLEND_WARPS + warp;
-    const PatchGeom pg = patch_geom(tile, grid_x, patch, lane);
+    const PatchGeom pg = patch_geom(tile - view * tiles_per_view, grid_x, patch, lane);
+    {   // this view's images and per-view gradient accumulators
+        const size_t N = (size_t)W * H, vP = (size_t)view * P;
+        out_alpha += (size_t)view * N;
+        n_contrib += (size_t)view * N;
+        dL_dpix += (size_t)view * C * N;
+        dL_dpix_depth += (size_t)view * N;
+        dL_dpix_alpha += (size_t)view * N;
+        dL_dmean2D += 3 * vP;
+        dL_dabsmean2D += 3 * vP;
+        dL_dconic += 4 * vP;
+        dL_ddepth += vP;
+        dL_dcolor += (size_t)view * color_view_stride;
+    }
     const int px = pg.px, py = pg.py;
     const bool inside = px < W && py < H;
     const uint32_t pix_id = (uint32_t)W * py + px;
@@ -297,22 +312,24 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
     }
 }
 
-int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+int launch_blend_backward(int P, int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                           const PairRecord* records, const uint8_t* masks, const float* bg,
                           const float* out_alpha, const uint32_t* n_contrib, const float* dL_dpix,
                           const float* dL_dpix_depth, const float* dL_dpix_alpha, float* dL_dmean2D,
                           float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
-                          float* dL_ddepth, cudaStream_t stream)
+                          size_t color_view_stride, float* dL_ddepth, cudaStream_t stream)
 {
-    const int tiles = vp.grid_x * vp.grid_y;
+    const int tiles = vp.tiles * vp.views;
     if (C == 4)
         blend_backward_kernel<4><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
-            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_alpha, n_contrib, dL_dpix,
-            dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
+            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, vp.tiles, P, bg, out_alpha, n_contrib, dL_dpix,
+            dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+            color_view_stride, dL_ddepth);
     else if (C == 3)
         blend_backward_kernel<3><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
-            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_alpha, n_contrib, dL_dpix,
-            dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth);
+            ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, vp.tiles, P, bg, out_alpha, n_contrib, dL_dpix,
+            dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+            color_view_stride, dL_ddepth);
     else {
         set_error("blend_backward: unsupported channel count %d (3 or 4)", C);
         return -2;

@@ -27,7 +27,7 @@ template <int C, bool TOUCH>
 __global__ void __launch_bounds__(BLEND_THREADS)
 blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tile_order,
                      const PairRecord* __restrict__ records, const uint8_t* __restrict__ masks,
-                     int W, int H, int grid_x, const float* __restrict__ bg,
+                     int W, int H, int grid_x, int tiles_per_view, int P, const float* __restrict__ bg,
                      float* __restrict__ out_color, float* __restrict__ out_depth,
                      float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
                      int* __restrict__ n_touched)
@@ -36,9 +36,10 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];   // chunk-relative index of each parked record
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tile = tile_order[blockIdx.x / BLEND_SUBS];
+    const int tile = tile_order[blockIdx.x / BLEND_SUBS];          // global (view-major) tile number
+    const int view = tile / tiles_per_view;
     const int patch = (blockIdx.x % BLEND_SUBS) * BLEND_WARPS + warp;
-    const PatchGeom pg = patch_geom(tile, grid_x, patch, lane);
+    const PatchGeom pg = patch_geom(tile - view * tiles_per_view, grid_x, patch, lane);
     const int px = pg.px, py = pg.py;
     const bool inside = px < W && py < H;
     const uint32_t pix_id = (uint32_t)W * py + px;
@@ -48,6 +49,14 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
 
     const uint2 range = ranges[tile];
     const int lo = range.x, hi = range.y;
+    {   // this view's images
+        const size_t N = (size_t)W * H;
+        out_color += (size_t)view * C * N;
+        out_depth += (size_t)view * N;
+        out_alpha += (size_t)view * N;
+        n_contrib += (size_t)view * N;
+        if (TOUCH) n_touched += (size_t)view * P;
+    }
 
     bool done = !inside;
     float T = 1.0f;
@@ -154,16 +163,16 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
     }
 }
 
-int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+int launch_blend_forward(int P, int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                          const PairRecord* records, const uint8_t* masks, const float* bg, float* out_color,
                          float* out_depth, float* out_alpha, uint32_t* n_contrib, int* n_touched,
                          cudaStream_t stream)
 {
-    const int tiles = vp.grid_x * vp.grid_y;
+    const int tiles = vp.tiles * vp.views;
 #define SL_LAUNCH_FWD(CC, TT)                                                                                    \
     blend_forward_kernel<CC, TT><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(                               \
-        ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, bg, out_color, out_depth, out_alpha, n_contrib, \
-        n_touched)
+        ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, vp.tiles, P, bg, out_color, out_depth, out_alpha, \
+        n_contrib, n_touched)
     if (C == 4) {
         if (n_touched) SL_LAUNCH_FWD(4, true); else SL_LAUNCH_FWD(4, false);
     } else if (C == 3) {

@@ -7,6 +7,7 @@
 // Rasterizer::backward (:586-692): blend backward -> per-Gaussian backward.
 // Everything is enqueued on the caller's stream.
 #include <atomic>
+#include <mutex>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -46,15 +47,17 @@ int check_stage(bool debug, cudaStream_t stream, const char* what)
 // (sl_profile_enable / sl_profile_read).  Off by default; when off the hot path
 // records nothing.
 enum Stage {
-    ST_PREPROCESS = 0, ST_SCAN, ST_DEPTH_SORT, ST_EMIT, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD,
+    ST_PREPROCESS = 0, ST_SCAN, ST_EMIT, ST_SORT, ST_RANGES, ST_BLEND_FWD, ST_BLEND_BWD,
     ST_PREPROCESS_BWD, ST_COUNT
 };
 static const char* const kStageNames[ST_COUNT] = {
-    "preprocess", "tile_scan", "depth_sort", "emit_pairs", "sort_pairs", "pair_records", "blend_forward",
+    "preprocess", "tile_scan", "emit_pairs", "sort_pairs", "pair_records", "blend_forward",
     "blend_backward", "preprocess_backward"};
 
 struct Profiler {
-    bool enabled = false;
+    std::mutex mu;            // guards everything below; taken only while profiling is enabled
+    std::atomic<bool> enabled{false};
+    int device = -1;          // the device that was current at sl_profile_enable(1): only its calls are timed
     bool created = false;
     cudaEvent_t ev[ST_COUNT][2];
     bool recorded[ST_COUNT] = {};
@@ -63,7 +66,7 @@ struct Profiler {
 };
 static Profiler g_prof;
 static std::atomic<long long> g_launches{0};
-static std::atomic<int> g_binning_mode{0};  // sl_set_binning_mode(): 0 default, 1 radix sort, 2 tile buckets, 3 ordered emit
+static std::atomic<int> g_binning_mode{0};  // sl_set_binning_mode(): 0 default, 1 radix sort, 2 tile buckets
 constexpr int kDefaultBinningMode = 2;
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
@@ -72,8 +75,13 @@ struct StageTimer {
     int st;
     cudaStream_t stream;
     bool on;
-    StageTimer(int st_, cudaStream_t s) : st(st_), stream(s), on(g_prof.enabled)
+    StageTimer(int st_, cudaStream_t s) : st(st_), stream(s), on(g_prof.enabled.load(std::memory_order_relaxed))
     {
+        if (!on) return;
+        int dev = -1;
+        cudaGetDevice(&dev);
+        std::lock_guard<std::mutex> lock(g_prof.mu);
+        on = dev == g_prof.device;
         if (!on) return;
         if (!g_prof.created) {
             for (int i = 0; i < ST_COUNT; ++i)
@@ -94,6 +102,7 @@ struct StageTimer {
     ~StageTimer()
     {
         if (!on) return;
+        std::lock_guard<std::mutex> lock(g_prof.mu);
         cudaEventRecord(g_prof.ev[st][1], stream);
         g_prof.recorded[st] = true;
     }
@@ -108,7 +117,7 @@ static int tile_id_bits(uint32_t n)
     return bits;
 }
 
-static ViewParams make_view(int width, int height, float tan_fovx, float tan_fovy, float scale_modifier)
+static ViewParams make_view(int width, int height, float tan_fovx, float tan_fovy, float scale_modifier, int views)
 {
     ViewParams vp;
     vp.W = width;
@@ -120,6 +129,8 @@ static ViewParams make_view(int width, int height, float tan_fovx, float tan_fov
     vp.focal_y = height / (2.0f * tan_fovy);
     vp.focal_x = width / (2.0f * tan_fovx);
     vp.scale_modifier = scale_modifier;
+    vp.views = views;
+    vp.tiles = vp.grid_x * vp.grid_y;
     return vp;
 }
 
@@ -157,7 +168,16 @@ long long sl_launch_count(void) { return g_launches.load(std::memory_order_relax
 
 void sl_profile_enable(int on)
 {
-    g_prof.enabled = on != 0;
+    std::lock_guard<std::mutex> lock(g_prof.mu);
+    int dev = -1;
+    cudaGetDevice(&dev);
+    if (on != 0 && g_prof.created && dev != g_prof.device) {   // events belong to the device they were made on
+        for (int i = 0; i < ST_COUNT; ++i)
+            for (int j = 0; j < 2; ++j) cudaEventDestroy(g_prof.ev[i][j]);
+        g_prof.created = false;
+    }
+    if (on != 0) g_prof.device = dev;
+    g_prof.enabled.store(on != 0, std::memory_order_relaxed);
     for (int i = 0; i < ST_COUNT; ++i) {
         g_prof.total_ms[i] = 0.0;
         g_prof.calls[i] = 0;
@@ -167,7 +187,7 @@ void sl_profile_enable(int on)
 
 void sl_set_binning_mode(int mode)
 {
-    g_binning_mode.store(mode >= 1 && mode <= 3 ? mode : 0, std::memory_order_relaxed);
+    g_binning_mode.store(mode >= 1 && mode <= 2 ? mode : 0, std::memory_order_relaxed);
 }
 
 int sl_profile_stage_count(void) { return ST_COUNT; }
@@ -176,6 +196,7 @@ const char* sl_profile_stage_name(int stage) { return (stage >= 0 && stage < ST_
 
 int sl_profile_read(double* total_ms, long long* calls, int n)
 {
+    std::lock_guard<std::mutex> lock(g_prof.mu);
     for (int i = 0; i < ST_COUNT && i < n; ++i) {
         if (g_prof.recorded[i]) {
             float ms = 0.f;
@@ -192,13 +213,19 @@ int sl_profile_read(double* total_ms, long long* calls, int n)
     return ST_COUNT;
 }
 
-size_t sl_geometry_bytes(int P) { return required_bytes<GeomState>((size_t)(P > 0 ? P : 0)); }
+size_t sl_geometry_bytes_batch(int P, int n_views)
+{
+    return required_bytes<GeomState>((size_t)(P > 0 ? P : 0), (size_t)(n_views > 0 ? n_views : 1));
+}
+size_t sl_geometry_bytes(int P) { return sl_geometry_bytes_batch(P, 1); }
 size_t sl_binning_bytes(int R) { return required_bytes<BinningState>((size_t)(R > 0 ? R : 0)); }
-size_t sl_image_bytes(int width, int height)
+size_t sl_image_bytes_batch(int width, int height, int n_views)
 {
     const size_t gx = (width + SL_TILE_X - 1) / SL_TILE_X, gy = (height + SL_TILE_Y - 1) / SL_TILE_Y;
-    return required_bytes<ImageState>((size_t)width * height, gx * gy);
+    const size_t v = (size_t)(n_views > 0 ? n_views : 1);
+    return required_bytes<ImageState>(v * width * height, v * gx * gy);
 }
+size_t sl_image_bytes(int width, int height) { return sl_image_bytes_batch(width, height, 1); }
 
 int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                sl_alloc_fn binning_alloc, void* binning_ctx,
@@ -219,12 +246,16 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                           prefiltered, out_color, out_depth, out_alpha, radii, nullptr, debug, stream_);
 }
 
+// Long-segment sort CTAs launched when the host cannot know how many tiles need them (no read-back).
+constexpr int kNosyncLargeTiles = 256;
+
+// `n_views` cameras of one image size per call; outputs and per-view state are laid out [view][...].
 // `max_pairs` < 0: the reference's protocol -- read R back, size the binning chunk exactly.
-// `max_pairs` >= 0 (sl_forward_nosync): the caller's capacity; no host synchronisation at all.
+// `max_pairs` >= 0 (no read-back): the caller's capacity; no host synchronisation at all.
 static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                         sl_alloc_fn binning_alloc, void* binning_ctx,
                         sl_alloc_fn image_alloc, void* image_ctx,
-                        int P, int D, int M, int C,
+                        int n_views, int P, int D, int M, int C,
                         const float* background, int width, int height,
                         const float* means3D, const float* shs, const float* colors_precomp,
                         const float* opacities, const float* scales, float scale_modifier,
@@ -238,8 +269,9 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     const bool nosync = max_pairs >= 0;
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool dbg = debug != 0;
-    if (P < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4)) {
-        set_error("sl_forward: bad sizes (P=%d, W=%d, H=%d, C=%d; C must be 3 or 4)", P, width, height, C);
+    if (P < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4) || n_views < 1) {
+        set_error("sl_forward: bad sizes (P=%d, W=%d, H=%d, C=%d, views=%d; C must be 3 or 4)", P, width, height, C,
+                  n_views);
         return SL_ERR_ARGUMENT;
     }
     if (!geometry_alloc || !binning_alloc || !image_alloc || !out_color || !out_depth || !out_alpha ||
@@ -247,7 +279,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         set_error("sl_forward: a required pointer is NULL");
         return SL_ERR_ARGUMENT;
     }
-    const size_t N = (size_t)width * height;
+    const size_t N = (size_t)width * height * n_views;     // pixels of all views
     if (P == 0) {
         // Nothing to draw: all-zero outputs, as the reference binding returns
         // (rasterize_points.cu:69-72,84).
@@ -257,7 +289,12 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         if (status != nullptr) SL_CUDA(cudaMemsetAsync(status, 0, sizeof(int), stream), "forward memset");
         return 0;
     }
-    if (n_touched != nullptr) SL_CUDA(cudaMemsetAsync(n_touched, 0, (size_t)P * sizeof(int), stream), "n_touched memset");
+    if ((long long)P * n_views >= (1ll << 31)) {
+        set_error("sl_forward: %d Gaussians x %d views exceed the 2^31 index range", P, n_views);
+        return SL_ERR_CAPACITY;
+    }
+    if (n_touched != nullptr)
+        SL_CUDA(cudaMemsetAsync(n_touched, 0, (size_t)P * n_views * sizeof(int), stream), "n_touched memset");
     if (!means3D || !opacities || (!cov3D_precomp && (!scales || !rotations))) {
         set_error("sl_forward: means3D, opacities and either cov3D_precomp or scales+rotations are required");
         return SL_ERR_ARGUMENT;
@@ -275,32 +312,30 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         return SL_ERR_ARGUMENT;
     }
 
-    const ViewParams vp = make_view(width, height, tan_fovx, tan_fovy, scale_modifier);
-    const int n_tiles = vp.grid_x * vp.grid_y;
+    const ViewParams vp = make_view(width, height, tan_fovx, tan_fovy, scale_modifier, n_views);
+    const int n_tiles = vp.tiles * n_views;                 // tiles of all views, numbered view-major
 
-    char* chunk = geometry_alloc(geometry_ctx, sl_geometry_bytes(P));
+    char* chunk = geometry_alloc(geometry_ctx, sl_geometry_bytes_batch(P, n_views));
     if (!chunk) { set_error("sl_forward: geometry allocation failed"); return SL_ERR_ALLOC; }
-    GeomState geom = GeomState::from_chunk(chunk, P);
+    GeomState geom = GeomState::from_chunk(chunk, P, n_views);
     if (radii == nullptr) radii = geom.internal_radii;
 
-    char* img_chunk = image_alloc(image_ctx, sl_image_bytes(width, height));
+    char* img_chunk = image_alloc(image_ctx, sl_image_bytes_batch(width, height, n_views));
     if (!img_chunk) { set_error("sl_forward: image allocation failed"); return SL_ERR_ALLOC; }
     ImageState img = ImageState::from_chunk(img_chunk, N, n_tiles);
 
     // Per-tile pair counters (one 128-byte line each), filled by preprocess.
     SL_CUDA(cudaMemsetAsync(img.tile_counts, 0, (size_t)n_tiles * TILE_COUNTER_STRIDE * sizeof(uint32_t), stream),
             "tile counter memset");
-    SL_CUDA(cudaMemsetAsync(img.bin_info, 0, sizeof(BinInfo), stream), "bin info memset");
     int mode = g_binning_mode.load(std::memory_order_relaxed);
     if (mode == 0) mode = kDefaultBinningMode;
     if (nosync) mode = 2;   // the only binning path whose launches do not depend on R
-    const bool want_ordered = mode == 3 && ordered_supported(n_tiles);
     int rc;
     {
         StageTimer t(ST_PREPROCESS, stream);
         rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
                                colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered != 0, radii,
-                               geom, img.tile_counts, want_ordered ? &img.bin_info->rect_tiles : nullptr, stream);
+                               geom, img.tile_counts, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess");
@@ -308,9 +343,9 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     {
         StageTimer t(ST_SCAN, stream);
         rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles,
-                              want_ordered ? geom.block_vis : nullptr, (int)geom.pre_blocks,
                               nosync ? (uint32_t)max_pairs : 0xffffffffu,
-                              nosync ? (uint32_t)TILE_SORT_SMALL : 0xffffffffu, status, stream);
+                              nosync ? (uint32_t)TILE_SORT_LARGE : 0xffffffffu,
+                              nosync ? (uint32_t)kNosyncLargeTiles : 0xffffffffu, status, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile scan");
@@ -319,8 +354,9 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     BinInfo info;
     if (nosync) {
         // No read-back: the chunk holds `max_pairs` pairs; tile_scan_kernel has flagged the frame on the
-        // device if it needs more (or has a tile list beyond the 256-thread segment sort), in which
-        // case the remaining stages do nothing.  Launch shapes below assume the worst admissible case.
+        // device if it needs more (or has a tile list beyond what one CTA sorts, or more long lists than
+        // the fixed launch below covers), in which case the remaining stages do nothing.  Launch shapes
+        // below assume the worst admissible case.
         memset(&info, 0, sizeof(info));
         info.num_pairs = (uint32_t)max_pairs;
         info.max_pairs = (uint32_t)TILE_SORT_SMALL;
@@ -334,64 +370,44 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     }
     const int R = (int)info.num_pairs;
 
-    // Binning, three interchangeable paths that produce the same sorted arrays:
-    //   3 depth-ordered emit (ordered_binning.cu): sort the visible Gaussians once, write
-    //     every pair straight to its final list position;
+    // Binning, two interchangeable paths that produce the same sorted arrays:
     //   2 tile buckets (tile_binning.cu): scatter pairs into their tile's segment, sort each segment
-    //     in shared memory -- taken when the tile grid is too large for the ordered emit's masks;
+    //     in registers / shared memory by one CTA;
     //   1 the reference's own pipeline shape -- prefix sum, Gaussian-major emit, global radix sort --
-    //     taken when a tile's list exceeds what one CTA sorts in shared memory.
-    const int V = (int)info.num_visible;
-    const bool ordered_path = want_ordered;
-    const size_t ordered_blocks = ordered_path ? (size_t)ordered_rows(info.rect_tiles) : 0;
-    const bool radix_path = !ordered_path && (info.n_huge > 0 || mode == 1);
+    //     taken when a tile's list exceeds what one CTA sorts.
+    const bool radix_path = info.n_huge > 0 || mode == 1;
 
-    const size_t bin_bytes = ordered_path ? required_bytes<BinningState>((size_t)R, (size_t)V, (size_t)n_tiles,
-                                                                         ordered_blocks)
-                                          : sl_binning_bytes(R);
-    char* bin_chunk = binning_alloc(binning_ctx, bin_bytes);
+    char* bin_chunk = binning_alloc(binning_ctx, sl_binning_bytes(R));
     if (!bin_chunk) { set_error("sl_forward: binning allocation failed"); return SL_ERR_ALLOC; }
-    BinningState bin = ordered_path ? BinningState::from_chunk(bin_chunk, R, V, n_tiles, ordered_blocks)
-                                    : BinningState::from_chunk(bin_chunk, R);
+    BinningState bin = BinningState::from_chunk(bin_chunk, R);
+    // colours the blend reads: the caller's (shared by all views) or this call's SH -> RGB results (per view)
     const float* features = colors_precomp != nullptr ? colors_precomp : geom.rgb;
+    const size_t feature_view_stride = colors_precomp != nullptr ? 0 : (size_t)3 * P;
 
-    if (R > 0 && ordered_path) {
-        {
-            StageTimer t(ST_DEPTH_SORT, stream);
-            rc = launch_depth_sort(P, V, geom, radii, vp.grid_x, vp.grid_y, bin, stream);
-        }
-        if (rc) return rc;
-        SL_STAGE(dbg, stream, "depth sort");
-        {
-            StageTimer t(ST_EMIT, stream);
-            rc = launch_ordered_emit(V, info.rect_tiles, C, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges,
-                                     features, bin, stream);
-        }
-        if (rc) return rc;
-        SL_STAGE(dbg, stream, "ordered emit");
-    } else
     if (R > 0 && !radix_path) {
         {
             StageTimer t(ST_EMIT, stream);
-            rc = launch_scatter_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, img.ranges, img.tile_counts,
+            rc = launch_scatter_pairs(P, geom, radii, tile_mask, vp, img.ranges, img.tile_counts,
                                       bin.point_list_keys_unsorted, bin.point_list_unsorted, img.bin_info, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "scatter pairs");
         {
             StageTimer t(ST_SORT, stream);
-            rc = launch_tile_sort(C, info, img.ranges, img.tile_order, img.large_tiles, n_tiles, vp.grid_x, bin.point_list_keys_unsorted,
+            rc = launch_tile_sort(P, C, info.max_pairs, nosync ? -kNosyncLargeTiles : (int)info.n_large, img.ranges,
+                                  img.tile_order, img.large_tiles, vp, bin.point_list_keys_unsorted,
                                   bin.point_list_unsorted, bin.point_list_keys, bin.point_list, geom, features,
-                                  bin.records, bin.masks, img.bin_info, stream);
+                                  feature_view_stride, bin.records, bin.masks, img.bin_info, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "tile sort");
     } else if (R > 0) {
         {
             StageTimer t(ST_EMIT, stream);
-            rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P, geom.scan_desc, geom.counters, stream);
+            rc = launch_inclusive_scan(geom.tiles_touched, geom.point_offsets, P * n_views, geom.scan_desc,
+                                       geom.counters, stream);
             if (rc == 0)
-                rc = launch_emit_pairs(P, geom, radii, tile_mask, vp.grid_x, vp.grid_y, bin.point_list_keys_unsorted,
+                rc = launch_emit_pairs(P, geom, radii, tile_mask, vp, bin.point_list_keys_unsorted,
                                        bin.point_list_unsorted, stream);
         }
         if (rc) return rc;
@@ -405,8 +421,8 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         SL_STAGE(dbg, stream, "sort");
         {
             StageTimer t(ST_RANGES, stream);
-            rc = launch_build_records(R, C, bin.point_list_keys, bin.point_list, geom, features, vp.grid_x, n_tiles,
-                                      bin.records, bin.masks, img.ranges, stream);
+            rc = launch_build_records(R, P, C, bin.point_list_keys, bin.point_list, geom, features,
+                                      feature_view_stride, vp, bin.records, bin.masks, img.ranges, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "pair records");
@@ -414,7 +430,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
 
     {
         StageTimer t(ST_BLEND_FWD, stream);
-        rc = launch_blend_forward(C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background, out_color,
+        rc = launch_blend_forward(P, C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background, out_color,
                                   out_depth, out_alpha, img.n_contrib, n_touched, stream);
     }
     if (rc) return rc;
@@ -435,7 +451,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                    float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
                    int debug, void* stream_)
 {
-    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, C,
+    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, 1, P, D, M, C,
                         background, width, height, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
                         rotations, cov3D_precomp, tile_mask, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
                         prefiltered, out_color, out_depth, out_alpha, radii, n_touched, debug, stream_, -1, nullptr);
@@ -458,11 +474,36 @@ int sl_forward_nosync(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         set_error("sl_forward_nosync: max_pairs >= 0 and a device status word are required");
         return SL_ERR_ARGUMENT;
     }
-    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, P, D, M, C,
+    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, 1, P, D, M, C,
                         background, width, height, means3D, shs, colors_precomp, opacities, scales, scale_modifier,
                         rotations, cov3D_precomp, tile_mask, viewmatrix, projmatrix, cam_pos, tan_fovx, tan_fovy,
                         prefiltered, out_color, out_depth, out_alpha, radii, n_touched, /*debug=*/0, stream_, max_pairs,
                         status);
+}
+
+int sl_forward_batch(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                     sl_alloc_fn binning_alloc, void* binning_ctx,
+                     sl_alloc_fn image_alloc, void* image_ctx,
+                     int n_views, int P, int D, int M, int C,
+                     const float* background, int width, int height,
+                     const float* means3D, const float* shs, const float* colors_precomp,
+                     const float* opacities, const float* scales, float scale_modifier,
+                     const float* rotations, const float* cov3D_precomp, const uint8_t* tile_mask,
+                     const float* viewmatrices, const float* projmatrices, const float* cam_positions,
+                     float tan_fovx, float tan_fovy, int prefiltered,
+                     float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
+                     int max_pairs, int* status, int debug, void* stream_)
+{
+    if (max_pairs >= 0 && status == nullptr) {
+        set_error("sl_forward_batch: max_pairs >= 0 (no read-back) needs a device status word");
+        return SL_ERR_ARGUMENT;
+    }
+    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, n_views, P, D,
+                        M, C, background, width, height, means3D, shs, colors_precomp, opacities, scales,
+                        scale_modifier, rotations, cov3D_precomp, tile_mask, viewmatrices, projmatrices, cam_positions,
+                        tan_fovx, tan_fovy, prefiltered, out_color, out_depth, out_alpha, radii, n_touched,
+                        max_pairs >= 0 ? 0 : debug, stream_, max_pairs < 0 ? -1 : max_pairs,
+                        max_pairs >= 0 ? status : nullptr);
 }
 
 int sl_backward(int P, int D, int M, int R, int C,
@@ -500,42 +541,83 @@ int sl_backward_ext(int P, int D, int M, int R, int C,
                     float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                     int debug, void* stream_)
 {
+    if (P > 0 && (!dL_dmean3D || !dL_dcov3D)) {
+        g_error[0] = 0;
+        set_error("sl_backward: a required pointer is NULL");
+        return SL_ERR_ARGUMENT;
+    }
+    return sl_backward_batch(1, P, D, M, R, C, background, width, height, means3D, shs, colors_precomp, scales,
+                             scale_modifier, rotations, cov3D_precomp, viewmatrix, projmatrix, campos, tan_fovx,
+                             tan_fovy, radii, geometry_chunk, binning_chunk, image_chunk, accum_alphas, dL_dpix,
+                             dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+                             dL_ddepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, debug, stream_);
+}
+
+int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
+                      const float* background, int width, int height,
+                      const float* means3D, const float* shs, const float* colors_precomp,
+                      const float* scales, float scale_modifier, const float* rotations,
+                      const float* cov3D_precomp, const float* viewmatrices, const float* projmatrices,
+                      const float* cam_positions, float tan_fovx, float tan_fovy, const int* radii,
+                      char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                      const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                      const float* dL_dpix_alpha,
+                      float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                      float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                      float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                      int debug, void* stream_)
+{
     g_error[0] = 0;
     cudaStream_t stream = (cudaStream_t)stream_;
     const bool dbg = debug != 0;
-    if (P < 0 || R < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4)) {
-        set_error("sl_backward: bad sizes (P=%d, R=%d, W=%d, H=%d, C=%d)", P, R, width, height, C);
+    if (P < 0 || R < 0 || width <= 0 || height <= 0 || (C != 3 && C != 4) || n_views < 1) {
+        set_error("sl_backward: bad sizes (P=%d, R=%d, W=%d, H=%d, C=%d, views=%d)", P, R, width, height, C, n_views);
         return SL_ERR_ARGUMENT;
     }
     if (P == 0) return 0;
     if (!geometry_chunk || !binning_chunk || !image_chunk || !accum_alphas || !dL_dpix || !dL_dpix_depth ||
         !dL_dpix_alpha || !dL_dmean2D || !dL_dabsmean2D || !dL_dconic || !dL_dopacity || !dL_dcolor ||
-        !dL_ddepth || !dL_dmean3D || !dL_dcov3D || !means3D || !background || !viewmatrix || !projmatrix) {
+        !dL_ddepth || !means3D || !background || !viewmatrices || !projmatrices) {
         set_error("sl_backward: a required pointer is NULL");
         return SL_ERR_ARGUMENT;
     }
-    if (scales != nullptr && (!rotations || !dL_dscale || !dL_drot)) {
+    // dL_dmean3D == NULL: the caller only wants the camera-pose gradients (pose refinement against a
+    // fixed map); then none of the per-Gaussian outputs of the last stage is written.
+    const bool pose_only = dL_dmean3D == nullptr;
+    if (pose_only && dL_dtau == nullptr) {
+        set_error("sl_backward: neither dL_dmean3D nor dL_dtau is wanted");
+        return SL_ERR_ARGUMENT;
+    }
+    if (!pose_only && !dL_dcov3D) {
+        set_error("sl_backward: dL_dcov3D is required with dL_dmean3D");
+        return SL_ERR_ARGUMENT;
+    }
+    if (!pose_only && scales != nullptr && (!rotations || !dL_dscale || !dL_drot)) {
         set_error("sl_backward: scales given without rotations / dL_dscale / dL_drot");
         return SL_ERR_ARGUMENT;
     }
-    if (shs != nullptr && (!dL_dsh || !campos || C != 3)) {
+    if (shs != nullptr && ((!pose_only && !dL_dsh) || !cam_positions || C != 3)) {
         set_error("sl_backward: SH gradients need dL_dsh, campos and C == 3");
         return SL_ERR_ARGUMENT;
     }
-    const ViewParams vp = make_view(width, height, tan_fovx, tan_fovy, scale_modifier);
-    const int n_tiles = vp.grid_x * vp.grid_y;
+    const ViewParams vp = make_view(width, height, tan_fovx, tan_fovy, scale_modifier, n_views);
+    const int n_tiles = vp.tiles * n_views;
 
-    GeomState geom = GeomState::from_chunk(geometry_chunk, P);
+    GeomState geom = GeomState::from_chunk(geometry_chunk, P, n_views);
     BinningState bin = BinningState::from_chunk(binning_chunk, R);
-    ImageState img = ImageState::from_chunk(image_chunk, (size_t)width * height, n_tiles);
+    ImageState img = ImageState::from_chunk(image_chunk, (size_t)width * height * n_views, n_tiles);
     if (radii == nullptr) radii = geom.internal_radii;
+    // With precomputed colours dL/dcolour is the same quantity in every view and is summed in place;
+    // SH colours depend on the view direction, so each view keeps its own (P, 3) block for the SH backward.
+    const size_t color_view_stride = shs != nullptr ? (size_t)3 * P : 0;
 
     int rc;
     {
         StageTimer t(ST_BLEND_BWD, stream);
-        rc = launch_blend_backward(C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background,
+        rc = launch_blend_backward(P, C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background,
                                    accum_alphas, img.n_contrib, dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D,
-                                   dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, dL_ddepth, stream);
+                                   dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor, color_view_stride, dL_ddepth,
+                                   stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend backward");
@@ -543,9 +625,10 @@ int sl_backward_ext(int P, int D, int M, int R, int C,
     const float* cov3D_ptr = (cov3D_precomp != nullptr) ? cov3D_precomp : geom.cov3D;
     {
         StageTimer t(ST_PREPROCESS_BWD, stream);
-        rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, scales, rotations, cov3D_ptr,
-                                        viewmatrix, projmatrix, campos, vp, dL_dmean2D, dL_dconic, dL_dmean3D,
-                                        dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, stream);
+        rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, pose_only ? nullptr : scales,
+                                        rotations, cov3D_ptr, viewmatrices, projmatrices, cam_positions, vp, dL_dmean2D,
+                                        dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D,
+                                        pose_only ? nullptr : dL_dsh, dL_dscale, dL_drot, dL_dtau, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess backward");

@@ -1,5 +1,10 @@
 // splatloc_b200/csrc/kernels.h -- host-side launchers of every stage.
 // Each returns 0 or a negative C-ABI error code (see include/splatloc_b200.h).
+//
+// Every stage handles `vp.views` cameras of the same image size in one launch (sl_forward_batch /
+// sl_backward_batch; the reference-shaped entry points pass 1).  Cameras are `views` consecutive
+// 16-float matrices / 3-float centres; per-view arrays are laid out [view][...]; tiles are numbered
+// view-major, global tile = view * vp.tiles + tile, and a pair's sort key carries the global number.
 #pragma once
 #include "common.cuh"
 #include "state.cuh"
@@ -12,15 +17,18 @@ struct ViewParams {
     float tan_fovx, tan_fovy;
     float focal_x, focal_y;
     float scale_modifier;
+    int views;   // cameras rendered by this call
+    int tiles;   // tiles per view (grid_x * grid_y)
 };
 
-// K1: per-Gaussian forward preprocess (reference: FORWARD::preprocess, forward.cu:995-1050).
+// K1: per-Gaussian forward preprocess (reference: FORWARD::preprocess, forward.cu:995-1050); also
+// counts the pairs of every tile for the tile-bucketed binning.
 int launch_preprocess(int P, int D, int M, int C, const float* means3D, const float* scales,
                       const float* rotations, const float* opacities, const float* shs,
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
-                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                      const float* viewmatrices, const float* projmatrices, const float* cam_positions,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      uint32_t* tile_counts, uint32_t* rect_tiles, cudaStream_t stream);
+                      uint32_t* tile_counts, cudaStream_t stream);
 
 // K10: frustum visibility (reference: checkFrustum, rasterizer_impl.cu:54-66).
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -32,73 +40,69 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned lon
 
 // K3: emit (tile | depth) keys and Gaussian ids (reference: duplicateWithKeys, rasterizer_impl.cu:70-132).
 int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
-                      int grid_x, int grid_y, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
+                      const ViewParams& vp, uint64_t* keys, uint32_t* vals, cudaStream_t stream);
 
 // ---- tile-bucketed binning (the default path; no counterpart in the reference, which sorts all
 // pairs globally): per-tile counts come out of preprocess, one CTA turns them into ranges, launch
 // order and the totals the host reads back; pairs are scattered straight into their tile's segment
-// and each segment is sorted on (depth bits, Gaussian id) in shared memory by one CTA, which also
-// writes the PairRecords and masks.  The result equals the stable global sort on (tile | depth).
+// and each segment is sorted on (depth bits, Gaussian id) by one CTA, which also writes the
+// PairRecords and masks.  The result equals the stable global sort on (tile | depth).
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, uint32_t* block_vis, int n_blocks, uint32_t max_pairs, uint32_t max_tile_pairs,
+                     int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, uint32_t max_large_tiles,
                      int* status, cudaStream_t stream);
-int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask, int grid_x,
-                         int grid_y, const uint2* ranges, uint32_t* cursors, uint64_t* keys, uint32_t* vals,
-                         const BinInfo* dev_info, cudaStream_t stream);
-int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
-                     const uint32_t* large_tiles, int n_tiles,
-                     int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
-                     uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
-                     uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream);
-
-// ---- depth-ordered emit (ordered_binning.cu): the visible Gaussians are sorted ONCE by depth and every
-// pair is then written straight to its final list position -- no per-tile sort.
-bool ordered_supported(int n_tiles);      // false: too many tiles for the per-CTA counters, use another path
-int ordered_rows(size_t rect_tiles);      // pair blocks (CTAs) for `rect_tiles` rectangle tiles
-int launch_depth_sort(int P, int V, const GeomState& g, const int* radii, int grid_x, int grid_y, BinningState& bin,
-                      cudaStream_t stream);
-int launch_ordered_emit(int V, size_t rect_tiles, int C, const GeomState& g, const int* radii,
-                        const uint8_t* tile_mask, int grid_x, int grid_y, const uint2* ranges, const float* features,
-                        BinningState& bin, cudaStream_t stream);
+int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
+                         const ViewParams& vp, const uint2* ranges, uint32_t* cursors, uint64_t* keys,
+                         uint32_t* vals, const BinInfo* dev_info, cudaStream_t stream);
+// `n_large_launch`: CTAs of the long-segment sort to launch (the exact count when the host knows it,
+// a fixed capacity in no-read-back mode: surplus CTAs leave at once).
+int launch_tile_sort(int P, int C, uint32_t longest, int n_large_launch, const uint2* ranges,
+                     const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
+                     const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                     uint32_t* point_list, const GeomState& g, const float* features, size_t feature_view_stride,
+                     PairRecord* records, uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream);
 
 // K4: stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit);
 // result in (keys_out, vals_out); the inputs are preserved.
-// `histograms_ready`: the caller ran sort_prepare() and accumulated the digit histograms itself.
 int sort_prepare(SortScratch& sc, int n, int end_bit, cudaStream_t stream);
 int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
-                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream,
-                      bool histograms_ready = false);
-int launch_inclusive_scan_keys_hi(const uint64_t* keys, uint32_t* out, int n, unsigned long long* desc,
-                                  uint32_t* ticket, cudaStream_t stream);
+                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream);
 
 // Gather, once per frame, everything the blend kernels read for each sorted pair (PairRecord) plus
 // the per-patch reach mask, and write the per-tile ranges (reference: identifyTileRanges).
-int launch_build_records(int R, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
-                         const GeomState& g, const float* features, int grid_x, int n_tiles,
-                         PairRecord* records, uint8_t* masks, uint2* ranges, cudaStream_t stream);
+int launch_build_records(int R, int P, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
+                         const GeomState& g, const float* features, size_t feature_view_stride,
+                         const ViewParams& vp, PairRecord* records, uint8_t* masks, uint2* ranges,
+                         cudaStream_t stream);
 
 // K6: forward alpha blending per 16x16 tile (reference: renderCUDA, forward.cu:844-963).
-int launch_blend_forward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+// Outputs are [views][...]: out_color [views, C, H, W], out_depth / out_alpha / n_contrib [views, H, W],
+// n_touched [views, P].
+int launch_blend_forward(int P, int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                          const PairRecord* records, const uint8_t* masks, const float* bg, float* out_color,
                          float* out_depth, float* out_alpha, uint32_t* n_contrib, int* n_touched,
                          cudaStream_t stream);
 
 // K7: backward blending (reference: BACKWARD::render, backward.cu:1018-1209).
-int launch_blend_backward(int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
+// Per view: dL_dmean2D / dL_dabsmean2D [views, P, 3], dL_dconic [views, P, 4], dL_ddepth [views, P],
+// dL_dcolor + view * color_view_stride; summed over the views: dL_dopacity [P].
+int launch_blend_backward(int P, int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                           const PairRecord* records, const uint8_t* masks, const float* bg,
                           const float* out_alpha, const uint32_t* n_contrib, const float* dL_dpix,
                           const float* dL_dpix_depth, const float* dL_dpix_alpha, float* dL_dmean2D,
                           float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
-                          float* dL_ddepth, cudaStream_t stream);
+                          size_t color_view_stride, float* dL_ddepth, cudaStream_t stream);
 
-// K8+K9 fused: per-Gaussian backward (reference: BACKWARD::preprocess, backward.cu:1810-1876).
+// K8+K9 fused: per-Gaussian backward (reference: BACKWARD::preprocess, backward.cu:1810-1876).  One
+// thread carries a Gaussian through all views and stores each gradient once (the sum over the views).
+// dL_dmean3D == nullptr: only the camera-pose gradients dL_dtau [views, 6] are wanted.
 int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
                                const float* shs, const uint8_t* clamped, const float* scales,
-                               const float* rotations, const float* cov3D, const float* viewmatrix,
-                               const float* projmatrix, const float* campos, const ViewParams& vp,
+                               const float* rotations, const float* cov3D, const float* viewmatrices,
+                               const float* projmatrices, const float* cam_positions, const ViewParams& vp,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
-                               float* dL_dcolor, const float* dL_ddepth, float* dL_dcov3D, float* dL_dsh,
-                               float* dL_dscale, float* dL_drot, float* dL_dtau, cudaStream_t stream);
+                               const float* dL_dcolor, size_t color_view_stride, const float* dL_ddepth,
+                               float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                               cudaStream_t stream);
 
 // K11-K15: mean squared distance to the 3 nearest neighbours (reference: SimpleKNN::knn,
 // simple_knn.cu:186-221).  `scratch` must hold knn_scratch_bytes(P) bytes.

@@ -7,7 +7,7 @@
 //     computeCov2D (:347-389) and computeColorFromSH (:20-71).
 // K10 frustum visibility (rasterizer_impl.cu:54-66).
 //
-// One thread per Gaussian, 256 threads per block; the kernel is HBM-bound
+// One thread per (Gaussian, view), 256 threads per block; the kernel is HBM-bound
 // (44 B in, 8 B + 52 B per visible Gaussian out) and carries no shared state.
 #include "kernels.h"
 #include "sh.cuh"
@@ -176,9 +176,10 @@ preprocess_one(int idx, int D, int M, int C,
 }
 
 
-// K1.  One thread per Gaussian; afterwards the pairs of every tile are counted for the tile-bucketed
-// binning (one counter per 128-byte line).  A Gaussian covering up to 8 tiles adds its own counts;
-// one covering more (near or very flat splats cover thousands) is counted by its whole warp.
+// K1.  One thread per (Gaussian, view): blockIdx.y is the view.  Afterwards the pairs of every tile
+// are counted for the tile-bucketed binning (one counter per 128-byte line, tiles numbered
+// view-major).  A Gaussian covering up to 8 tiles adds its own counts; one covering more (near or
+// very flat splats cover thousands) is counted by its whole warp.
 __global__ void __launch_bounds__(PREPROCESS_THREADS)
 preprocess_kernel(int P, int D, int M, int C,
                   const float* __restrict__ means3D,
@@ -189,9 +190,9 @@ preprocess_kernel(int P, int D, int M, int C,
                   const float* __restrict__ cov3D_precomp,
                   const uint8_t* __restrict__ tile_mask,
                   const float* __restrict__ colors_precomp,
-                  const float* __restrict__ viewmatrix,
-                  const float* __restrict__ projmatrix,
-                  const float* __restrict__ cam_pos,
+                  const float* __restrict__ viewmatrices,
+                  const float* __restrict__ projmatrices,
+                  const float* __restrict__ cam_positions,
                   ViewParams vp, bool prefiltered,
                   int* __restrict__ radii,
                   float2* __restrict__ means2D,
@@ -201,39 +202,31 @@ preprocess_kernel(int P, int D, int M, int C,
                   uint8_t* __restrict__ clamped,
                   float4* __restrict__ conic_opacity,
                   uint32_t* __restrict__ tiles_touched,
-                  uint32_t* __restrict__ tile_counts,
-                  uint32_t* __restrict__ block_vis,
-                  uint32_t* __restrict__ rect_tiles)
+                  uint32_t* __restrict__ tile_counts)
 {
     constexpr uint32_t SOLO_MAX = 8;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
+    // this view's camera and its slices of the per-view arrays (cov3Ds is view-independent and shared)
+    const size_t view = blockIdx.y, voff = view * (size_t)P;
+    const float* viewmatrix = viewmatrices + 16 * view;
+    const float* projmatrix = projmatrices + 16 * view;
+    const float* cam_pos = cam_positions != nullptr ? cam_positions + 3 * view : nullptr;
+    tile_counts += view * (size_t)vp.tiles * TILE_COUNTER_STRIDE;
     uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
     uint32_t touched = 0;
     if (idx < P) {
         touched = preprocess_one(idx, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
-                                 colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, means2D,
-                                 depths, cov3Ds, rgb, clamped, conic_opacity, rmin, rmax);
-        tiles_touched[idx] = touched;
-    }
-    if (tile_counts == nullptr) return;
-
-    if (block_vis != nullptr) {
-        // depth-ordered emit only: Gaussians of this CTA that reach the binning stage (their stable
-        // compaction is ordered_binning.cu's input)
-        const int n_vis = __syncthreads_count(touched != 0);
-        if (threadIdx.x == 0) block_vis[blockIdx.x] = (uint32_t)n_vis;
+                                 colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii + voff,
+                                 means2D + voff, depths + voff, cov3Ds, rgb + 3 * voff, clamped + 3 * voff,
+                                 conic_opacity + voff, rmin, rmax);
+        tiles_touched[voff + idx] = touched;
     }
 
     auto count = [&](uint32_t t) {
         if (tile_mask == nullptr || tile_mask[t]) atomicAdd(&tile_counts[(size_t)t * TILE_COUNTER_STRIDE], 1u);
     };
     const uint32_t area = touched ? (rmax.x - rmin.x) * (rmax.y - rmin.y) : 0u;
-    if (block_vis != nullptr) {
-        // all tiles inside the visible Gaussians' rectangles (the pair count unless a tile mask removes some)
-        const uint32_t warp_tiles = __reduce_add_sync(0xffffffffu, area);
-        if (lane == 0 && warp_tiles != 0) atomicAdd(rect_tiles, warp_tiles);
-    }
     if (area > 0 && area <= SOLO_MAX) {
         for (uint32_t y = rmin.y; y < rmax.y; y++)
             for (uint32_t x = rmin.x; x < rmax.x; x++) count(y * vp.grid_x + x);
@@ -262,14 +255,15 @@ mark_visible_kernel(int P, const float* __restrict__ means3D, const float* __res
 int launch_preprocess(int P, int D, int M, int C, const float* means3D, const float* scales,
                       const float* rotations, const float* opacities, const float* shs,
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
-                      const float* viewmatrix, const float* projmatrix, const float* cam_pos,
+                      const float* viewmatrices, const float* projmatrices, const float* cam_positions,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      uint32_t* tile_counts, uint32_t* rect_tiles, cudaStream_t stream)
+                      uint32_t* tile_counts, cudaStream_t stream)
 {
-    preprocess_kernel<<<ceil_div(P, PREPROCESS_THREADS), PREPROCESS_THREADS, 0, stream>>>(
+    const dim3 grid(ceil_div(P, PREPROCESS_THREADS), vp.views);
+    preprocess_kernel<<<grid, PREPROCESS_THREADS, 0, stream>>>(
         P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
-        colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii, g.means2D, g.depths,
-        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts, rect_tiles != nullptr ? g.block_vis : nullptr, rect_tiles); count_launch();
+        colors_precomp, viewmatrices, projmatrices, cam_positions, vp, prefiltered, radii, g.means2D, g.depths,
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts); count_launch();
     return 0;
 }
 

@@ -10,15 +10,20 @@
 //   + optional SH backward (colour -> SH coefficients and view direction),
 //   + optional 3D covariance -> scale / raw quaternion (no normalisation
 //     Jacobian, as in the reference, backward.cu:730).
-// Only Gaussians with radii > 0 are touched; all other rows keep the caller's
-// zeros.  HBM-bound: ~100 B in, 36..64 B out per visible Gaussian.
+// Only Gaussians with radii > 0 in some view are touched; all other rows keep the
+// caller's zeros.  HBM-bound: ~100 B in per (visible Gaussian, view), 36..64 B out
+// per Gaussian.  With several views per call (sl_backward_batch) the gradients of
+// a Gaussian are summed over the views before they are stored.
 #include "kernels.h"
 #include "sh.cuh"
 
 namespace sl {
 
-// One visible Gaussian.  `pose` (when wanted) receives this Gaussian's contribution to the gradient of
-// the loss w.r.t. a left perturbation Exp(rho, theta) of the world-to-camera transform.
+// One Gaussian in one view where it is visible.  The pointers are the view's slices of the per-view
+// arrays.  Its dL/dmean3D and dL/dcov3D are stored into (first == true) or added to the running sums
+// over the views, `g_mean_acc` / `g_cov_acc`; dL/dsh likewise goes to / adds to memory.  `pose` (when
+// wanted) receives this Gaussian's contribution to the gradient of the loss w.r.t. a left
+// perturbation Exp(rho, theta) of this view's world-to-camera transform.
 __device__ __forceinline__ void
 per_gaussian_backward(int idx, int D, int M, int C,
                            const float* __restrict__ means3D, const int* __restrict__ radii,
@@ -29,13 +34,10 @@ per_gaussian_backward(int idx, int D, int M, int C,
                            ViewParams vp,
                            const float* __restrict__ dL_dmean2D,  // (P,3)
                            const float* __restrict__ dL_dconics,  // (P,4)
-                           float* __restrict__ dL_dmeans,         // (P,3)
                            const float* __restrict__ dL_dcolor,   // (P,C)
                            const float* __restrict__ dL_ddepth,   // (P,1)
-                           float* __restrict__ dL_dcov,           // (P,6)
                            float* __restrict__ dL_dsh,            // (P,M,3)
-                           float* __restrict__ dL_dscale,         // (P,3)
-                           float* __restrict__ dL_drot,           // (P,4)
+                           bool first, f3& g_mean_acc, float (&g_cov_acc)[6],
                            bool want_pose, float (&pose)[6])
 {
     const float* cov3D = cov3Ds + 6 * idx;
@@ -94,7 +96,7 @@ per_gaussian_backward(int idx, int D, int M, int C,
         for (int i = 0; i < 6; i++) g_cov[i] = 0;
     }
 #pragma unroll
-    for (int i = 0; i < 6; i++) dL_dcov[6 * idx + i] = g_cov[i];
+    for (int i = 0; i < 6; i++) g_cov_acc[i] = first ? g_cov[i] : g_cov_acc[i] + g_cov[i];
 
     // gradients w.r.t. the upper 2x3 of T (cov2D = T^T Vrk^T T)
     const float dL_dT00 = 2 * (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_da +
@@ -196,7 +198,7 @@ per_gaussian_backward(int idx, int D, int M, int C,
     if (shs != nullptr) {
         f3 cp = {campos[0], campos[1], campos[2]};
         f3 dL_dRGB = {dL_dcolor[idx * C + 0], dL_dcolor[idx * C + 1], dL_dcolor[idx * C + 2]};
-        f3 g = sh_to_rgb_backward(idx, D, M, mean, cp, shs, clamped, dL_dRGB, dL_dsh);
+        f3 g = sh_to_rgb_backward(idx, D, M, mean, cp, shs, clamped, dL_dRGB, dL_dsh, !first);
         g_mean.x += g.x;
         g_mean.y += g.y;
         g_mean.z += g.z;
@@ -206,20 +208,27 @@ per_gaussian_backward(int idx, int D, int M, int C,
             pose[2] += view[2] * g.x + view[6] * g.y + view[10] * g.z;
         }
     }
-    dL_dmeans[3 * idx + 0] = g_mean.x;
-    dL_dmeans[3 * idx + 1] = g_mean.y;
-    dL_dmeans[3 * idx + 2] = g_mean.z;
+    g_mean_acc.x = first ? g_mean.x : g_mean_acc.x + g_mean.x;
+    g_mean_acc.y = first ? g_mean.y : g_mean_acc.y + g_mean.y;
+    g_mean_acc.z = first ? g_mean.z : g_mean_acc.z + g_mean.z;
+}
 
-    // ---------------------------------------------------------------- cov3D -> scale, rotation
-    if (scales != nullptr) {
+// dL/dcov3D (summed over the views) -> dL/dscale, dL/drotation.  The map from the covariance gradient
+// is linear and view-independent, so it runs once per Gaussian however many views there are.
+__device__ __forceinline__ void
+cov3d_to_scale_rot_backward(int idx, float scale_modifier, const float* __restrict__ scales,
+                            const float* __restrict__ rotations, const float (&g_cov)[6],
+                            float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+{
+    {
         const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
         const float r = q.x, x = q.y, y = q.z, z = q.w;
         mat3 R = mat3_cols(
             1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
             2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
             2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-        const f3 s = {vp.scale_modifier * scales[3 * idx], vp.scale_modifier * scales[3 * idx + 1],
-                      vp.scale_modifier * scales[3 * idx + 2]};
+        const f3 s = {scale_modifier * scales[3 * idx], scale_modifier * scales[3 * idx + 1],
+                      scale_modifier * scales[3 * idx + 2]};
         mat3 S = mat3_cols(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
         S.c[0][0] = s.x;
         S.c[1][1] = s.y;
@@ -262,60 +271,93 @@ per_gaussian_backward(int idx, int D, int M, int C,
     }
 }
 
-// 4 CTAs per SM (64 registers): the kernel waits on scattered loads, measured 27 us against 30 at 3 (80 registers)
-__global__ void __launch_bounds__(256, 4)
+// One thread per Gaussian, walking the views of the call: the Gaussian's gradients are summed over the
+// views in registers and stored once (rows that no view sees keep the caller's zeros), the camera-pose
+// gradient of every view is reduced over the CTA and leaves with one atomic per CTA, view and value.
+// One view: 4 CTAs per SM (64 registers; the kernel waits on scattered loads, measured 27 us against 30 at
+// 3 CTAs / 80 registers).  Several views: the running sums get 80 registers (at 64 they spill 256 bytes).
+#ifndef SL_PBWD_MULTI_CTAS
+#define SL_PBWD_MULTI_CTAS 3
+#endif
+template <bool MULTI>
+__global__ void __launch_bounds__(256, MULTI ? SL_PBWD_MULTI_CTAS : 4)
 preprocess_backward_kernel(int P, int D, int M, int C,
                            const float* __restrict__ means3D, const int* __restrict__ radii,
                            const float* __restrict__ shs, const uint8_t* __restrict__ clamped,
                            const float* __restrict__ scales, const float* __restrict__ rotations,
-                           const float* __restrict__ cov3Ds, const float* __restrict__ view,
-                           const float* __restrict__ proj, const float* __restrict__ campos,
+                           const float* __restrict__ cov3Ds, const float* __restrict__ viewmatrices,
+                           const float* __restrict__ projmatrices, const float* __restrict__ cam_positions,
                            ViewParams vp,
                            const float* __restrict__ dL_dmean2D, const float* __restrict__ dL_dconics,
                            float* __restrict__ dL_dmeans, const float* __restrict__ dL_dcolor,
-                           const float* __restrict__ dL_ddepth, float* __restrict__ dL_dcov,
-                           float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,
+                           size_t color_view_stride, const float* __restrict__ dL_ddepth,
+                           float* __restrict__ dL_dcov, float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,
                            float* __restrict__ dL_drot, float* dL_dtau)
 {
-    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
-    const bool want_pose = dL_dtau != nullptr;
-    float pose[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (idx < P && radii[idx] > 0)
-        per_gaussian_backward(idx, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3Ds, view, proj,
-                              campos, vp, dL_dmean2D, dL_dconics, dL_dmeans, dL_dcolor, dL_ddepth, dL_dcov, dL_dsh,
-                              dL_dscale, dL_drot, want_pose, pose);
-    if (!want_pose) return;
-
-    // 6 floats per view: warp shuffle, then shared memory across the 8 warps, one atomic per CTA and value
     __shared__ float s_pose[8][6];
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool want_pose = dL_dtau != nullptr;
+    f3 g_mean = {0.f, 0.f, 0.f};
+    float g_cov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    bool seen = false;
+    const int n_views = MULTI ? vp.views : 1;
+    for (int v = 0; v < n_views; ++v) {
+        const size_t vP = (size_t)v * P;
+        float pose[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (idx < P && radii[vP + idx] > 0) {
+            per_gaussian_backward(idx, D, M, C, means3D, radii, shs, clamped + 3 * vP, scales, rotations, cov3Ds,
+                                  viewmatrices + 16 * v, projmatrices + 16 * v,
+                                  cam_positions != nullptr ? cam_positions + 3 * v : nullptr, vp,
+                                  dL_dmean2D + 3 * vP, dL_dconics + 4 * vP, dL_dcolor + v * color_view_stride,
+                                  dL_ddepth + vP, dL_dsh, MULTI ? !seen : true, g_mean, g_cov, want_pose, pose);
+            seen = true;
+        }
+        if (want_pose) {
+            // 6 floats per view: warp shuffle, then shared memory across the 8 warps
 #pragma unroll
-    for (int k = 0; k < 6; ++k) {
-        float v = pose[k];
+            for (int k = 0; k < 6; ++k) {
+                float x = pose[k];
 #pragma unroll
-        for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-        if (lane == 0) s_pose[warp][k] = v;
+                for (int o = 16; o > 0; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+                if (lane == 0) s_pose[warp][k] = x;
+            }
+            __syncthreads();
+            if (threadIdx.x < 6) {
+                float x = 0.f;
+#pragma unroll
+                for (int w = 0; w < 8; ++w) x += s_pose[w][threadIdx.x];
+                if (x != 0.f) atomicAdd(&dL_dtau[6 * v + threadIdx.x], x);
+            }
+            __syncthreads();
+        }
     }
-    __syncthreads();
-    if (threadIdx.x < 6) {
-        float v = 0.f;
+    if (!seen || dL_dmeans == nullptr) return;   // dL_dmeans == nullptr: only the pose gradients were wanted
+    dL_dmeans[3 * idx + 0] = g_mean.x;
+    dL_dmeans[3 * idx + 1] = g_mean.y;
+    dL_dmeans[3 * idx + 2] = g_mean.z;
 #pragma unroll
-        for (int w = 0; w < 8; ++w) v += s_pose[w][threadIdx.x];
-        if (v != 0.f) atomicAdd(&dL_dtau[threadIdx.x], v);
-    }
+    for (int i = 0; i < 6; i++) dL_dcov[6 * idx + i] = g_cov[i];
+    if (scales != nullptr) cov3d_to_scale_rot_backward(idx, vp.scale_modifier, scales, rotations, g_cov, dL_dscale, dL_drot);
 }
 
 int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
                                const float* shs, const uint8_t* clamped, const float* scales,
-                               const float* rotations, const float* cov3D, const float* viewmatrix,
-                               const float* projmatrix, const float* campos, const ViewParams& vp,
+                               const float* rotations, const float* cov3D, const float* viewmatrices,
+                               const float* projmatrices, const float* cam_positions, const ViewParams& vp,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
-                               float* dL_dcolor, const float* dL_ddepth, float* dL_dcov3D, float* dL_dsh,
-                               float* dL_dscale, float* dL_drot, float* dL_dtau, cudaStream_t stream)
+                               const float* dL_dcolor, size_t color_view_stride, const float* dL_ddepth,
+                               float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                               cudaStream_t stream)
 {
-    preprocess_backward_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(
-        P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrix, projmatrix, campos,
-        vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, dL_ddepth, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau); count_launch();
+#define SL_LAUNCH_PBWD(MM)                                                                                       \
+    preprocess_backward_kernel<MM><<<ceil_div(P, 256), 256, 0, stream>>>(                                        \
+        P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrices, projmatrices,         \
+        cam_positions, vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D, \
+        dL_dsh, dL_dscale, dL_drot, dL_dtau)
+    if (vp.views > 1) SL_LAUNCH_PBWD(true); else SL_LAUNCH_PBWD(false);
+#undef SL_LAUNCH_PBWD
+    count_launch();
     return 0;
 }
 

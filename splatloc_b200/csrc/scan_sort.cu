@@ -52,8 +52,7 @@ __device__ __forceinline__ uint32_t warp_inclusive_scan(uint32_t v, int lane)
 constexpr unsigned long long SCAN_AGG = 1ull << 32;
 constexpr unsigned long long SCAN_INCL = 2ull << 32;
 
-// KEYS_HI: the addends are the high 32-bit words of an array of u64 (the tile counts that ride on
-// the depth keys of ordered_binning.cu) instead of a plain u32 array.
+// KEYS_HI: the addends are the high 32-bit words of an array of u64 instead of a plain u32 array.
 template <bool KEYS_HI>
 __global__ void __launch_bounds__(256)
 inclusive_scan_kernel(const uint32_t* __restrict__ in, uint32_t* __restrict__ out, int n,
@@ -351,18 +350,6 @@ int launch_inclusive_scan(const uint32_t* in, uint32_t* out, int n, unsigned lon
     return 0;
 }
 
-int launch_inclusive_scan_keys_hi(const uint64_t* keys, uint32_t* out, int n, unsigned long long* desc,
-                                  uint32_t* ticket, cudaStream_t stream)
-{
-    const int blocks = ceil_div(n, SCAN_ITEMS_PER_BLOCK);
-    SL_CUDA(cudaMemsetAsync(desc, 0, (size_t)(blocks + 1) * sizeof(unsigned long long), stream), "scan memset");
-    SL_CUDA(cudaMemsetAsync(ticket, 0, sizeof(uint32_t), stream), "scan memset");
-    inclusive_scan_kernel<true><<<blocks, 256, 0, stream>>>(reinterpret_cast<const uint32_t*>(keys), out, n, desc,
-                                                            ticket);
-    count_launch();
-    return 0;
-}
-
 size_t SortScratch::bytes(size_t n)
 {
     char* p = nullptr;
@@ -410,17 +397,14 @@ int sort_prepare(SortScratch& sc, int n, int end_bit, cudaStream_t stream)
 }
 
 int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
-                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream,
-                      bool histograms_ready)
+                      uint32_t* vals_out, SortScratch& sc, int n, int end_bit, cudaStream_t stream)
 {
     if (n <= 0) return 0;
     const int passes = (end_bit + SORT_RADIX_BITS - 1) / SORT_RADIX_BITS;
-    if (!histograms_ready) {
-        const int rc = sort_prepare(sc, n, end_bit, stream);
-        if (rc) return rc;
-        const int hist_blocks = min(ceil_div(n, 256 * 8), 148 * 8);
-        sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, /*aggregate_from=*/3, sc.histograms); count_launch();
-    }
+    const int rc = sort_prepare(sc, n, end_bit, stream);
+    if (rc) return rc;
+    const int hist_blocks = min(ceil_div(n, 256 * 8), 148 * 8);
+    sort_histogram_kernel<<<hist_blocks, 256, 0, stream>>>(keys_in, n, passes, /*aggregate_from=*/3, sc.histograms); count_launch();
     sort_scan_hist_kernel<<<passes, SORT_RADIX, 0, stream>>>(sc.histograms); count_launch();
     if (sort_items_per_block(n) == SORT_ITEMS_PER_BLOCK)
         return sort_passes<SORT_ITEMS_PER_BLOCK / SORT_THREADS>(keys_in, vals_in, keys_out, vals_out, sc, n, passes, stream);

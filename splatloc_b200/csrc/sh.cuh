@@ -81,7 +81,7 @@ __device__ __forceinline__ f3 sh_to_rgb(int idx, int deg, int max_coeffs, const 
 __device__ __forceinline__ f3 sh_to_rgb_backward(int idx, int deg, int max_coeffs, const f3& pos,
                                                  const f3& campos, const float* __restrict__ shs,
                                                  const uint8_t* __restrict__ clamped, f3 dL_dRGB,
-                                                 float* __restrict__ dL_dshs)
+                                                 float* __restrict__ dL_dshs, bool accumulate = false)
 {
     f3 d0 = {pos.x - campos.x, pos.y - campos.y, pos.z - campos.z};
     float len = sqrtf(d0.x * d0.x + d0.y * d0.y + d0.z * d0.z);
@@ -97,10 +97,11 @@ __device__ __forceinline__ f3 sh_to_rgb_backward(int idx, int deg, int max_coeff
     float* dsh = dL_dshs + (size_t)idx * max_coeffs * 3;
 #pragma unroll
     for (int k = 0; k < 16; ++k) {
-        if (k < n) {
-            dsh[3 * k + 0] = b[k] * dL_dRGB.x;
-            dsh[3 * k + 1] = b[k] * dL_dRGB.y;
-            dsh[3 * k + 2] = b[k] * dL_dRGB.z;
+        if (k < n && dL_dshs != nullptr) {   // nullptr: only the direction gradient is wanted
+            // `accumulate`: a later view of a multi-view call adds to what an earlier one stored
+            dsh[3 * k + 0] = b[k] * dL_dRGB.x + (accumulate ? dsh[3 * k + 0] : 0.f);
+            dsh[3 * k + 1] = b[k] * dL_dRGB.y + (accumulate ? dsh[3 * k + 1] : 0.f);
+            dsh[3 * k + 2] = b[k] * dL_dRGB.z + (accumulate ? dsh[3 * k + 2] : 0.f);
         }
     }
 

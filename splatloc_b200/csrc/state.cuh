@@ -28,7 +28,7 @@ constexpr int TILE_COUNTER_STRIDE = 32;      // u32 words between per-tile count
 constexpr int TILE_SORT_SMALL = 4096;        // pairs a 256-thread CTA sorts (16 keys per thread, 32 KB of smem)
 constexpr int TILE_SORT_LARGE = 16384;       // pairs a 1024-thread CTA sorts in 128 KB of shared memory
 
-constexpr int PREPROCESS_THREADS = 256;      // CTA size of preprocess (and of the visible-Gaussian compaction)
+constexpr int PREPROCESS_THREADS = 256;      // CTA size of preprocess
 
 // What the host reads back after the per-tile scan (one 32-byte copy).
 struct BinInfo {
@@ -36,10 +36,8 @@ struct BinInfo {
     uint32_t n_large;        // tiles with more than TILE_SORT_SMALL pairs
     uint32_t n_huge;         // tiles with more than TILE_SORT_LARGE pairs (-> radix-sort fallback)
     uint32_t max_pairs;      // longest tile list
-    uint32_t num_visible;    // V: Gaussians that touch at least one tile
-    uint32_t rect_tiles;     // A: tiles inside their rectangles (= R unless a tile mask removes some)
     uint32_t overflow;       // no-readback mode: R or a tile's list exceeds what the caller provided for
-    uint32_t pad[1];
+    uint32_t pad[3];
 };
 
 template <typename T>
@@ -51,44 +49,46 @@ __host__ __device__ inline void carve(char*& chunk, T*& ptr, size_t count, size_
 }
 
 struct GeomState {
+    // A call renders `views` cameras at once (sl_forward_batch; 1 for the reference-shaped entry
+    // points).  Per-view arrays are laid out [view][Gaussian]; with views == 1 the chunk is the
+    // reference's, field for field.
     // --- reference-compatible prefix ---
-    float* depths;            // [P]   view-space z (sort-key low word)
-    uint8_t* clamped;         // [3P]  SH colour clamp flags
-    int* internal_radii;      // [P]   used when the caller passes radii == nullptr
-    float2* means2D;          // [P]   pixel-space centre
-    float* cov3D;             // [6P]  upper triangle of the world covariance
-    float4* conic_opacity;    // [P]   (conic xx, xy, yy, opacity)
-    float* rgb;               // [3P]  SH -> RGB result (C == 3 only)
-    uint32_t* tiles_touched;  // [P]
-    uint32_t* point_offsets;  // [P]   inclusive prefix sum of tiles_touched
+    float* depths;            // [views * P]   view-space z (sort-key low word)
+    uint8_t* clamped;         // [views * 3P]  SH colour clamp flags
+    int* internal_radii;      // [views * P]   used when the caller passes radii == nullptr
+    float2* means2D;          // [views * P]   pixel-space centre
+    float* cov3D;             // [6P]          upper triangle of the world covariance (the same for every view)
+    float4* conic_opacity;    // [views * P]   (conic xx, xy, yy, opacity)
+    float* rgb;               // [views * 3P]  SH -> RGB result (C == 3 only)
+    uint32_t* tiles_touched;  // [views * P]
+    uint32_t* point_offsets;  // [views * P]   inclusive prefix sum of tiles_touched (radix-sort path only)
     // --- own scratch ---
     unsigned long long* scan_desc;  // [scan_blocks] decoupled look-back descriptors
     uint32_t* counters;             // [8] dynamic block tickets etc.
-    uint32_t* block_vis;            // [pre_blocks] visible Gaussians per preprocess CTA, then their exclusive scan
     size_t scan_blocks;
-    size_t pre_blocks;
 
-    static GeomState from_chunk(char*& chunk, size_t P)
+    static GeomState from_chunk(char*& chunk, size_t P, size_t views = 1)
     {
         GeomState g;
-        carve(chunk, g.depths, P);
-        carve(chunk, g.clamped, P * 3);
-        carve(chunk, g.internal_radii, P);
-        carve(chunk, g.means2D, P);
+        const size_t VP = views * P;
+        carve(chunk, g.depths, VP);
+        carve(chunk, g.clamped, VP * 3);
+        carve(chunk, g.internal_radii, VP);
+        carve(chunk, g.means2D, VP);
         carve(chunk, g.cov3D, P * 6);
-        carve(chunk, g.conic_opacity, P);
-        carve(chunk, g.rgb, P * 3);
-        carve(chunk, g.tiles_touched, P);
-        carve(chunk, g.point_offsets, P);
-        g.scan_blocks = (P + SCAN_ITEMS_PER_BLOCK - 1) / SCAN_ITEMS_PER_BLOCK;
+        carve(chunk, g.conic_opacity, VP);
+        carve(chunk, g.rgb, VP * 3);
+        carve(chunk, g.tiles_touched, VP);
+        carve(chunk, g.point_offsets, VP);
+        g.scan_blocks = (VP + SCAN_ITEMS_PER_BLOCK - 1) / SCAN_ITEMS_PER_BLOCK;
         carve(chunk, g.scan_desc, g.scan_blocks + 1);
         carve(chunk, g.counters, 8);
-        g.pre_blocks = (P + PREPROCESS_THREADS - 1) / PREPROCESS_THREADS;
-        carve(chunk, g.block_vis, g.pre_blocks + 1);
         return g;
     }
 };
 
+// `N` and `Tn` are the pixels and tiles of ALL views of the call (views * W * H, views * tiles per view);
+// tiles are numbered view-major: global tile = view * tiles_per_view + tile.
 struct ImageState {
     uint32_t* n_contrib;  // [N] last contributing list position per pixel
     uint2* ranges;        // [Tn] [first, last+1) in the sorted pair list
@@ -152,19 +152,8 @@ struct BinningState {
     PairRecord* records;     // [R] per sorted pair: everything the blend kernels read, gathered once
     uint8_t* masks;          // [R] bit w: the pair can reach the w-th 8x4 patch of its tile
     SortScratch sort;
-    // --- depth-ordered emit (ordered_binning.cu); present when the chunk was sized with V > 0 ---
-    uint64_t* vis_keys_in;   // [V] depth bits of the visible Gaussians in id order (sort input)
-    uint32_t* vis_ids_in;    // [V] their ids
-    uint64_t* vis_keys;      // [V] the same, sorted
-    uint32_t* vis_ids;       // [V] ids in (depth bits, id) order
-    uint32_t* pair_incl;     // [V] inclusive prefix sum of their tile counts: pair indices, Gaussian-major
-    uint16_t* block_hist;    // [rows * Tn] pairs of each 2048-pair block in each tile
-    uint32_t* block_base;    // [rows * Tn] list position of the block's first pair in each tile
-    SortScratch vis_sort;
-    size_t rows;
 
-    // `V`, `Tn`, `rows`: visible Gaussians, tiles and pair blocks of the ordered emit (0: not used)
-    static BinningState from_chunk(char*& chunk, size_t R, size_t V = 0, size_t Tn = 0, size_t rows = 0)
+    static BinningState from_chunk(char*& chunk, size_t R)
     {
         BinningState b;
         carve(chunk, b.point_list, R);
@@ -174,26 +163,6 @@ struct BinningState {
         carve(chunk, b.records, R);
         carve(chunk, b.masks, R + 64);   // slack: the blend kernels prefetch one 32-entry chunk ahead
         b.sort = SortScratch::from_chunk(chunk, R);
-        b.rows = rows;
-        if (V != 0) {
-            carve(chunk, b.vis_keys_in, V);
-            carve(chunk, b.vis_ids_in, V);
-            carve(chunk, b.vis_keys, V);
-            carve(chunk, b.vis_ids, V);
-            carve(chunk, b.pair_incl, V);
-            carve(chunk, b.block_hist, b.rows * Tn);
-            carve(chunk, b.block_base, b.rows * Tn);
-            b.vis_sort = SortScratch::from_chunk(chunk, V);
-        } else {
-            b.vis_keys_in = nullptr;
-            b.vis_ids_in = nullptr;
-            b.vis_keys = nullptr;
-            b.vis_ids = nullptr;
-            b.pair_incl = nullptr;
-            b.block_hist = nullptr;
-            b.block_base = nullptr;
-            b.vis_sort = SortScratch();
-        }
         return b;
     }
 };

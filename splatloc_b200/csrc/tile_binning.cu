@@ -27,10 +27,12 @@ namespace sl {
 #endif
 
 // ------------------------------------------------------------------ 2. per-tile scan (one CTA)
+// `n_tiles` counts the tiles of all views of the call (view-major numbering): one scan gives every
+// tile of every view its segment of the single pair list, and one launch order for all of them.
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
                  uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles,
-                 uint32_t* block_vis, int n_blocks, uint32_t max_pairs, uint32_t max_tile_pairs, int* status)
+                 uint32_t max_pairs, uint32_t max_tile_pairs, uint32_t max_large_tiles, int* status)
 {
     constexpr int NT = 1024;
     __shared__ uint32_t s_warp[32];
@@ -38,35 +40,6 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
     __shared__ uint32_t s_carry, s_max, s_large, s_huge;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
-    if (blockIdx.x == 1) {
-        // second CTA, in parallel: exclusive scan (in place) of the visible-Gaussian counts of the
-        // preprocess CTAs -- where each of them compacts its Gaussians to (ordered_binning.cu)
-        if (tid == 0) s_carry = 0;
-        __syncthreads();
-        for (int base = 0; base < n_blocks; base += NT) {
-            const int b = base + tid;
-            const uint32_t c = (b < n_blocks) ? block_vis[b] : 0u;
-            uint32_t incl = c;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) {
-                const uint32_t v = __shfl_up_sync(0xffffffffu, incl, o);
-                if (lane >= o) incl += v;
-            }
-            if (lane == 31) s_warp[warp] = incl;
-            __syncthreads();
-            uint32_t off = s_carry;
-            for (int w = 0; w < warp; ++w) off += s_warp[w];
-            if (b < n_blocks) block_vis[b] = off + incl - c;
-            __syncthreads();
-            if (tid == NT - 1) s_carry = off + incl;
-            __syncthreads();
-        }
-        if (tid == 0) {
-            block_vis[n_blocks] = s_carry;
-            info->num_visible = s_carry;
-        }
-        return;
-    }
     if (tid == 0) { s_carry = 0; s_max = 0; s_large = 0; s_huge = 0; }
     s_hist[tid] = 0;
     __syncthreads();
@@ -110,7 +83,7 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
     __syncthreads();
     // No-readback mode (sl_forward_nosync): the host sized the binning chunk without knowing R.  If
     // the frame does not fit, every later stage of this frame does nothing and the caller is told.
-    const bool overflow = s_carry > max_pairs || s_max > max_tile_pairs;
+    const bool overflow = s_carry > max_pairs || s_max > max_tile_pairs || s_large > max_large_tiles;
     if (tid == 0) {
         info->num_pairs = s_carry;
         info->n_large = s_large;
@@ -158,7 +131,7 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
 __global__ void __launch_bounds__(256)
 scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __restrict__ depths,
                      const uint32_t* __restrict__ tiles_touched, const int* __restrict__ radii,
-                     const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y,
+                     const uint8_t* __restrict__ tile_mask, int grid_x, int grid_y, int tiles_per_view,
                      const uint2* __restrict__ ranges, uint32_t* cursors,
                      uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, const BinInfo* __restrict__ info)
 {
@@ -166,21 +139,24 @@ scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __r
     if (info->overflow) return;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
+    const size_t voff = (size_t)blockIdx.y * P;                    // blockIdx.y: the view
+    const uint32_t tile0 = blockIdx.y * (uint32_t)tiles_per_view;  // its first global tile
     uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
     uint32_t depth_bits = 0, area = 0;
     if (idx < P) {
-        const int r = radii[idx];
-        if (r > 0 && tiles_touched[idx] != 0) {
-            const float2 xy = means2D[idx];
+        const int r = radii[voff + idx];
+        if (r > 0 && tiles_touched[voff + idx] != 0) {
+            const float2 xy = means2D[voff + idx];
             tile_rect(xy.x, xy.y, r, grid_x, grid_y, rmin, rmax);
-            depth_bits = __float_as_uint(depths[idx]);
+            depth_bits = __float_as_uint(depths[voff + idx]);
             area = (rmax.x - rmin.x) * (rmax.y - rmin.y);
         }
     }
     auto emit = [&](uint32_t t, uint32_t dbits, uint32_t id) {
         if (tile_mask != nullptr && !tile_mask[t]) return;
-        const uint32_t slot = ranges[t].x + atomicAdd(&cursors[(size_t)t * TILE_COUNTER_STRIDE], 1u);
-        keys[slot] = ((uint64_t)t << 32) | dbits;
+        const uint32_t gt = tile0 + t;
+        const uint32_t slot = ranges[gt].x + atomicAdd(&cursors[(size_t)gt * TILE_COUNTER_STRIDE], 1u);
+        keys[slot] = ((uint64_t)gt << 32) | dbits;
         vals[slot] = id;
     };
     if (area > 0 && area <= SOLO_MAX) {
@@ -281,7 +257,7 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
 // Sort one tile's segment (n <= E * THREADS pairs) and write every per-pair output.
 template <int C, int E, int THREADS>
 __device__ __forceinline__ void sort_and_emit_tile(
-    uint32_t tile, uint2 range, int grid_x, unsigned long long* smem,
+    uint32_t tile, uint32_t local_tile, uint2 range, int grid_x, unsigned long long* smem,
     const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float* __restrict__ depths,
@@ -299,7 +275,7 @@ __device__ __forceinline__ void sort_and_emit_tile(
     }
     cta_bitonic_sort<E, THREADS>(key, smem, tid);
 
-    const int tile_x0 = (tile % grid_x) * SL_TILE_X, tile_y0 = (tile / grid_x) * SL_TILE_Y;
+    const int tile_x0 = (local_tile % grid_x) * SL_TILE_X, tile_y0 = (local_tile / grid_x) * SL_TILE_Y;
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const uint32_t g = wbase + 32 * r;
@@ -329,26 +305,36 @@ __device__ __forceinline__ void sort_and_emit_tile(
     }
 }
 
-// One CTA per tile of `tiles[blockIdx.x]`; handles segments with min_len < n <= 16 * THREADS and
-// picks the network size from n.
+// One CTA per tile of `tiles[blockIdx.x]` (global, view-major tile numbers); handles segments with
+// min_len < n <= 16 * THREADS and picks the network size from n.  The per-Gaussian arrays are those
+// of the tile's view.
 template <int C, int THREADS>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? SL_SORT_MIN_CTAS : 1)
-tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tiles, int grid_x, uint32_t min_len,
+tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tiles, int n_listed, int grid_x,
+                 int tiles_per_view, int P, uint32_t min_len,
                  const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
                  const float2* __restrict__ means2D, const float* __restrict__ depths,
                  const float4* __restrict__ conic_opacity, const float* __restrict__ features,
+                 size_t feature_view_stride,
                  PairRecord* __restrict__ records, uint8_t* __restrict__ masks, const BinInfo* __restrict__ dev_info)
 {
     extern __shared__ __align__(16) unsigned long long s_key[];
     if (dev_info->overflow) return;
+    if (n_listed < 0 && blockIdx.x >= dev_info->n_large) return;    // long-segment launch sized by capacity
     const uint32_t tile = tiles[blockIdx.x];
     const uint2 range = ranges[tile];
     const uint32_t n = range.y - range.x;
     if (n <= min_len || n > 16u * THREADS) return;
+    const uint32_t view = tile / (uint32_t)tiles_per_view, local_tile = tile - view * (uint32_t)tiles_per_view;
+    const size_t voff = (size_t)view * P;
+    means2D += voff;
+    depths += voff;
+    conic_opacity += voff;
+    features += view * feature_view_stride;
 #define SL_SORT_CASE(EE)                                                                                         \
-    sort_and_emit_tile<C, EE, THREADS>(tile, range, grid_x, s_key, keys_in, vals_in, keys_out, point_list, means2D, \
-                                       depths, conic_opacity, features, records, masks)
+    sort_and_emit_tile<C, EE, THREADS>(tile, local_tile, range, grid_x, s_key, keys_in, vals_in, keys_out, point_list, \
+                                       means2D, depths, conic_opacity, features, records, masks)
     if (n <= 1u * THREADS) SL_SORT_CASE(1);
     else if (n <= 2u * THREADS) SL_SORT_CASE(2);
     else if (n <= 4u * THREADS) SL_SORT_CASE(4);
@@ -358,70 +344,77 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 }
 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, uint32_t* block_vis, int n_blocks, uint32_t max_pairs, uint32_t max_tile_pairs,
+                     int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, uint32_t max_large_tiles,
                      int* status, cudaStream_t stream)
 {
-    // the second CTA (offsets for the depth-ordered emit) only when that path is selected
-    tile_scan_kernel<<<block_vis != nullptr ? 2 : 1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info,
-                                                                        n_tiles, block_vis, n_blocks, max_pairs,
-                                                                        max_tile_pairs, status);
+    tile_scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles, max_pairs,
+                                             max_tile_pairs, max_large_tiles, status);
     count_launch();
     return 0;
 }
 
-int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask, int grid_x,
-                         int grid_y, const uint2* ranges, uint32_t* cursors, uint64_t* keys, uint32_t* vals,
-                         const BinInfo* dev_info, cudaStream_t stream)
+int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
+                         const ViewParams& vp, const uint2* ranges, uint32_t* cursors, uint64_t* keys,
+                         uint32_t* vals, const BinInfo* dev_info, cudaStream_t stream)
 {
-    scatter_pairs_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, g.means2D, g.depths, g.tiles_touched, radii,
-                                                               tile_mask, grid_x, grid_y, ranges, cursors, keys, vals,
-                                                               dev_info);
+    const dim3 grid(ceil_div(P, 256), vp.views);
+    scatter_pairs_kernel<<<grid, 256, 0, stream>>>(P, g.means2D, g.depths, g.tiles_touched, radii, tile_mask,
+                                                   vp.grid_x, vp.grid_y, vp.tiles, ranges, cursors, keys, vals,
+                                                   dev_info);
     count_launch();
     return 0;
 }
 
 template <int C>
-static int tile_sort_launches(const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
-                              const uint32_t* large_tiles, int n_tiles,
-                              int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const uint2* ranges,
+                              const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
+                              const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                               uint32_t* point_list, const GeomState& g, const float* features,
-                              PairRecord* records, uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream)
+                              size_t feature_view_stride, PairRecord* records, uint8_t* masks,
+                              const BinInfo* dev_info, cudaStream_t stream)
 {
+    const int n_tiles = vp.tiles * vp.views;
     // Long segments (work list written by tile_scan_kernel) get a 1024-thread CTA with 128 KB of
-    // shared memory each; the 256-thread launch covers all tiles and skips those.
-    if (info.n_large > 0) {
+    // shared memory each; the 256-thread launch covers all tiles and skips those.  n_large_launch < 0:
+    // the host does not know how many there are (no read-back) and launches -n_large_launch CTAs,
+    // of which the surplus leave at once.
+    if (n_large_launch != 0) {
         constexpr int T = 1024;
         const size_t smem = (size_t)TILE_SORT_LARGE * sizeof(unsigned long long);
         SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 "tile sort smem attribute");
-        tile_sort_kernel<C, T><<<(int)info.n_large, T, smem, stream>>>(
-            ranges, large_tiles, grid_x, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list, g.means2D,
-            g.depths, g.conic_opacity, features, records, masks, dev_info);
+        const int ctas = n_large_launch < 0 ? -n_large_launch : n_large_launch;
+        tile_sort_kernel<C, T><<<ctas, T, smem, stream>>>(
+            ranges, large_tiles, n_large_launch, vp.grid_x, vp.tiles, P, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in,
+            keys_out, point_list, g.means2D, g.depths, g.conic_opacity, features, feature_view_stride, records, masks,
+            dev_info);
         count_launch();
     }
     constexpr int T = 256;
     // shared memory is only touched by the cross-warp steps: size it for the longest short segment
-    const uint32_t longest = info.max_pairs < (uint32_t)TILE_SORT_SMALL ? info.max_pairs : (uint32_t)TILE_SORT_SMALL;
+    if (longest > (uint32_t)TILE_SORT_SMALL) longest = (uint32_t)TILE_SORT_SMALL;
     uint32_t pad = T;
     while (pad < longest) pad <<= 1;
     tile_sort_kernel<C, T><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
-        ranges, tile_order, grid_x, 0u, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
-        features, records, masks, dev_info);
+        ranges, tile_order, n_tiles, vp.grid_x, vp.tiles, P, 0u, keys_in, vals_in, keys_out, point_list, g.means2D,
+        g.depths, g.conic_opacity, features, feature_view_stride, records, masks, dev_info);
     count_launch();
     return 0;
 }
 
-int launch_tile_sort(int C, const BinInfo& info, const uint2* ranges, const uint32_t* tile_order,
-                     const uint32_t* large_tiles, int n_tiles,
-                     int grid_x, const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
-                     uint32_t* point_list, const GeomState& g, const float* features, PairRecord* records,
-                     uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream)
+int launch_tile_sort(int P, int C, uint32_t longest, int n_large_launch, const uint2* ranges,
+                     const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
+                     const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
+                     uint32_t* point_list, const GeomState& g, const float* features, size_t feature_view_stride,
+                     PairRecord* records, uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream)
 {
     if (C == 4)
-        return tile_sort_launches<4>(info, ranges, tile_order, large_tiles, n_tiles, grid_x, keys_in, vals_in, keys_out, point_list,
-                                     g, features, records, masks, dev_info, stream);
-    return tile_sort_launches<3>(info, ranges, tile_order, large_tiles, n_tiles, grid_x, keys_in, vals_in, keys_out, point_list, g,
-                                 features, records, masks, dev_info, stream);
+        return tile_sort_launches<4>(P, longest, n_large_launch, ranges, tile_order, large_tiles, vp, keys_in, vals_in,
+                                     keys_out, point_list, g, features, feature_view_stride, records, masks, dev_info,
+                                     stream);
+    return tile_sort_launches<3>(P, longest, n_large_launch, ranges, tile_order, large_tiles, vp, keys_in, vals_in,
+                                 keys_out, point_list, g, features, feature_view_stride, records, masks, dev_info,
+                                 stream);
 }
 
 }  // namespace sl

@@ -77,7 +77,8 @@ class _RasterizeGaussians(torch.autograd.Function):
 
         ctx.raster_settings = rs
         ctx.num_rendered = num_rendered
-        ctx.want_pose = theta is not None or rho is not None
+        ctx.pose = (theta is not None, rho is not None)     # which of the two placeholders were given
+        ctx.want_pose = ctx.pose[0] or ctx.pose[1]
         ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
                               geom, binning, img, alpha, means2D)
         ctx.mark_non_differentiable(radii)
@@ -100,7 +101,8 @@ class _RasterizeGaussians(torch.autograd.Function):
         (g_abs2D, g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales, g_rot) = res[:9]
         g_theta = g_rho = None
         if ctx.want_pose:   # extension: camera-pose gradient, (rho, theta) order in the C ABI
-            g_rho, g_theta = res[9][:3], res[9][3:]
+            g_rho = res[9][:3] if ctx.pose[1] else None       # an input that was None must get None back
+            g_theta = res[9][3:] if ctx.pose[0] else None
 
         # densification statistics read |dL/dmean2D| from this attribute
         means2D.absgrad = g_abs2D
@@ -172,6 +174,102 @@ class GaussianRasterizer(nn.Module):
         out = rasterize_gaussians(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
                                   cov3D_precomp, tile_mask, self.raster_settings, theta, rho,
                                   self.return_n_touched, self.max_pairs, status)
+        self.overflow = status[0] if status else None
+        return out
+
+
+# ------------------------------------------------------------------ several cameras per call
+class _RasterizeGaussiansBatch(torch.autograd.Function):
+    """V cameras of one image size in one call (sl_forward_batch / sl_backward_batch).  No counterpart
+    in the reference, whose callers loop over the cameras of a window (train_gaussians.py:195-229)."""
+
+    @staticmethod
+    def forward(ctx, means3D, means2D, sh, colors_precomp, opacities, scales, rotations, cov3Ds_precomp,
+                tile_mask, raster_settings, theta, rho, want_n_touched, max_pairs, status_out, pose_only):
+        rs = raster_settings
+        res = _C.rasterize_gaussians_batch(
+            rs.bg, means3D, colors_precomp, opacities, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            tile_mask, rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, rs.image_height, rs.image_width, sh,
+            rs.sh_degree, rs.campos, rs.prefiltered, rs.debug, want_n_touched, max_pairs)
+        (num_rendered, color, depth, alpha, radii, geom, binning, img) = res[:8]
+        if max_pairs is not None and status_out is not None:
+            status_out.append(res[-1])
+        ctx.raster_settings = rs
+        ctx.num_rendered = num_rendered
+        ctx.pose = (theta is not None, rho is not None)
+        ctx.pose_only = pose_only
+        ctx.save_for_backward(colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh,
+                              geom, binning, img, alpha, means2D)
+        ctx.mark_non_differentiable(radii)
+        if want_n_touched:
+            ctx.mark_non_differentiable(res[8])
+            return color, depth, alpha, radii, res[8]
+        return color, depth, alpha, radii
+
+    @staticmethod
+    def backward(ctx, grad_color, grad_depth, grad_alpha, _grad_radii, _grad_n_touched=None):
+        rs = ctx.raster_settings
+        (colors_precomp, means3D, scales, rotations, cov3Ds_precomp, radii, sh, geom, binning, img,
+         alpha, means2D) = ctx.saved_tensors
+        want_pose = ctx.pose[0] or ctx.pose[1]
+        res = _C.rasterize_gaussians_backward_batch(
+            rs.bg, means3D, radii, colors_precomp, scales, rotations, rs.scale_modifier, cov3Ds_precomp,
+            rs.viewmatrix, rs.projmatrix, rs.tanfovx, rs.tanfovy, grad_color, grad_depth, grad_alpha, sh,
+            rs.sh_degree, rs.campos, geom, ctx.num_rendered, binning, img, alpha, rs.debug, want_pose, ctx.pose_only)
+        (g_abs2D, g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales, g_rot) = res[:9]
+        g_theta = g_rho = None
+        if want_pose:
+            g_rho = res[9][:, :3] if ctx.pose[1] else None
+            g_theta = res[9][:, 3:] if ctx.pose[0] else None
+        means2D.absgrad = g_abs2D
+        if ctx.pose_only:
+            g_means2D = g_colors = g_opac = None
+        elif sh.numel() != 0:
+            g_colors = None       # per-view SH colour gradients are an intermediate, not an input's gradient
+        return (g_means3D, g_means2D, g_sh, g_colors, g_opac, g_scales, g_rot, g_cov3D, None, None,
+                g_theta, g_rho, None, None, None, None)
+
+
+class BatchedGaussianRasterizer(nn.Module):
+    """`GaussianRasterizer` for V cameras at once.  `raster_settings.viewmatrix` / `.projmatrix` are
+    (V, 4, 4) and `.campos` (V, 3) (same conventions per camera); image size, field of view, background
+    and SH degree are shared.  forward() returns color (V, C, H, W), depth (V, 1, H, W), alpha (V, 1, H, W),
+    radii (V, P) [, n_touched (V, P)]; each view equals what `GaussianRasterizer` returns for that camera,
+    bit for bit.  After backward the Gaussians' `.grad` hold the SUM over the views (one store per value,
+    no atomics across views), `means2D` -- a (V, P, 3) placeholder -- holds the per-view screen-space
+    gradients and `means2D.absgrad` their absolute counterparts, and `theta` / `rho` (V, 3) the per-view
+    camera-pose gradients.  `pose_only=True`: the map is fixed, only theta / rho receive gradients."""
+
+    def __init__(self, raster_settings: GaussianRasterizationSettings, return_n_touched: bool = False,
+                 max_pairs: int | None = None, pose_only: bool = False):
+        super().__init__()
+        self.raster_settings = raster_settings
+        self.return_n_touched = return_n_touched
+        self.max_pairs = max_pairs
+        self.pose_only = pose_only
+        self.overflow = None
+
+    def forward(self, means3D, means2D, opacities, shs=None, colors_precomp=None, scales=None,
+                rotations=None, cov3D_precomp=None, tile_mask=None, *, theta=None, rho=None):
+        if (shs is None) == (colors_precomp is None):
+            raise Exception('Please provide excatly one of either SHs or precomputed colors!')
+        has_sr = scales is not None or rotations is not None
+        if (cov3D_precomp is None and (scales is None or rotations is None)) or \
+                (cov3D_precomp is not None and has_sr):
+            raise Exception('Please provide exactly one of either scale/rotation pair or precomputed 3D covariance!')
+        if self.pose_only and theta is None and rho is None:
+            raise Exception('pose_only needs theta and/or rho')
+        none = torch.Tensor([])
+        shs = none if shs is None else shs
+        colors_precomp = none if colors_precomp is None else colors_precomp
+        scales = none if scales is None else scales
+        rotations = none if rotations is None else rotations
+        cov3D_precomp = none if cov3D_precomp is None else cov3D_precomp
+        tile_mask = none.bool() if tile_mask is None else tile_mask.bool()
+        status = []
+        out = _RasterizeGaussiansBatch.apply(means3D, means2D, shs, colors_precomp, opacities, scales, rotations,
+                                             cov3D_precomp, tile_mask, self.raster_settings, theta, rho,
+                                             self.return_n_touched, self.max_pairs, status, self.pose_only)
         self.overflow = status[0] if status else None
         return out
 

@@ -1,11 +1,11 @@
-"""CUDA-graph replay of one view's forward + backward through the rasterizer.
+"""CUDA-graph replay of a forward + backward step through the rasterizer, one or several views.
 
 The reference's forward blocks the host once per call to read the pair count back
 (`cuda_rasterizer/rasterizer_impl.cu:522`), so its training step cannot be captured; between that
 read, the Python glue and the autograd engine a step spends more host time than the GPU needs for
-its kernels.  `GaussianRasterizer(..., max_pairs=N)` (sl_forward_nosync) has no such read, so the
-whole step -- forward, optional device -> host copy of the images, backward -- is captured once and
-replayed with a single launch (there is no reference counterpart to cite).
+its kernels.  The no-read-back forward (sl_forward_nosync / sl_forward_batch with a pair capacity)
+has no such read, so the whole step -- forward, optional device -> host copy of the images, backward
+-- is captured once and replayed with a single launch (there is no reference counterpart to cite).
 
     step = GraphedViewStep(params, H, W, tanfovx, tanfovy, bg, max_pairs=2_000_000)
     for view in views:
@@ -13,6 +13,12 @@ replayed with a single launch (there is no reference counterpart to cite).
         step.upstream.copy_(dL_dimages)          # (C + 2, H, W): d loss / d (colour | depth | alpha)
         step.replay()
         ... params[k].grad, step.color, step.depth, step.alpha, step.radii, step.overflow ...
+
+`n_views=V` renders V cameras of the same size per replay with the batch entry points (the mapping
+loop's window of views, `train_gaussians.py:195-229`): the static inputs become `viewmatrices`
+(V, 4, 4), `projmatrices`, `campos` (V, 3) and `upstream_color` (V, C, H, W), `upstream_depth`,
+`upstream_alpha` (V, 1, H, W); the images get a leading view dimension and `params[k].grad` is the
+sum over the V views.
 
 `step.overflow` is a (1,) int32 device tensor: 1 if the frame had more than `max_pairs` pairs (then
 the images are background-only and the gradients zero); read it when convenient and redo that frame
@@ -22,92 +28,123 @@ from __future__ import annotations
 
 import torch
 
-from .diff_gauss import GaussianRasterizationSettings, GaussianRasterizer
+from . import _C, _capi
+
+_EMPTY = torch.Tensor([])
 
 
 class GraphedViewStep:
     def __init__(self, params: dict, H: int, W: int, tanfovx: float, tanfovy: float, bg: torch.Tensor,
                  max_pairs: int, sh_degree: int = 0, scale_modifier: float = 1.0, host_images: torch.Tensor | None = None,
-                 warmup: int = 3):
-        """`params`: leaf tensors `means3D`, `opacities`, `scales`, `rotations` and `colors_precomp` (P, C)
-        or `shs` (P, M, 3); those that require grad receive `.grad` on every replay.
-        `host_images`: optional pinned (C + 2, H, W) tensor; the images are copied into it inside the
-        graph, overlapped with the backward, and are complete when the replay is."""
+                 warmup: int = 3, n_views: int = 1):
+        """`params`: tensors `means3D`, `opacities`, `scales`, `rotations` and `colors_precomp` (P, C) or
+        `shs` (P, M, 3); after every replay their `.grad` is this step's gradient (a view of the step's
+        own packed block, `self.grad_block` -- overwritten by the next replay, not accumulated).
+        `max_pairs`: (tile, Gaussian) pair capacity of one replay, all views together.
+        `host_images`: optional pinned tensor of V * (C + 2) * H * W floats (for V = 1: (C + 2, H, W));
+        the images are copied into it inside the graph, overlapped with the backward, laid out
+        [colour of all views | depth | alpha], and are complete when the replay is."""
         self.params = params
         dev = params["means3D"].device
-        self.H, self.W = int(H), int(W)
+        self.H, self.W, self.V = int(H), int(W), int(n_views)
         self.max_pairs = int(max_pairs)
+        self.tanfovx, self.tanfovy = float(tanfovx), float(tanfovy)
+        self.bg, self.sh_degree, self.scale_modifier = bg, int(sh_degree), float(scale_modifier)
         colors = params.get("colors_precomp")
-        self.C = int(colors.shape[1]) if colors is not None else 3
+        self.C = C = int(colors.shape[1]) if colors is not None else 3
+        V, N = self.V, self.H * self.W
         # static inputs of the captured step
-        self.viewmatrix = torch.zeros(4, 4, device=dev)
-        self.projmatrix = torch.zeros(4, 4, device=dev)
-        self.campos = torch.zeros(3, device=dev)
-        self.upstream = torch.zeros(self.C + 2, self.H, self.W, device=dev)
-        self.means2D = torch.zeros_like(params["means3D"], requires_grad=True)
+        self.viewmatrices = torch.zeros(V, 4, 4, device=dev)
+        self.projmatrices = torch.zeros(V, 4, 4, device=dev)
+        self.cam_positions = torch.zeros(V, 3, device=dev)
+        self.upstream_flat = torch.zeros(V * (C + 2) * N, device=dev)
+        self.upstream_color = self.upstream_flat[:V * C * N].view(V, C, self.H, self.W)
+        self.upstream_depth = self.upstream_flat[V * C * N:V * (C + 1) * N].view(V, 1, self.H, self.W)
+        self.upstream_alpha = self.upstream_flat[V * (C + 1) * N:].view(V, 1, self.H, self.W)
+        if V == 1:      # single-view names: one camera, one packed (C + 2, H, W) gradient block
+            self.viewmatrix, self.projmatrix, self.campos = self.viewmatrices[0], self.projmatrices[0], self.cam_positions[0]
+            self.upstream = self.upstream_flat.view(C + 2, self.H, self.W)
         self.host_images = host_images
-        self._settings = GaussianRasterizationSettings(self.H, self.W, tanfovx, tanfovy, bg, scale_modifier,
-                                                       self.viewmatrix, self.projmatrix, sh_degree, self.campos, False, False)
+        if host_images is not None and host_images.numel() != V * (C + 2) * N:
+            raise ValueError(f"host_images must hold {V * (C + 2) * N} floats")
         self._side = torch.cuda.Stream(device=dev) if host_images is not None else None
         self.graph = None
         self.color = self.depth = self.alpha = self.radii = self.overflow = None
+        self.grad_block = None           # the packed gradient block of the captured backward (flat float32)
+        self.means2D_grad = self.means2D_absgrad = None
 
         with torch.cuda.device(dev):
             s = torch.cuda.Stream()
             s.wait_stream(torch.cuda.current_stream())
             with torch.cuda.stream(s):
                 for _ in range(max(1, warmup)):
-                    self._clear_grads()
                     self._step()
             torch.cuda.current_stream().wait_stream(s)
             torch.cuda.synchronize()
-            self._clear_grads()
+            lib = _capi.load()
+            n0 = lib.sl_launch_count()
             self.graph = torch.cuda.CUDAGraph()
             with torch.cuda.graph(self.graph):
-                self.color, self.depth, self.alpha, self.radii, self.overflow = self._step()
-
-    def _clear_grads(self):
-        for t in list(self.params.values()) + [self.means2D]:
-            if t is not None and t.requires_grad:
-                t.grad = None
+                self._step()
+            # every launch of the captured pass went through the library's launch counter
+            self.kernels_per_replay = int(lib.sl_launch_count() - n0)
+        self._bind_grads()
 
     def _step(self):
-        p = self.params
-        rast = GaussianRasterizer(self._settings, max_pairs=self.max_pairs)
-        color, depth, alpha, radii = rast(means3D=p["means3D"], means2D=self.means2D, opacities=p["opacities"],
-                                          shs=p.get("shs"), colors_precomp=p.get("colors_precomp"),
-                                          scales=p["scales"], rotations=p["rotations"])
+        p, V = self.params, self.V
+        shs = p.get("shs")
+        colors = p.get("colors_precomp")
+        shs = _EMPTY if shs is None else shs.detach()
+        colors = _EMPTY if colors is None else colors.detach()
+        means3D, scales, rot = p["means3D"].detach(), p["scales"].detach(), p["rotations"].detach()
+        fw = _C.rasterize_gaussians_batch(
+            self.bg, means3D, colors, p["opacities"].detach(), scales, rot, self.scale_modifier, _EMPTY, _EMPTY.bool(),
+            self.viewmatrices, self.projmatrices, self.tanfovx, self.tanfovy, self.H, self.W, shs, self.sh_degree,
+            self.cam_positions, False, False, False, self.max_pairs)
+        R, color, depth, alpha, radii, geom, binning, img, status = fw
         if self.host_images is not None:
             main = torch.cuda.current_stream()
             self._side.wait_stream(main)
             with torch.cuda.stream(self._side):
-                C = self.C
-                self.host_images[:C].copy_(color.detach(), non_blocking=True)
-                self.host_images[C:C + 1].copy_(depth.detach(), non_blocking=True)
-                self.host_images[C + 1:].copy_(alpha.detach(), non_blocking=True)
-        C = self.C
-        torch.autograd.backward([color, depth, alpha], [self.upstream[:C], self.upstream[C:C + 1], self.upstream[C + 1:]])
+                self.host_images.view(-1).copy_(color._base, non_blocking=True)
+        bw = _C.rasterize_gaussians_backward_batch(
+            self.bg, means3D, radii, colors, scales, rot, self.scale_modifier, _EMPTY, self.viewmatrices,
+            self.projmatrices, self.tanfovx, self.tanfovy, self.upstream_color, self.upstream_depth, self.upstream_alpha,
+            shs, self.sh_degree, self.cam_positions, geom, R, binning, img, alpha, False)
         if self.host_images is not None:
             torch.cuda.current_stream().wait_stream(self._side)
-        return color, depth, alpha, radii, rast.overflow
+        self._fw, self._bw = fw, bw
+        if V == 1:
+            self.color, self.depth, self.alpha, self.radii = color[0], depth[0], alpha[0], radii[0]
+        else:
+            self.color, self.depth, self.alpha, self.radii = color, depth, alpha, radii
+        self.overflow = status
 
-    def set_camera(self, viewmatrix: torch.Tensor, projmatrix: torch.Tensor, campos: torch.Tensor) -> None:
+    def _bind_grads(self):
+        """Point `.grad` of the parameters at the captured backward's outputs (views of one block)."""
+        (g_abs2D, g_means2D, g_colors, g_opac, g_means3D, g_cov3D, g_sh, g_scales, g_rot) = self._bw[:9]
+        self.grad_block = g_means3D._base
+        self.means2D_grad = g_means2D[0] if self.V == 1 else g_means2D
+        self.means2D_absgrad = g_abs2D[0] if self.V == 1 else g_abs2D
+        p = self.params
+        pairs = [("means3D", g_means3D), ("opacities", g_opac), ("scales", g_scales), ("rotations", g_rot),
+                 ("colors_precomp", g_colors), ("shs", g_sh)]
+        for name, g in pairs:
+            t = p.get(name)
+            if t is not None and t.requires_grad:
+                t.grad = g.view(t.shape)
+
+    def set_camera(self, viewmatrix: torch.Tensor, projmatrix: torch.Tensor, campos: torch.Tensor, view: int = 0) -> None:
         """Copy a camera (reference convention: transposed world-to-view, full projection, centre) into
-        the step's static inputs; host or device tensors."""
-        self.viewmatrix.copy_(viewmatrix, non_blocking=True)
-        self.projmatrix.copy_(projmatrix, non_blocking=True)
-        self.campos.copy_(campos, non_blocking=True)
+        the static inputs of view `view`; host or device tensors."""
+        self.viewmatrices[view].copy_(viewmatrix, non_blocking=True)
+        self.projmatrices[view].copy_(projmatrix, non_blocking=True)
+        self.cam_positions[view].copy_(campos, non_blocking=True)
 
     def replay(self) -> None:
         self.graph.replay()
 
     def trainable_grads(self) -> torch.Tensor:
         """The gradients of means3D, opacity, scales, rotations and colours / SH of the last replay as ONE
-        flat tensor (they are the leading blocks of a single allocation): what a multi-GPU step
-        all-reduces.  Requires all of them to be leaves of this step."""
-        from ._C import trainable_grad_numel
-        g = self.params["means3D"].grad
-        shs = self.params.get("shs")
-        M = int(shs.shape[1]) if shs is not None else 0
-        n = trainable_grad_numel(int(g.shape[0]), self.C if shs is None else 3, M)
-        return g.as_strided((n,), (1,), g.storage_offset())
+        flat tensor (the leading span of the step's packed block): what a multi-GPU step all-reduces."""
+        return self.grad_block[:self.grad_block.trainable_numel]

@@ -15,7 +15,7 @@ import math
 import torch
 
 from . import scenes
-from .diff_gauss import GaussianRasterizationSettings, GaussianRasterizer
+from .diff_gauss import BatchedGaussianRasterizer, GaussianRasterizationSettings, GaussianRasterizer
 
 
 def _skew(v: torch.Tensor) -> torch.Tensor:
@@ -42,6 +42,33 @@ def se3_exp(tau: torch.Tensor) -> torch.Tensor:
     T[:3, :3] = R
     T[:3, 3] = V @ rho
     T[3, 3].fill_(1.0)
+    return T
+
+
+def se3_exp_batch(tau: torch.Tensor) -> torch.Tensor:
+    """(F, 4, 4) matrices of Exp(rho_f, theta_f) for tau (F, 6); float64, no host synchronisation."""
+    tau = tau.double()
+    rho, th = tau[:, :3], tau[:, 3:]
+    a2 = (th * th).sum(1)
+    a = torch.sqrt(a2)
+    small = a2 < 1e-16
+    a_safe = torch.where(small, torch.ones_like(a), a)
+    A = torch.where(small, 1 - a2 / 6, torch.sin(a_safe) / a_safe)
+    B = torch.where(small, 0.5 - a2 / 24, (1 - torch.cos(a_safe)) / (a_safe * a_safe))
+    Cc = torch.where(small, 1.0 / 6 - a2 / 120, (a_safe - torch.sin(a_safe)) / (a_safe ** 3))
+    F = tau.shape[0]
+    K = torch.zeros(F, 3, 3, dtype=torch.float64, device=tau.device)
+    K[:, 0, 1], K[:, 0, 2] = -th[:, 2], th[:, 1]
+    K[:, 1, 0], K[:, 1, 2] = th[:, 2], -th[:, 0]
+    K[:, 2, 0], K[:, 2, 1] = -th[:, 1], th[:, 0]
+    K2 = K @ K
+    I3 = torch.eye(3, dtype=torch.float64, device=tau.device).expand(F, 3, 3)
+    R = I3 + A[:, None, None] * K + B[:, None, None] * K2
+    Vm = I3 + B[:, None, None] * K + Cc[:, None, None] * K2
+    T = torch.zeros(F, 4, 4, dtype=torch.float64, device=tau.device)
+    T[:, :3, :3] = R
+    T[:, :3, 3] = (Vm @ rho[:, :, None])[:, :, 0]
+    T[:, 3, 3].fill_(1.0)
     return T
 
 
@@ -170,6 +197,87 @@ class PoseRefiner:
         if int(st["overflow"]) != 0:
             return self.refine(w2c_init, target_color, target_depth, iters)
         return st["w2c"].clone(), list(st["losses"][:iters].clone())
+
+    # ------------------------------------------------------------------ F frames per launch
+    def camera_tensors_batch(self, w2c: torch.Tensor):
+        """(F, 4, 4) world-to-camera matrices -> stacked viewmatrix / projmatrix / campos, on the device."""
+        view = w2c.transpose(1, 2).float().contiguous()
+        full = (view @ self.proj_t).contiguous()
+        campos = (-(w2c[:, :3, :3].transpose(1, 2) @ w2c[:, :3, 3:4])[:, :, 0]).float().contiguous()
+        return view, full, campos
+
+    def _capture_batch(self, w2c_init, target_color, target_depth, max_iters):
+        dev, F = self.device, int(w2c_init.shape[0])
+        st = self._bstate = {
+            "w2c": w2c_init.double().to(dev).clone(), "m": torch.zeros(F, 6, dtype=torch.float64, device=dev),
+            "v": torch.zeros(F, 6, dtype=torch.float64, device=dev), "t": torch.zeros((), dtype=torch.float64, device=dev),
+            "color": target_color.to(dev).clone(), "depth": target_depth.to(dev).clone(),
+            "losses": torch.zeros(max_iters, F, device=dev), "i": torch.zeros(1, dtype=torch.long, device=dev),
+            "overflow": torch.zeros(1, dtype=torch.int32, device=dev)}
+        cap = sum(self._pair_capacity(st["w2c"][f]) for f in range(F))
+        g = self.g
+
+        def one_iteration():
+            theta = torch.zeros(F, 3, device=dev, requires_grad=True)
+            rho = torch.zeros(F, 3, device=dev, requires_grad=True)
+            view, full, campos = self.camera_tensors_batch(st["w2c"])
+            rs = GaussianRasterizationSettings(self.H, self.W, self.tanfovx, self.tanfovy, self.bg, 1.0, view, full, 0,
+                                               campos, False, False)
+            rast = BatchedGaussianRasterizer(rs, max_pairs=cap, pose_only=True)
+            color, depth, alpha, _ = rast(means3D=g["means3D"], means2D=self.means2D, opacities=g["opacities"],
+                                          colors_precomp=g["colors_precomp"], scales=g["scales"],
+                                          rotations=g["rotations"], theta=theta, rho=rho)
+            valid = (st["depth"] > 0).float()
+            loss = (color - st["color"]).abs().mean(dim=(1, 2, 3)) + \
+                self.depth_weight * ((depth - st["depth"]).abs() * valid).mean(dim=(1, 2, 3))
+            loss.sum().backward()            # frames are independent: each tau only sees its own loss
+            grad = torch.cat([rho.grad, theta.grad], 1).double()
+            st["t"].add_(1.0)
+            st["m"].mul_(0.9).add_(0.1 * grad)
+            st["v"].mul_(0.999).add_(0.001 * grad * grad)
+            m_hat = st["m"] / (1 - torch.pow(0.9, st["t"]))
+            v_hat = st["v"] / (1 - torch.pow(0.999, st["t"]))
+            st["w2c"].copy_(se3_exp_batch(-(self.lr * m_hat / (v_hat.sqrt() + 1e-12))) @ st["w2c"])
+            st["losses"].index_copy_(0, st["i"], loss.detach().reshape(1, F))
+            st["i"].add_(1)
+            st["overflow"].copy_(torch.maximum(st["overflow"], rast.overflow))
+
+        snapshot = {k: v.clone() for k, v in st.items()}
+        with torch.cuda.device(dev):
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(2):
+                    one_iteration()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            self._bgraph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self._bgraph):
+                one_iteration()
+        for k, v in snapshot.items():
+            st[k].copy_(v)
+        self._bgraph_shape = (F, max_iters)
+
+    def refine_batch(self, w2c_init: torch.Tensor, target_color: torch.Tensor, target_depth: torch.Tensor, iters: int = 100):
+        """`refine_graphed` for F query frames at once: `w2c_init` (F, 4, 4), `target_color` (F, C, H, W),
+        `target_depth` (F, 1, H, W).  One CUDA-graph replay per iteration renders all F cameras with the
+        batch entry points (`pose_only`: no per-Gaussian gradient is formed for the fixed map) and
+        updates F independent Adam states.  Returns ((F, 4, 4) refined poses, (iters, F) losses), or
+        None if a frame exceeded the pair capacity chosen at capture (refine those frames singly)."""
+        F = int(w2c_init.shape[0])
+        if getattr(self, "_bgraph", None) is None or self._bgraph_shape[0] != F or self._bgraph_shape[1] < iters:
+            self._capture_batch(w2c_init, target_color, target_depth, iters)
+        st = self._bstate
+        st["w2c"].copy_(w2c_init.double())
+        st["color"].copy_(target_color)
+        st["depth"].copy_(target_depth)
+        for k in ("m", "v", "t", "losses", "i", "overflow"):
+            st[k].zero_()
+        for _ in range(iters):
+            self._bgraph.replay()
+        if int(st["overflow"]) != 0:
+            return None
+        return st["w2c"].clone(), st["losses"][:iters].clone()
 
     def refine(self, w2c_init: torch.Tensor, target_color: torch.Tensor, target_depth: torch.Tensor, iters: int = 100):
         """Adam (beta 0.9 / 0.999) on tau, re-linearised at every step.  Returns (w2c, [loss per iteration])."""

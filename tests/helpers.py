@@ -78,7 +78,9 @@ def run_backend(be, d, debug=False, backward=True):
         out["n_contrib"] = im["n_contrib"]
         out["ranges"] = im["ranges"]
         if R > 0:
-            b = interpret_binningBuffer(binning, R)
+            # a no-read-back forward carves the chunk for its stated capacity; the first R entries are filled
+            cap = getattr(be, "capacity", None) or R
+            b = {k: v[:R] for k, v in interpret_binningBuffer(binning, cap).items()}
             # The emitted (key, id) pairs as a multiset: their order in the unsorted arrays is an
             # implementation detail (Gaussian-major in the reference, tile-bucketed here by default).
             ku, vu = b["point_list_keys_unsorted"].clone(), b["point_list_unsorted"].clone().long()
@@ -87,6 +89,9 @@ def run_backend(be, d, debug=False, backward=True):
             o = torch.argsort(ku, stable=True)
             out["emitted_keys"] = ku[o]
             out["emitted_vals"] = vu[o].int()
+            # the raw emission order (Gaussian-major in the reference and in binning mode 1)
+            out["keys_unsorted_raw"] = b["point_list_keys_unsorted"]
+            out["vals_unsorted_raw"] = b["point_list_unsorted"]
             out["keys_sorted"] = b["point_list_keys"]
             out["point_list"] = b["point_list"]
     if backward:
@@ -166,3 +171,45 @@ def golden_reference(g):
         o = torch.argsort(ku, stable=True)
         b["emitted_keys"], b["emitted_vals"] = ku[o], vu[o].int()
     return b
+
+
+# ---------------------------------------------------------------- gradient agreement, calibrated
+def reference_self_noise(ref, d, runs=3):
+    """Run the reference `runs` times on the same input.  Its backward sums with float atomics in
+    whatever order the hardware serves them, so two runs differ; returns (first run, {gradient
+    name: largest element-wise difference seen between any two runs})."""
+    outs = [run_backend(ref, d) for _ in range(runs)]
+    noise = {}
+    for k in GRAD_KEYS:
+        if k not in outs[0] or outs[0][k].numel() == 0:
+            continue
+        n = 0.0
+        for i in range(runs):
+            for j in range(i + 1, runs):
+                n = max(n, float((outs[i][k].double() - outs[j][k].double()).abs().max()))
+        noise[k] = n
+    return outs[0], noise
+
+
+NOISE_FACTOR = 2.0
+
+
+def compare_grads_calibrated(a, b, noise, rtol=RTOL, atol=ATOL, factor=NOISE_FACTOR):
+    """Gradient check without hand-set slack: an element agrees if it is within north_star's
+    rtol 1e-4 / atol 1e-5, or within `factor` x the difference the reference shows against ITSELF
+    between runs on this very input (`noise`, from reference_self_noise).  Returns (mismatch
+    descriptions, {name: (max err, self-noise, max |ref|)})."""
+    bad, stats = [], {}
+    for k in GRAD_KEYS:
+        if k not in b or b[k].numel() == 0:
+            continue
+        x, y = a[k].double(), b[k].double()
+        err = (x - y).abs()
+        strict = atol + rtol * y.abs()
+        ok = (err <= strict) | (err <= factor * noise.get(k, 0.0))
+        stats[k] = (float(err.max()), noise.get(k, 0.0), float(y.abs().max()))
+        nbad = int((~ok).sum())
+        if nbad or not torch.isfinite(x).all():
+            bad.append(f"{k}: {nbad}/{y.numel()} outside rtol/atol and {factor}x reference self-noise "
+                       f"({noise.get(k, 0.0):.3e}); max err {float(err.max()):.3e}, max |ref| {float(y.abs().max()):.3e}")
+    return bad, stats
