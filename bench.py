@@ -867,6 +867,11 @@ def main():
         raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
 
     job, out, state = run_train_step(args, args.impl)
+
+    def note(name):      # progress on stderr: a sub-record that fails later does not hide the earlier ones
+        if job.rank == 0:
+            print(json.dumps({name: out[name]}), file=sys.stderr, flush=True)
+    note("value")
     subs = {"sweep", "pose_refine", "multiview", "train_window"} if args.sub == "all" else \
         (set() if args.sub == "none" else set(args.sub.split(",")))
     if args.points != P_DEFAULT:
@@ -875,12 +880,15 @@ def main():
     if args.impl == "ours":
         if "multiview" in subs:
             out["multiview"] = sub_multiview(job, args, state["sc"])
+            note("multiview")
         state.clear()
         torch.cuda.empty_cache()
         if "pose_refine" in subs:
             out["pose_refine"] = sub_pose_refine(job, args)
+            note("pose_refine")
         if "train_window" in subs:
             out["train_window"] = sub_train_window(job, args)
+            note("train_window")
     state.clear()
     torch.cuda.empty_cache()
     if "sweep" in subs and job.world == 1:

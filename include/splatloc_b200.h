@@ -156,8 +156,7 @@ int sl_forward_ext(sl_alloc_fn geometry_alloc, void* geometry_ctx,
  * captured in a CUDA graph and replayed with no host work between its kernels.
  *   returns max_pairs: pass THAT as R to sl_backward[_ext] (it locates the chunk's arrays).
  *   status [1] (device int, required): 0 after the call's work has run, or 1 if the frame had more
- *     than max_pairs pairs, a tile with more than 16384 of them, or more than 256 tiles with more than
- *     4096.  Then colour / depth / alpha are
+ *     than max_pairs pairs or a tile with more than 16384 of them.  Then colour / depth / alpha are
  *     background-only, n_contrib is 0 and the backward yields zero gradients: check the word when
  *     convenient and redo the frame with sl_forward_ext or a larger max_pairs.
  * Always uses the tile-bucket binning (sl_set_binning_mode does not apply).  debug is not available. */

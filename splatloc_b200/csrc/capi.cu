@@ -246,9 +246,6 @@ int sl_forward(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                           prefiltered, out_color, out_depth, out_alpha, radii, nullptr, debug, stream_);
 }
 
-// Long-segment sort CTAs launched when the host cannot know how many tiles need them (no read-back).
-constexpr int kNosyncLargeTiles = 256;
-
 // `n_views` cameras of one image size per call; outputs and per-view state are laid out [view][...].
 // `max_pairs` < 0: the reference's protocol -- read R back, size the binning chunk exactly.
 // `max_pairs` >= 0 (no read-back): the caller's capacity; no host synchronisation at all.
@@ -344,8 +341,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         StageTimer t(ST_SCAN, stream);
         rc = launch_tile_scan(img.tile_counts, img.ranges, img.tile_order, img.large_tiles, img.bin_info, n_tiles,
                               nosync ? (uint32_t)max_pairs : 0xffffffffu,
-                              nosync ? (uint32_t)TILE_SORT_LARGE : 0xffffffffu,
-                              nosync ? (uint32_t)kNosyncLargeTiles : 0xffffffffu, status, stream);
+                              nosync ? (uint32_t)TILE_SORT_LARGE : 0xffffffffu, status, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "tile scan");
@@ -354,8 +350,8 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     BinInfo info;
     if (nosync) {
         // No read-back: the chunk holds `max_pairs` pairs; tile_scan_kernel has flagged the frame on the
-        // device if it needs more (or has a tile list beyond what one CTA sorts, or more long lists than
-        // the fixed launch below covers), in which case the remaining stages do nothing.  Launch shapes
+        // device if it needs more (or has a tile list beyond what one CTA sorts), in which case the
+        // remaining stages do nothing.  Launch shapes
         // below assume the worst admissible case.
         memset(&info, 0, sizeof(info));
         info.num_pairs = (uint32_t)max_pairs;
@@ -394,7 +390,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         SL_STAGE(dbg, stream, "scatter pairs");
         {
             StageTimer t(ST_SORT, stream);
-            rc = launch_tile_sort(P, C, info.max_pairs, nosync ? -kNosyncLargeTiles : (int)info.n_large, img.ranges,
+            rc = launch_tile_sort(P, C, info.max_pairs, nosync ? -1 : (int)info.n_large, img.ranges,
                                   img.tile_order, img.large_tiles, vp, bin.point_list_keys_unsorted,
                                   bin.point_list_unsorted, bin.point_list_keys, bin.point_list, geom, features,
                                   feature_view_stride, bin.records, bin.masks, img.bin_info, stream);

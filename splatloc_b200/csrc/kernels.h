@@ -48,13 +48,12 @@ int launch_emit_pairs(int P, const GeomState& g, const int* radii, const uint8_t
 // and each segment is sorted on (depth bits, Gaussian id) by one CTA, which also writes the
 // PairRecords and masks.  The result equals the stable global sort on (tile | depth).
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, uint32_t max_large_tiles,
-                     int* status, cudaStream_t stream);
+                     int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, int* status, cudaStream_t stream);
 int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint8_t* tile_mask,
                          const ViewParams& vp, const uint2* ranges, uint32_t* cursors, uint64_t* keys,
                          uint32_t* vals, const BinInfo* dev_info, cudaStream_t stream);
-// `n_large_launch`: CTAs of the long-segment sort to launch (the exact count when the host knows it,
-// a fixed capacity in no-read-back mode: surplus CTAs leave at once).
+// `n_large_launch`: length of the long-segment work list when the host knows it, < 0 in no-read-back
+// mode (the CTAs then read it from the device), 0: no long segments.
 int launch_tile_sort(int P, int C, uint32_t longest, int n_large_launch, const uint2* ranges,
                      const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
                      const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,

@@ -33,8 +33,12 @@ struct KnnGrid {
     float ext_x, ext_y, ext_z;
 };
 
+constexpr int KNN_HIST_BINS = 1024;   // per-axis bins of the coordinate histogram that trims outliers
+
 struct KnnScratch {
-    uint32_t* bbox;        // [6] order-preserving uint encodings of min xyz, max xyz
+    uint32_t* bbox;        // [6] order-preserving uint encodings of min xyz, max xyz of all points,
+                           // then [6] the same for the trimmed box the grid is laid over
+    uint32_t* axis_hist;   // [3 * KNN_HIST_BINS] per-axis histogram of the coordinates over the raw box
     uint32_t* cell_of;     // [P]
     uint32_t* counts;      // [n_cells] histogram, consumed by the scatter
     uint32_t* cell_end;    // [n_cells] inclusive prefix sum of counts
@@ -45,7 +49,8 @@ struct KnnScratch {
     static KnnScratch from_chunk(char*& chunk, size_t P, size_t n_cells)
     {
         KnnScratch s;
-        carve(chunk, s.bbox, 8);
+        carve(chunk, s.bbox, 16);
+        carve(chunk, s.axis_hist, 3 * KNN_HIST_BINS);
         carve(chunk, s.cell_of, P);
         carve(chunk, s.counts, n_cells);
         carve(chunk, s.cell_end, n_cells);
@@ -116,8 +121,65 @@ knn_bbox_kernel(int P, const float* __restrict__ pts, uint32_t* bbox)
     }
 }
 
+// The grid is laid over a TRIMMED bounding box: a single far outlier (common in depth
+// back-projection) would otherwise stretch the raw box until nearly all points share a handful of
+// cells and every query degenerates to brute force.  Per axis, the P / 1000 smallest and largest
+// coordinates are cut off with a 1024-bin histogram; points outside the trimmed box are clamped
+// into the border cells (cell_coord), which the search handles like any other cell content: the
+// stopping bound below only ever uses the INNER faces of the searched block.
+__global__ void __launch_bounds__(256)
+knn_axis_hist_kernel(int P, const float* __restrict__ pts, const uint32_t* __restrict__ bbox,
+                     uint32_t* __restrict__ axis_hist)
+{
+    __shared__ uint32_t s_hist[3 * KNN_HIST_BINS];
+    for (int k = threadIdx.x; k < 3 * KNN_HIST_BINS; k += blockDim.x) s_hist[k] = 0u;
+    __syncthreads();
+    float mn[3], sc[3];
+#pragma unroll
+    for (int a = 0; a < 3; ++a) {
+        mn[a] = ord2f(bbox[a]);
+        const float ext = ord2f(bbox[3 + a]) - mn[a];
+        sc[a] = ext > 0.f ? (float)KNN_HIST_BINS / ext : 0.f;
+    }
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < P; i += gridDim.x * blockDim.x) {
+#pragma unroll
+        for (int a = 0; a < 3; ++a) {
+            const float f = (pts[3 * i + a] - mn[a]) * sc[a];
+            const int b = (f >= 0.f) ? min(KNN_HIST_BINS - 1, (int)fminf(f, (float)(KNN_HIST_BINS - 1))) : 0;
+            atomicAdd(&s_hist[a * KNN_HIST_BINS + b], 1u);
+        }
+    }
+    __syncthreads();
+    for (int k = threadIdx.x; k < 3 * KNN_HIST_BINS; k += blockDim.x)
+        if (s_hist[k]) atomicAdd(&axis_hist[k], s_hist[k]);
+}
+
+// One warp per axis: walk the histogram from both ends until P / 1000 points are passed.
+__global__ void knn_trim_box_kernel(int P, uint32_t* bbox, const uint32_t* __restrict__ axis_hist)
+{
+    const int a = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (a >= 3) return;
+    const uint32_t trim = (uint32_t)(P / 1000);
+    const uint32_t* h = axis_hist + a * KNN_HIST_BINS;
+    int lo = 0, hi = KNN_HIST_BINS - 1;
+    if (lane == 0) {
+        uint32_t acc = 0;
+        while (lo < KNN_HIST_BINS - 1 && acc + h[lo] <= trim) acc += h[lo++];
+        acc = 0;
+        while (hi > lo && acc + h[hi] <= trim) acc += h[hi--];
+        const float mn = ord2f(bbox[a]), mx = ord2f(bbox[3 + a]);
+        const float w = (mx - mn) / (float)KNN_HIST_BINS;
+        // bin edges, never outside the raw box
+        const float tmn = lo == 0 ? mn : fminf(mx, mn + (float)lo * w);
+        const float tmx = hi == KNN_HIST_BINS - 1 ? mx : fmaxf(tmn, fminf(mx, mn + (float)(hi + 1) * w));
+        bbox[6 + a] = f2ord(tmn);
+        bbox[9 + a] = f2ord(tmx);
+    }
+}
+
 __device__ __forceinline__ KnnGrid make_grid(const uint32_t* bbox, int G)
 {
+    bbox += 6;   // the trimmed box
     KnnGrid g;
     g.min_x = ord2f(bbox[0]); g.min_y = ord2f(bbox[1]); g.min_z = ord2f(bbox[2]);
     g.ext_x = ord2f(bbox[3]) - g.min_x;
@@ -225,13 +287,17 @@ knn_query_kernel(int P, const float4* __restrict__ sorted, const uint32_t* __res
         }
         // Every point outside the searched block is at least `reach` away (with a
         // safety margin for the rounding of the cell assignment).
+        // Box-relative coordinates: `ref - min` is the very expression the cell assignment rounds, so
+        // the bound is off by a few ulp of the EXTENT, whatever the cloud's distance from the origin
+        // (min + k * cell would round at ulp(|coordinate|), which exceeds the pad for a far-away cloud).
         float reach = FLT_MAX;
-        if (g.ext_x > 0.f && ix - r > 0) reach = fminf(reach, ref.x - (g.min_x + (float)(ix - r) * g.cell_x) - 4e-6f * g.ext_x);
-        if (g.ext_x > 0.f && ix + r < G - 1) reach = fminf(reach, (g.min_x + (float)(ix + r + 1) * g.cell_x) - ref.x - 4e-6f * g.ext_x);
-        if (g.ext_y > 0.f && iy - r > 0) reach = fminf(reach, ref.y - (g.min_y + (float)(iy - r) * g.cell_y) - 4e-6f * g.ext_y);
-        if (g.ext_y > 0.f && iy + r < G - 1) reach = fminf(reach, (g.min_y + (float)(iy + r + 1) * g.cell_y) - ref.y - 4e-6f * g.ext_y);
-        if (g.ext_z > 0.f && iz - r > 0) reach = fminf(reach, ref.z - (g.min_z + (float)(iz - r) * g.cell_z) - 4e-6f * g.ext_z);
-        if (g.ext_z > 0.f && iz + r < G - 1) reach = fminf(reach, (g.min_z + (float)(iz + r + 1) * g.cell_z) - ref.z - 4e-6f * g.ext_z);
+        const float rx = ref.x - g.min_x, ry = ref.y - g.min_y, rz = ref.z - g.min_z;
+        if (g.ext_x > 0.f && ix - r > 0) reach = fminf(reach, rx - (float)(ix - r) * g.cell_x - 4e-6f * g.ext_x);
+        if (g.ext_x > 0.f && ix + r < G - 1) reach = fminf(reach, (float)(ix + r + 1) * g.cell_x - rx - 4e-6f * g.ext_x);
+        if (g.ext_y > 0.f && iy - r > 0) reach = fminf(reach, ry - (float)(iy - r) * g.cell_y - 4e-6f * g.ext_y);
+        if (g.ext_y > 0.f && iy + r < G - 1) reach = fminf(reach, (float)(iy + r + 1) * g.cell_y - ry - 4e-6f * g.ext_y);
+        if (g.ext_z > 0.f && iz - r > 0) reach = fminf(reach, rz - (float)(iz - r) * g.cell_z - 4e-6f * g.ext_z);
+        if (g.ext_z > 0.f && iz + r < G - 1) reach = fminf(reach, (float)(iz + r + 1) * g.cell_z - rz - 4e-6f * g.ext_z);
         if (reach == FLT_MAX) break;  // the block already covers the whole grid
         if (reach > 0.f && best[2] < reach * reach * 0.9999f) break;
     }
@@ -259,6 +325,9 @@ int launch_knn(int P, const float* points, float* mean_dists, char* scratch, cud
 
     knn_bbox_init_kernel<<<1, 32, 0, stream>>>(s.bbox); count_launch();
     knn_bbox_kernel<<<min(ceil_div(P, 256), 148 * 8), 256, 0, stream>>>(P, points, s.bbox); count_launch();
+    SL_CUDA(cudaMemsetAsync(s.axis_hist, 0, 3 * KNN_HIST_BINS * sizeof(uint32_t), stream), "knn memset");
+    knn_axis_hist_kernel<<<min(ceil_div(P, 256 * 8), 148 * 4), 256, 0, stream>>>(P, points, s.bbox, s.axis_hist); count_launch();
+    knn_trim_box_kernel<<<1, 96, 0, stream>>>(P, s.bbox, s.axis_hist); count_launch();
     SL_CUDA(cudaMemsetAsync(s.counts, 0, n_cells * sizeof(uint32_t), stream), "knn memset");
     knn_count_kernel<<<ceil_div(P, 256), 256, 0, stream>>>(P, points, s.bbox, L, s.cell_of, s.counts); count_launch();
     int rc = launch_inclusive_scan(s.counts, s.cell_end, (int)n_cells, s.scan_desc, s.ticket, stream);
@@ -298,7 +367,7 @@ namespace sl {
 //           (different streams, different host threads) race on it and give garbage.
 //         * No cudaMalloc / cudaFree / allocating library call is made, on any call.
 constexpr int kKnnStaticMaxPoints = 65536;
-constexpr size_t kKnnStaticScratchBytes = 3670016;   // 3.5 MiB >= knn_scratch_bytes(65536) = 3408928
+constexpr size_t kKnnStaticScratchBytes = 3670016;   // 3.5 MiB >= knn_scratch_bytes(65536) = 3421216
 
 static __device__ __align__(256) unsigned char g_knn_static_scratch[kKnnStaticScratchBytes];
 

@@ -32,7 +32,7 @@ namespace sl {
 __global__ void __launch_bounds__(1024)
 tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __restrict__ order,
                  uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles,
-                 uint32_t max_pairs, uint32_t max_tile_pairs, uint32_t max_large_tiles, int* status)
+                 uint32_t max_pairs, uint32_t max_tile_pairs, int* status)
 {
     constexpr int NT = 1024;
     __shared__ uint32_t s_warp[32];
@@ -83,7 +83,7 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
     __syncthreads();
     // No-readback mode (sl_forward_nosync): the host sized the binning chunk without knowing R.  If
     // the frame does not fit, every later stage of this frame does nothing and the caller is told.
-    const bool overflow = s_carry > max_pairs || s_max > max_tile_pairs || s_large > max_large_tiles;
+    const bool overflow = s_carry > max_pairs || s_max > max_tile_pairs;
     if (tid == 0) {
         info->num_pairs = s_carry;
         info->n_large = s_large;
@@ -305,9 +305,9 @@ __device__ __forceinline__ void sort_and_emit_tile(
     }
 }
 
-// One CTA per tile of `tiles[blockIdx.x]` (global, view-major tile numbers); handles segments with
-// min_len < n <= 16 * THREADS and picks the network size from n.  The per-Gaussian arrays are those
-// of the tile's view.
+// CTAs stride over the work list `tiles` (global, view-major tile numbers); a CTA handles segments
+// with min_len < n <= 16 * THREADS and picks the network size from n.  The per-Gaussian arrays are
+// those of the tile's view.
 template <int C, int THREADS>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? SL_SORT_MIN_CTAS : 1)
 tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tiles, int n_listed, int grid_x,
@@ -321,34 +321,34 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 {
     extern __shared__ __align__(16) unsigned long long s_key[];
     if (dev_info->overflow) return;
-    if (n_listed < 0 && blockIdx.x >= dev_info->n_large) return;    // long-segment launch sized by capacity
-    const uint32_t tile = tiles[blockIdx.x];
-    const uint2 range = ranges[tile];
-    const uint32_t n = range.y - range.x;
-    if (n <= min_len || n > 16u * THREADS) return;
-    const uint32_t view = tile / (uint32_t)tiles_per_view, local_tile = tile - view * (uint32_t)tiles_per_view;
-    const size_t voff = (size_t)view * P;
-    means2D += voff;
-    depths += voff;
-    conic_opacity += voff;
-    features += view * feature_view_stride;
+    // n_listed < 0: the host does not know how long the work list is (no read-back): the device does.
+    const uint32_t listed = n_listed < 0 ? dev_info->n_large : (uint32_t)n_listed;
+    // grid-stride over the list: the long-segment launch is a few resident CTAs, not one per tile
+    for (uint32_t b = blockIdx.x; b < listed; b += gridDim.x) {
+        const uint32_t tile = tiles[b];
+        const uint2 range = ranges[tile];
+        const uint32_t n = range.y - range.x;
+        if (n <= min_len || n > 16u * THREADS) continue;
+        const uint32_t view = tile / (uint32_t)tiles_per_view, local_tile = tile - view * (uint32_t)tiles_per_view;
+        const size_t voff = (size_t)view * P;
+        const float* feat = features + view * feature_view_stride;
 #define SL_SORT_CASE(EE)                                                                                         \
     sort_and_emit_tile<C, EE, THREADS>(tile, local_tile, range, grid_x, s_key, keys_in, vals_in, keys_out, point_list, \
-                                       means2D, depths, conic_opacity, features, records, masks)
-    if (n <= 1u * THREADS) SL_SORT_CASE(1);
-    else if (n <= 2u * THREADS) SL_SORT_CASE(2);
-    else if (n <= 4u * THREADS) SL_SORT_CASE(4);
-    else if (n <= 8u * THREADS) SL_SORT_CASE(8);
-    else SL_SORT_CASE(16);
+                                       means2D + voff, depths + voff, conic_opacity + voff, feat, records, masks)
+        if (n <= 1u * THREADS) SL_SORT_CASE(1);
+        else if (n <= 2u * THREADS) SL_SORT_CASE(2);
+        else if (n <= 4u * THREADS) SL_SORT_CASE(4);
+        else if (n <= 8u * THREADS) SL_SORT_CASE(8);
+        else SL_SORT_CASE(16);
 #undef SL_SORT_CASE
+    }
 }
 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
-                     int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, uint32_t max_large_tiles,
-                     int* status, cudaStream_t stream)
+                     int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, int* status, cudaStream_t stream)
 {
     tile_scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles, max_pairs,
-                                             max_tile_pairs, max_large_tiles, status);
+                                             max_tile_pairs, status);
     count_launch();
     return 0;
 }
@@ -374,20 +374,20 @@ static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const
                               const BinInfo* dev_info, cudaStream_t stream)
 {
     const int n_tiles = vp.tiles * vp.views;
-    // Long segments (work list written by tile_scan_kernel) get a 1024-thread CTA with 128 KB of
-    // shared memory each; the 256-thread launch covers all tiles and skips those.  n_large_launch < 0:
-    // the host does not know how many there are (no read-back) and launches -n_large_launch CTAs,
-    // of which the surplus leave at once.
+    // Long segments (work list written by tile_scan_kernel) go to 1024-thread CTAs with 128 KB of shared
+    // memory (one resident per SM) that stride over the list; the 256-thread launch covers all tiles
+    // and skips those.  n_large_launch < 0: the host does not know the list's length (no read-back);
+    // the CTAs read it from the device.
     if (n_large_launch != 0) {
         constexpr int T = 1024;
         const size_t smem = (size_t)TILE_SORT_LARGE * sizeof(unsigned long long);
         SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 "tile sort smem attribute");
-        const int ctas = n_large_launch < 0 ? -n_large_launch : n_large_launch;
-        tile_sort_kernel<C, T><<<ctas, T, smem, stream>>>(
-            ranges, large_tiles, n_large_launch, vp.grid_x, vp.tiles, P, (uint32_t)TILE_SORT_SMALL, keys_in, vals_in,
-            keys_out, point_list, g.means2D, g.depths, g.conic_opacity, features, feature_view_stride, records, masks,
-            dev_info);
+        const int listed = n_large_launch < 0 ? n_tiles : n_large_launch;
+        tile_sort_kernel<C, T><<<listed < 148 ? listed : 148, T, smem, stream>>>(
+            ranges, large_tiles, n_large_launch < 0 ? -1 : n_large_launch, vp.grid_x, vp.tiles, P,
+            (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
+            features, feature_view_stride, records, masks, dev_info);
         count_launch();
     }
     constexpr int T = 256;

@@ -5,8 +5,9 @@ and one `GraphedViewStep.replay()` -- each against the UNMODIFIED reference CUDA
 (oracle/_ref) and against the committed reference outputs (tests/golden).
 
 Integer outputs and the images must be bit-identical.  Gradients: within north_star's rtol 1e-4 /
-atol 1e-5 or within 2x the difference the reference shows against itself between runs on the same
-input (its atomics add in a varying order); no hand-set slack (tests/helpers.py)."""
+atol 1e-5 or within a small multiple (4x on the worst element, 2x in RMS) of the difference the
+reference shows against itself between three runs on the same input (its atomics add in a varying
+order); no hand-set slack (tests/helpers.py: compare_grads_calibrated)."""
 import pytest
 import torch
 
@@ -75,7 +76,7 @@ def _bench_inputs(sc, cam_index):
 def test_config2_bench_cameras_match_reference_cuda(bench_scene, cam_index):
     ref, ours = _ref(), _ours()
     d = _bench_inputs(bench_scene, cam_index)
-    b, noise = H.reference_self_noise(ref, d, runs=2)
+    b, noise = H.reference_self_noise(ref, d, runs=3)
     a = H.run_backend(ours, d)
     assert b["R"] > 100000
     bad = [m for m in H.compare(a, b) if not m.startswith("g_")]      # integers + images: exact / strict
@@ -89,7 +90,7 @@ def test_config2_bench_cameras_match_reference_cuda(bench_scene, cam_index):
 def test_config2_nosync_path_matches_reference_cuda(bench_scene, cam_index):
     ref = _ref()
     d = _bench_inputs(bench_scene, cam_index)
-    b, noise = H.reference_self_noise(ref, d, runs=2)
+    b, noise = H.reference_self_noise(ref, d, runs=3)
     be = _NoSync()
     a = H.run_backend(be, d)
     assert int(be.status) == 0
@@ -132,7 +133,7 @@ def _check_graph_against(a, b, noise):
 def test_config2_graph_replay_matches_reference_cuda(bench_scene):
     ref = _ref()
     d = _bench_inputs(bench_scene, 3)
-    b, noise = H.reference_self_noise(ref, d, runs=2)
+    b, noise = H.reference_self_noise(ref, d, runs=3)
     a = _graph_step_outputs(d, max_pairs=int(1.25 * b["R"]) + 4096)
     _check_graph_against(a, b, noise)
 
@@ -141,7 +142,7 @@ def test_sh3_graph_replay_and_nosync_match_reference_cuda():
     """Config-1-shaped (SH degree 3, C = 3) through the no-read-back path and a graph replay."""
     ref = _ref()
     d = H.scene_inputs(200000, 0, sh_degree=3)
-    b, noise = H.reference_self_noise(ref, d, runs=2)
+    b, noise = H.reference_self_noise(ref, d, runs=3)
     be = _NoSync()
     a = H.run_backend(be, d)
     assert int(be.status) == 0

@@ -167,6 +167,29 @@ def test_knn_bit_exact(P):
         f"{int((a.view(torch.int32) != b.view(torch.int32)).sum())}/{P} differ"
 
 
+@pytest.mark.parametrize("what", ["translated", "outlier", "outliers_1pct"])
+def test_knn_bit_exact_far_from_origin_and_with_outliers(what):
+    """The grid of the search is laid over a trimmed bounding box and its stopping bound is formed in
+    box-relative coordinates: a cloud far from the origin, or one with far outliers (depth
+    back-projection produces them), must still give the reference's bits."""
+    from splatloc_b200 import scenes
+    ref, ours = _ref(), _ours()
+    pts = scenes.make_knn_points(200000, seed=3)
+    if what == "translated":
+        pts = pts + 1000.0
+    elif what == "outlier":
+        pts[12345] = torch.tensor([1.0e4, -2.0e4, 3.0e3])
+    else:
+        g = torch.Generator().manual_seed(1)
+        idx = torch.randperm(pts.shape[0], generator=g)[:2000]
+        pts[idx] = pts[idx] + 200.0 * torch.randn((2000, 3), generator=g)
+    pts = pts.contiguous().cuda()
+    a, b = ours.distCUDA2(pts), ref.distCUDA2(pts)
+    torch.cuda.synchronize()
+    assert torch.equal(a.view(torch.int32), b.view(torch.int32)), \
+        f"{int((a.view(torch.int32) != b.view(torch.int32)).sum())} differ"
+
+
 def test_autograd_front_end():
     """The diff_gauss-compatible module: 4-tuple, gradients on the leaf tensors, absgrad side channel."""
     from splatloc_b200.diff_gauss import GaussianRasterizationSettings, GaussianRasterizer
