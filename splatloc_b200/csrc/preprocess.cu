@@ -141,6 +141,11 @@ preprocess_one(int idx, int D, int M, int C,
         return 0;
     }
     float my_radius = ceil(3.f * sqrt(max(lambda1, lambda2)));
+    // A NaN covariance (a degenerate camera, e.g. an all-zero matrix, or non-finite inputs) passes every
+    // comparison above and arrives here with a radius that converts to 0: without this line the
+    // Gaussian would count tiles it never emits pairs for (the reference has that inconsistency and
+    // then sorts uninitialised keys).  Finite inputs always give a radius >= 1, so nothing else changes.
+    if (!((int)my_radius > 0)) return 0;
 
     float2 point_image = {ndc_to_pix(p_proj.x, vp.W), ndc_to_pix(p_proj.y, vp.H)};
     uint2 rmin, rmax;
