@@ -238,6 +238,51 @@ int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
                       float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                       int debug, void* stream);
 
+/* ---- render() with its pre-processing inside ----------------------------
+ * SplatLoc's render() (gaussian_splatting/gaussian_renderer/__init__.py:12-141) turns the optimiser's
+ * raw parameters into rasterizer inputs with PyTorch ops on every call -- opacity = sigmoid(_opacity),
+ * scales = exp(_scaling) (repeated 3x when isotropic), rotations = normalize(_rotation)
+ * (scene/gaussian_model.py:75-110), colours = clamp_min(eval_sh(0, _features_dc) + 0.5, 0)
+ * (utils/sh_utils.py:55-73) concatenated with _kp_score (:85-102) -- materialising four (P, .) tensors
+ * and their autograd nodes.  These entry points take the raw parameters and apply the activations inside
+ * preprocess / the record gather, and the backward returns gradients of the RAW parameters.  For the
+ * configuration SplatLoc trains with: SH degree 0 (configs/.../base_config.yaml:88), convert_SHs_python.
+ *   features_dc [P, 3]  kp_score [P] | NULL (then 3 channels)  raw_opacity [P]
+ *   raw_scaling [P, scale_dim], scale_dim 3 or 1  raw_rotation [P, 4]
+ * Camera, image, tile mask, max_pairs / status / debug and the n_views layout: as sl_forward_batch.
+ * C = 4 with kp_score, else 3; out_color [n_views, C, H, W].  render()'s "render" is channels 0..2 and
+ * "kp_prob" channel C - 1 of it.
+ * sl_backward_render: intermediates (ZERO on entry, contents afterwards are scratch):
+ *     dL_dmean2D, dL_dabsmean2D [n_views, P, 3] (render()'s viewspace_points.grad / .absgrad),
+ *     dL_dconic [n_views, P, 4], dL_dcolor [P, C], dL_ddepth [n_views, P], dL_dcov3D [P, 6];
+ *   results (ZERO on entry, summed over the views): dL_dmean3D [P, 3], dL_dfeatures_dc [P, 3],
+ *     dL_dkp_score [P] (NULL iff kp_score is), dL_draw_opacity [P], dL_draw_scaling [P, scale_dim],
+ *     dL_draw_rotation [P, 4]. */
+int sl_forward_render(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                      sl_alloc_fn binning_alloc, void* binning_ctx,
+                      sl_alloc_fn image_alloc, void* image_ctx,
+                      int n_views, int P, const float* background, int width, int height,
+                      const float* means3D, const float* features_dc, const float* kp_score,
+                      const float* raw_opacity, const float* raw_scaling, int scale_dim, float scale_modifier,
+                      const float* raw_rotation, const uint8_t* tile_mask,
+                      const float* viewmatrices, const float* projmatrices, const float* cam_positions,
+                      float tan_fovx, float tan_fovy,
+                      float* out_color, float* out_depth, float* out_alpha, int* radii,
+                      int max_pairs, int* status, int debug, void* stream);
+int sl_backward_render(int n_views, int P, int R, const float* background, int width, int height,
+                       const float* means3D, const float* features_dc, const float* kp_score,
+                       const float* raw_opacity, const float* raw_scaling, int scale_dim, float scale_modifier,
+                       const float* raw_rotation,
+                       const float* viewmatrices, const float* projmatrices, const float* cam_positions,
+                       float tan_fovx, float tan_fovy, const int* radii,
+                       char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                       const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                       const float* dL_dpix_alpha,
+                       float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dcolor,
+                       float* dL_ddepth, float* dL_dcov3D,
+                       float* dL_dmean3D, float* dL_dfeatures_dc, float* dL_dkp_score, float* dL_draw_opacity,
+                       float* dL_draw_scaling, float* dL_draw_rotation, int debug, void* stream);
+
 /* Frustum visibility, present[i] in {0,1}.  Replaces
  * CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:71-76,
  * rasterizer_impl.cu:379-391), bound by markVisible (DGR/rasterize_points.cu:215-234). */

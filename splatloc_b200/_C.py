@@ -411,6 +411,98 @@ def rasterize_gaussians_backward_batch(background, means3D, radii, colors, scale
     return out + (g_tau,) if want_pose else out
 
 
+def render_forward(background, means3D, features_dc, kp_score, raw_opacity, raw_scaling, raw_rotation,
+                   scale_modifier, tile_mask, viewmatrices, projmatrices, tan_fovx, tan_fovy, image_height,
+                   image_width, campos, debug=False, max_pairs=None):
+    """render()'s pre-processing + rasterizer forward in one call (sl_forward_render): raw optimiser
+    parameters in (gaussian_model.py:75-110 getters and gaussian_renderer/__init__.py:85-102 are applied
+    inside the kernels).  `features_dc` (P, 3) or (P, 1, 3); `kp_score` (P, 1) or an empty tensor;
+    `raw_scaling` (P, 3) or (P, 1); cameras stacked as for `rasterize_gaussians_batch`.
+    -> (num_rendered, color (V, C, H, W), depth (V, 1, H, W), alpha (V, 1, H, W), radii (V, P),
+        geomBuffer, binningBuffer, imgBuffer) [+ status]"""
+    lib = _capi.load()
+    if not means3D.is_cuda:
+        raise RuntimeError("means3D must be a CUDA tensor (the rasterizer has no CPU path)")
+    dev = means3D.device
+    V, P, H, W = int(viewmatrices.shape[0]), int(means3D.shape[0]), int(image_height), int(image_width)
+    means3D = _f32(means3D, "means3D")
+    features_dc = _f32(features_dc, "features_dc")
+    kp_score = _f32(kp_score, "kp_score")
+    raw_opacity = _f32(raw_opacity, "raw_opacity")
+    raw_scaling = _f32(raw_scaling, "raw_scaling")
+    raw_rotation = _f32(raw_rotation, "raw_rotation")
+    viewmatrices, projmatrices, campos = _f32(viewmatrices, "viewmatrices"), _f32(projmatrices, "projmatrices"), _f32(campos, "campos")
+    if P and features_dc.numel() != 3 * P:
+        raise RuntimeError("features_dc must have 3 values per Gaussian (SH degree 0)")
+    scale_dim = int(raw_scaling.numel() // P) if P else 3
+    n_ch = 4 if kp_score.numel() != 0 else 3
+    background = _pad_bg(_f32(background, "bg"), n_ch)
+    if tile_mask is not None and tile_mask.numel() != 0:
+        tile_mask = tile_mask.to(torch.bool).contiguous()
+    with _on_device(dev):
+        N = H * W
+        images = torch.empty(V * (n_ch + 2) * N, dtype=torch.float32, device=dev)
+        color = images[:V * n_ch * N].view(V, n_ch, H, W)
+        depth = images[V * n_ch * N:V * (n_ch + 1) * N].view(V, 1, H, W)
+        alpha = images[V * (n_ch + 1) * N:].view(V, 1, H, W)
+        radii = torch.empty((V, P), dtype=torch.int32, device=dev)
+        geom, binning, img = _chunks(dev)
+        status = torch.empty(1, dtype=torch.int32, device=dev) if max_pairs is not None else None
+        rc = lib.sl_forward_render(
+            geom.callback, None, binning.callback, None, img.callback, None,
+            V, P, _ptr(background), W, H, _ptr(means3D), _ptr(features_dc), _ptr(kp_score),
+            _ptr(raw_opacity), _ptr(raw_scaling), scale_dim, float(scale_modifier), _ptr(raw_rotation), _ptr(tile_mask),
+            _ptr(viewmatrices), _ptr(projmatrices), _ptr(campos), float(tan_fovx), float(tan_fovy),
+            color.data_ptr(), depth.data_ptr(), alpha.data_ptr(), _ptr(radii),
+            -1 if max_pairs is None else int(max_pairs), _ptr(status), int(bool(debug)), _stream(dev))
+        geom_t, binning_t, img_t = geom.take(), binning.take(), img.take()
+        rendered = _capi.check(rc)
+    out = (rendered, color, depth, alpha, radii, geom_t, binning_t, img_t)
+    return out + (status,) if status is not None else out
+
+
+def render_backward(background, means3D, radii, features_dc, kp_score, raw_opacity, raw_scaling, raw_rotation,
+                    scale_modifier, viewmatrices, projmatrices, tan_fovx, tan_fovy, dL_dout_color, dL_dout_depth,
+                    dL_dout_alpha, campos, geomBuffer, R, binningBuffer, imageBuffer, out_alpha, debug=False):
+    """Backward of `render_forward` (sl_backward_render): gradients of the RAW parameters.
+    -> (dL_dabsmeans2D (V, P, 3), dL_dmeans2D (V, P, 3), dL_dmeans3D (P, 3), dL_dfeatures_dc (P, 3),
+        dL_dkp_score (P, 1), dL_draw_opacity (P, 1), dL_draw_scaling (P, scale_dim), dL_draw_rotation (P, 4))"""
+    lib = _capi.load()
+    dev = means3D.device
+    P = int(means3D.shape[0])
+    V, n_ch, H, W = (int(x) for x in dL_dout_color.shape)
+    means3D = _f32(means3D, "means3D")
+    features_dc, kp_score = _f32(features_dc, "features_dc"), _f32(kp_score, "kp_score")
+    raw_opacity, raw_scaling, raw_rotation = _f32(raw_opacity, "raw_opacity"), _f32(raw_scaling, "raw_scaling"), _f32(raw_rotation, "raw_rotation")
+    dL_dout_color, dL_dout_depth, dL_dout_alpha = (_f32(dL_dout_color, "dL_dout_color"), _f32(dL_dout_depth, "dL_dout_depth"),
+                                                   _f32(dL_dout_alpha, "dL_dout_alpha"))
+    out_alpha = _f32(out_alpha, "out_alpha")
+    background = _pad_bg(_f32(background, "bg"), n_ch)
+    viewmatrices, projmatrices, campos = _f32(viewmatrices, "viewmatrices"), _f32(projmatrices, "projmatrices"), _f32(campos, "campos")
+    scale_dim = int(raw_scaling.numel() // P) if P else 3
+    with_kp = kp_score.numel() != 0
+    with _on_device(dev):
+        # results first (one contiguous span for a multi-GPU all-reduce), then per-view statistics, then scratch
+        counts = [P * 3, P, P * scale_dim, P * 4, P * 3, P if with_kp else 0,
+                  V * P * 3, V * P * 3, V * P, V * P * 4, P * n_ch, P * 6]
+        flat = torch.zeros(sum((n + 3) // 4 * 4 for n in counts), dtype=torch.float32, device=dev)
+        (g_mean3D, g_opac, g_scale, g_rot, g_fdc, g_kp, g_mean2D, g_abs2D, g_depth, g_conic, g_color, g_cov3D) = _carve(flat, counts)
+        flat.trainable_numel = g_mean2D.storage_offset() - flat.storage_offset()
+        if P != 0:
+            rc = lib.sl_backward_render(
+                V, P, int(R), _ptr(background), W, H, _ptr(means3D), _ptr(features_dc), _ptr(kp_score),
+                _ptr(raw_opacity), _ptr(raw_scaling), scale_dim, float(scale_modifier), _ptr(raw_rotation),
+                _ptr(viewmatrices), _ptr(projmatrices), _ptr(campos), float(tan_fovx), float(tan_fovy), _ptr(radii.contiguous()),
+                _ptr(geomBuffer), _ptr(binningBuffer), _ptr(imageBuffer),
+                _ptr(out_alpha), _ptr(dL_dout_color), _ptr(dL_dout_depth), _ptr(dL_dout_alpha),
+                g_mean2D.data_ptr(), g_abs2D.data_ptr(), g_conic.data_ptr(), g_color.data_ptr(), g_depth.data_ptr(),
+                g_cov3D.data_ptr(), g_mean3D.data_ptr(), g_fdc.data_ptr(), _ptr(g_kp), g_opac.data_ptr(),
+                g_scale.data_ptr(), g_rot.data_ptr(), int(bool(debug)), _stream(dev))
+            _capi.check(rc)
+    return (g_abs2D.view(V, P, 3), g_mean2D.view(V, P, 3), g_mean3D.view(P, 3), g_fdc.view(P, 3),
+            g_kp.view(P, 1) if with_kp else g_kp, g_opac.view(P, 1), g_scale.view(P, scale_dim), g_rot.view(P, 4))
+
+
 def mark_visible(means3D, viewmatrix, projmatrix):
     """-> bool tensor (P,): inside the padded view frustum."""
     lib = _capi.load()

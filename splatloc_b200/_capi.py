@@ -116,6 +116,27 @@ SIGNATURES = {
         _F, _F, _F, _F,                              # dL_dsh, dL_dscale, dL_drot, dL_dtau
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
+    "sl_forward_render": (C.c_int, [
+        ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p,
+        C.c_int, C.c_int, _F, C.c_int, C.c_int,      # n_views, P, background, width, height
+        _F, _F, _F,                                  # means3D, features_dc, kp_score
+        _F, _F, C.c_int, C.c_float,                  # raw_opacity, raw_scaling, scale_dim, scale_modifier
+        _F, _F,                                      # raw_rotation, tile_mask
+        _F, _F, _F, C.c_float, C.c_float,            # viewmatrices, projmatrices, cam_positions, tan_fovx, tan_fovy
+        _F, _F, _F, _F,                              # out_color, out_depth, out_alpha, radii
+        C.c_int, _F, C.c_int, C.c_void_p,            # max_pairs, status, debug, stream
+    ]),
+    "sl_backward_render": (C.c_int, [
+        C.c_int, C.c_int, C.c_int, _F, C.c_int, C.c_int,   # n_views, P, R, background, width, height
+        _F, _F, _F,                                  # means3D, features_dc, kp_score
+        _F, _F, C.c_int, C.c_float, _F,              # raw_opacity, raw_scaling, scale_dim, scale_modifier, raw_rotation
+        _F, _F, _F, C.c_float, C.c_float, _F,        # viewmatrices, projmatrices, cam_positions, tan_fovx, tan_fovy, radii
+        _F, _F, _F,                                  # geometry, binning, image chunks
+        _F, _F, _F, _F,                              # accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha
+        _F, _F, _F, _F, _F, _F,                      # dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dcolor, dL_ddepth, dL_dcov3D
+        _F, _F, _F, _F, _F, _F,                      # dL_dmean3D, dL_dfeatures_dc, dL_dkp_score, dL_draw_opacity/scaling/rotation
+        C.c_int, C.c_void_p,                         # debug, stream
+    ]),
     "sl_mark_visible": (C.c_int, [C.c_int, _F, _F, _F, _F, C.c_void_p]),
     "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),

@@ -58,7 +58,7 @@ __global__ void __launch_bounds__(256)
 build_records_kernel(int R, int P, const uint64_t* __restrict__ keys, const uint32_t* __restrict__ point_list,
                      const float2* __restrict__ means2D, const float* __restrict__ depths,
                      const float4* __restrict__ conic_opacity, const float* __restrict__ features,
-                     size_t feature_view_stride, int grid_x, int tiles_per_view,
+                     size_t feature_view_stride, const float* __restrict__ kp, int raw, int grid_x, int tiles_per_view,
                      PairRecord* __restrict__ records, uint8_t* __restrict__ masks, uint2* __restrict__ ranges)
 {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -81,14 +81,7 @@ build_records_kernel(int R, int P, const uint64_t* __restrict__ keys, const uint
     const float2 xy = means2D[v];
     const float4 co = conic_opacity[v];
     features += view * feature_view_stride;
-    float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (C == 4) {
-        f = reinterpret_cast<const float4*>(features)[id];
-    } else {
-        f.x = features[id * C + 0];
-        if (C > 1) f.y = features[id * C + 1];
-        if (C > 2) f.z = features[id * C + 2];
-    }
+    const float4 f = gather_features<C>(features, kp, raw != 0, (uint32_t)id);
     PairRecord rec;
     rec.xyd = make_float4(xy.x, xy.y, depths[v], __int_as_float(id));
     rec.co = co;
@@ -99,18 +92,20 @@ build_records_kernel(int R, int P, const uint64_t* __restrict__ keys, const uint
 }
 
 int launch_build_records(int R, int P, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
-                         const GeomState& g, const float* features, size_t feature_view_stride,
+                         const GeomState& g, const float* features, size_t feature_view_stride, const RawParams* rawp,
                          const ViewParams& vp, PairRecord* records, uint8_t* masks, uint2* ranges,
                          cudaStream_t stream)
 {
+    const float* kp = rawp != nullptr ? rawp->kp_score : nullptr;
+    const int raw = rawp != nullptr ? 1 : 0;
     SL_CUDA(cudaMemsetAsync(ranges, 0, (size_t)vp.tiles * vp.views * sizeof(uint2), stream), "ranges memset");
     if (R > 0) {
         if (C == 4)
             build_records_kernel<4><<<ceil_div(R, 256), 256, 0, stream>>>(R, P, sorted_keys, point_list, g.means2D,
-                g.depths, g.conic_opacity, features, feature_view_stride, vp.grid_x, vp.tiles, records, masks, ranges);
+                g.depths, g.conic_opacity, features, feature_view_stride, kp, raw, vp.grid_x, vp.tiles, records, masks, ranges);
         else
             build_records_kernel<3><<<ceil_div(R, 256), 256, 0, stream>>>(R, P, sorted_keys, point_list, g.means2D,
-                g.depths, g.conic_opacity, features, feature_view_stride, vp.grid_x, vp.tiles, records, masks, ranges);
+                g.depths, g.conic_opacity, features, feature_view_stride, kp, raw, vp.grid_x, vp.tiles, records, masks, ranges);
         count_launch();
     }
     return 0;

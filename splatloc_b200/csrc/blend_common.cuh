@@ -127,6 +127,29 @@ __device__ __forceinline__ uint32_t patch_mask(float cx, float cy, const float4&
     return m & exact;
 }
 
+// The feature channels of Gaussian `id` as the blend kernels read them.  `kp` != nullptr: raw-parameter
+// mode, `features` holds f_dc (P, 3) and the colour is its degree-0 SH evaluation (common.cuh), with the
+// key-point score as the 4th channel.
+template <int C>
+__device__ __forceinline__ float4 gather_features(const float* __restrict__ features, const float* __restrict__ kp,
+                                                  bool raw, uint32_t id)
+{
+    float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (raw) {
+        f.x = act_sh0_colour(features[id * 3 + 0]);
+        f.y = act_sh0_colour(features[id * 3 + 1]);
+        f.z = act_sh0_colour(features[id * 3 + 2]);
+        if (C == 4) f.w = kp[id];
+    } else if (C == 4) {
+        f = reinterpret_cast<const float4*>(features)[id];
+    } else {
+        f.x = features[id * C + 0];
+        if (C > 1) f.y = features[id * C + 1];
+        if (C > 2) f.z = features[id * C + 2];
+    }
+    return f;
+}
+
 // Shared-space (32-bit) addressing done by hand: with generic pointers the compiler re-derives the
 // CTA's shared window base (S2R SR_CgaCtaId + shifts) inside the inner loop.
 __device__ __forceinline__ uint32_t smem_addr(const void* p)

@@ -260,7 +260,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
                         const float* viewmatrix, const float* projmatrix, const float* cam_pos,
                         float tan_fovx, float tan_fovy, int prefiltered,
                         float* out_color, float* out_depth, float* out_alpha, int* radii, int* n_touched,
-                        int debug, void* stream_, int max_pairs, int* status)
+                        int debug, void* stream_, int max_pairs, int* status, const RawParams* raw = nullptr)
 {
     g_error[0] = 0;
     const bool nosync = max_pairs >= 0;
@@ -332,7 +332,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         StageTimer t(ST_PREPROCESS, stream);
         rc = launch_preprocess(P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
                                colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered != 0, radii,
-                               geom, img.tile_counts, stream);
+                               geom, img.tile_counts, raw, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess");
@@ -393,7 +393,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
             rc = launch_tile_sort(P, C, info.max_pairs, nosync ? -1 : (int)info.n_large, img.ranges,
                                   img.tile_order, img.large_tiles, vp, bin.point_list_keys_unsorted,
                                   bin.point_list_unsorted, bin.point_list_keys, bin.point_list, geom, features,
-                                  feature_view_stride, bin.records, bin.masks, img.bin_info, stream);
+                                  feature_view_stride, raw, bin.records, bin.masks, img.bin_info, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "tile sort");
@@ -418,7 +418,7 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
         {
             StageTimer t(ST_RANGES, stream);
             rc = launch_build_records(R, P, C, bin.point_list_keys, bin.point_list, geom, features,
-                                      feature_view_stride, vp, bin.records, bin.masks, img.ranges, stream);
+                                      feature_view_stride, raw, vp, bin.records, bin.masks, img.ranges, stream);
         }
         if (rc) return rc;
         SL_STAGE(dbg, stream, "pair records");
@@ -549,7 +549,7 @@ int sl_backward_ext(int P, int D, int M, int R, int C,
                              dL_ddepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, debug, stream_);
 }
 
-int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
+static int backward_impl(int n_views, int P, int D, int M, int R, int C,
                       const float* background, int width, int height,
                       const float* means3D, const float* shs, const float* colors_precomp,
                       const float* scales, float scale_modifier, const float* rotations,
@@ -561,7 +561,8 @@ int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
                       float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
                       float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
                       float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
-                      int debug, void* stream_)
+                      int debug, void* stream_, const RawParams* raw, const float* raw_opacities,
+                      float* dL_dfdc, float* dL_dkp)
 {
     g_error[0] = 0;
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -624,11 +625,113 @@ int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
         rc = launch_preprocess_backward(P, D, M, C, means3D, radii, shs, geom.clamped, pose_only ? nullptr : scales,
                                         rotations, cov3D_ptr, viewmatrices, projmatrices, cam_positions, vp, dL_dmean2D,
                                         dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D,
-                                        pose_only ? nullptr : dL_dsh, dL_dscale, dL_drot, dL_dtau, stream);
+                                        pose_only ? nullptr : dL_dsh, dL_dscale, dL_drot, dL_dtau,
+                                        pose_only ? nullptr : raw, raw_opacities, colors_precomp, dL_dopacity, dL_dfdc,
+                                        dL_dkp, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess backward");
     return 0;
+}
+
+int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
+                      const float* background, int width, int height,
+                      const float* means3D, const float* shs, const float* colors_precomp,
+                      const float* scales, float scale_modifier, const float* rotations,
+                      const float* cov3D_precomp, const float* viewmatrices, const float* projmatrices,
+                      const float* cam_positions, float tan_fovx, float tan_fovy, const int* radii,
+                      char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                      const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                      const float* dL_dpix_alpha,
+                      float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                      float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                      float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                      int debug, void* stream_)
+{
+    return backward_impl(n_views, P, D, M, R, C, background, width, height, means3D, shs, colors_precomp, scales,
+                         scale_modifier, rotations, cov3D_precomp, viewmatrices, projmatrices, cam_positions, tan_fovx,
+                         tan_fovy, radii, geometry_chunk, binning_chunk, image_chunk, accum_alphas, dL_dpix,
+                         dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+                         dL_ddepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, debug, stream_, nullptr,
+                         nullptr, nullptr, nullptr);
+}
+
+// ---- render() with its pre-processing inside --------------------------------
+static int check_render_args(const char* who, int scale_dim, const float* features_dc, const float* raw_opacity,
+                             const float* raw_scaling, const float* raw_rotation)
+{
+    if (scale_dim != 1 && scale_dim != 3) {
+        set_error("%s: scale_dim must be 3, or 1 for isotropic Gaussians (got %d)", who, scale_dim);
+        return SL_ERR_ARGUMENT;
+    }
+    if (!features_dc || !raw_opacity || !raw_scaling || !raw_rotation) {
+        set_error("%s: features_dc, raw_opacity, raw_scaling and raw_rotation are required", who);
+        return SL_ERR_ARGUMENT;
+    }
+    return 0;
+}
+
+int sl_forward_render(sl_alloc_fn geometry_alloc, void* geometry_ctx,
+                      sl_alloc_fn binning_alloc, void* binning_ctx,
+                      sl_alloc_fn image_alloc, void* image_ctx,
+                      int n_views, int P, const float* background, int width, int height,
+                      const float* means3D, const float* features_dc, const float* kp_score,
+                      const float* raw_opacity, const float* raw_scaling, int scale_dim, float scale_modifier,
+                      const float* raw_rotation, const uint8_t* tile_mask,
+                      const float* viewmatrices, const float* projmatrices, const float* cam_positions,
+                      float tan_fovx, float tan_fovy,
+                      float* out_color, float* out_depth, float* out_alpha, int* radii,
+                      int max_pairs, int* status, int debug, void* stream_)
+{
+    g_error[0] = 0;
+    if (P > 0) {
+        const int rc = check_render_args("sl_forward_render", scale_dim, features_dc, raw_opacity, raw_scaling, raw_rotation);
+        if (rc) return rc;
+    }
+    if (max_pairs >= 0 && status == nullptr) {
+        set_error("sl_forward_render: max_pairs >= 0 (no read-back) needs a device status word");
+        return SL_ERR_ARGUMENT;
+    }
+    const RawParams raw = {kp_score, scale_dim};
+    return forward_impl(geometry_alloc, geometry_ctx, binning_alloc, binning_ctx, image_alloc, image_ctx, n_views, P,
+                        /*D=*/0, /*M=*/0, kp_score != nullptr ? 4 : 3, background, width, height, means3D, nullptr,
+                        features_dc, raw_opacity, raw_scaling, scale_modifier, raw_rotation, nullptr, tile_mask,
+                        viewmatrices, projmatrices, cam_positions, tan_fovx, tan_fovy, /*prefiltered=*/0, out_color,
+                        out_depth, out_alpha, radii, nullptr, max_pairs >= 0 ? 0 : debug, stream_,
+                        max_pairs < 0 ? -1 : max_pairs, max_pairs >= 0 ? status : nullptr, &raw);
+}
+
+int sl_backward_render(int n_views, int P, int R, const float* background, int width, int height,
+                       const float* means3D, const float* features_dc, const float* kp_score,
+                       const float* raw_opacity, const float* raw_scaling, int scale_dim, float scale_modifier,
+                       const float* raw_rotation,
+                       const float* viewmatrices, const float* projmatrices, const float* cam_positions,
+                       float tan_fovx, float tan_fovy, const int* radii,
+                       char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                       const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                       const float* dL_dpix_alpha,
+                       float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dcolor,
+                       float* dL_ddepth, float* dL_dcov3D,
+                       float* dL_dmean3D, float* dL_dfeatures_dc, float* dL_dkp_score, float* dL_draw_opacity,
+                       float* dL_draw_scaling, float* dL_draw_rotation, int debug, void* stream_)
+{
+    g_error[0] = 0;
+    if (P > 0) {
+        const int rc = check_render_args("sl_backward_render", scale_dim, features_dc, raw_opacity, raw_scaling, raw_rotation);
+        if (rc) return rc;
+        if (!dL_dmean3D || !dL_dfeatures_dc || !dL_draw_opacity || !dL_draw_scaling || !dL_draw_rotation ||
+            (kp_score != nullptr && !dL_dkp_score)) {
+            set_error("sl_backward_render: an output pointer is NULL");
+            return SL_ERR_ARGUMENT;
+        }
+    }
+    const RawParams raw = {kp_score, scale_dim};
+    return backward_impl(n_views, P, 0, 0, R, kp_score != nullptr ? 4 : 3, background, width, height, means3D, nullptr,
+                         features_dc, raw_scaling, scale_modifier, raw_rotation, nullptr, viewmatrices, projmatrices,
+                         cam_positions, tan_fovx, tan_fovy, radii, geometry_chunk, binning_chunk, image_chunk,
+                         accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic,
+                         dL_draw_opacity, dL_dcolor, dL_ddepth, dL_dmean3D, dL_dcov3D, nullptr, dL_draw_scaling,
+                         dL_draw_rotation, nullptr, debug, stream_, &raw, raw_opacity, dL_dfeatures_dc, dL_dkp_score);
 }
 
 int sl_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

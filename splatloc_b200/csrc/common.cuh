@@ -142,6 +142,31 @@ __device__ __forceinline__ bool in_frustum_ndc(const f3& p, const float* __restr
            (y > -1 - xy_pad) && (y < 1. + xy_pad);
 }
 
+// ---- raw-parameter mode: the activations SplatLoc's render() applies in PyTorch
+// before it calls the rasterizer (gaussian_model.py:75-110 getters, gaussian_renderer/__init__.py:85-102),
+// evaluated inside the kernels.  Written to round like the PyTorch float32 kernels they replace:
+//   opacity  = sigmoid(x)            = 1 / (1 + exp(-x))
+//   scale    = exp(x)
+//   rotation = x / max(|x|, 1e-12)   (torch.nn.functional.normalize)
+//   colour   = max(C0 * f_dc + 0.5, 0), a separate multiply and add (eval_sh at degree 0, sh_utils.py:73;
+//              then clamp_min(. + 0.5, 0))
+struct RawParams {
+    const float* kp_score;   // [P] appended as the 4th feature channel (render()'s torch.cat), or NULL
+    int scale_dim;           // 3, or 1 for isotropic Gaussians (render() repeats the one scale)
+};
+
+__device__ __forceinline__ float act_sigmoid(float x) { return 1.0f / (1.0f + expf(-x)); }
+__device__ __forceinline__ float act_sh0_colour(float f)
+{
+    return fmaxf(__fadd_rn(__fmul_rn(0.28209479177387814f, f), 0.5f), 0.0f);
+}
+__device__ __forceinline__ float4 act_normalize(float4 q)
+{
+    const float n = sqrtf(q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w);
+    const float d = fmaxf(n, 1e-12f);
+    return make_float4(q.x / d, q.y / d, q.z / d, q.w / d);
+}
+
 __host__ __device__ __forceinline__ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

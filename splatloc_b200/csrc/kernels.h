@@ -28,7 +28,7 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
                       const float* viewmatrices, const float* projmatrices, const float* cam_positions,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      uint32_t* tile_counts, cudaStream_t stream);
+                      uint32_t* tile_counts, const RawParams* raw, cudaStream_t stream);
 
 // K10: frustum visibility (reference: checkFrustum, rasterizer_impl.cu:54-66).
 int launch_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,
@@ -58,7 +58,8 @@ int launch_tile_sort(int P, int C, uint32_t longest, int n_large_launch, const u
                      const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
                      const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                      uint32_t* point_list, const GeomState& g, const float* features, size_t feature_view_stride,
-                     PairRecord* records, uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream);
+                     const RawParams* raw, PairRecord* records, uint8_t* masks, const BinInfo* dev_info,
+                     cudaStream_t stream);
 
 // K4: stable LSD radix sort of n (u64 key, u32 value) pairs on key bits [0, end_bit);
 // result in (keys_out, vals_out); the inputs are preserved.
@@ -69,7 +70,7 @@ int launch_sort_pairs(const uint64_t* keys_in, const uint32_t* vals_in, uint64_t
 // Gather, once per frame, everything the blend kernels read for each sorted pair (PairRecord) plus
 // the per-patch reach mask, and write the per-tile ranges (reference: identifyTileRanges).
 int launch_build_records(int R, int P, int C, const uint64_t* sorted_keys, const uint32_t* point_list,
-                         const GeomState& g, const float* features, size_t feature_view_stride,
+                         const GeomState& g, const float* features, size_t feature_view_stride, const RawParams* raw,
                          const ViewParams& vp, PairRecord* records, uint8_t* masks, uint2* ranges,
                          cudaStream_t stream);
 
@@ -91,6 +92,10 @@ int launch_blend_backward(int P, int C, const ViewParams& vp, const uint2* range
                           float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity, float* dL_dcolor,
                           size_t color_view_stride, float* dL_ddepth, cudaStream_t stream);
 
+// `raw` != nullptr (raw-parameter mode, common.cuh): `scales` / `rotations` / `raw_opacities` are the raw
+// parameters, `dL_dcolor` arrives as the gradient of the activated colour (P, C) and every gradient is
+// taken through its activation: dL_dscale, dL_drot, dL_dopacity (in place) become gradients of the raw
+// parameters, dL_dfdc (P, 3) receives the gradient of f_dc and dL_dkp (P) the 4th colour channel's.
 // K8+K9 fused: per-Gaussian backward (reference: BACKWARD::preprocess, backward.cu:1810-1876).  One
 // thread carries a Gaussian through all views and stores each gradient once (the sum over the views).
 // dL_dmean3D == nullptr: only the camera-pose gradients dL_dtau [views, 6] are wanted.
@@ -101,7 +106,8 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
                                const float* dL_dcolor, size_t color_view_stride, const float* dL_ddepth,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
-                               cudaStream_t stream);
+                               const RawParams* raw, const float* raw_opacities, const float* features_dc,
+                               float* dL_dopacity, float* dL_dfdc, float* dL_dkp, cudaStream_t stream);
 
 // K11-K15: mean squared distance to the 3 nearest neighbours (reference: SimpleKNN::knn,
 // simple_knn.cu:186-221).  `scratch` must hold knn_scratch_bytes(P) bytes.

@@ -78,6 +78,7 @@ __device__ __forceinline__ f3 cov2d_ewa(const f3& mean, float focal_x, float foc
 
 // One Gaussian.  Returns the number of tiles it touches (0 if culled, degenerate or off-screen)
 // and its tile rectangle.
+template <bool RAW>
 __device__ __forceinline__ uint32_t
 preprocess_one(int idx, int D, int M, int C,
                   const float* __restrict__ means3D,
@@ -91,7 +92,7 @@ preprocess_one(int idx, int D, int M, int C,
                   const float* __restrict__ viewmatrix,
                   const float* __restrict__ projmatrix,
                   const float* __restrict__ cam_pos,
-                  ViewParams vp, bool prefiltered,
+                  ViewParams vp, bool prefiltered, int scale_dim,
                   int* __restrict__ radii,
                   float2* __restrict__ means2D,
                   float* __restrict__ depths,
@@ -107,7 +108,9 @@ preprocess_one(int idx, int D, int M, int C,
     f3 p_orig = {means3D[3 * idx], means3D[3 * idx + 1], means3D[3 * idx + 2]};
     f3 p_view = xform_4x3(p_orig, viewmatrix);
     if (!prefiltered && !in_frustum_ndc(p_orig, projmatrix)) return 0;
-    if (opacities[idx] < 0.0001f) return 0;
+    // RAW: `opacities`, `scales`, `rotations` hold the optimiser's raw parameters (common.cuh)
+    const float opacity = RAW ? act_sigmoid(opacities[idx]) : opacities[idx];
+    if (opacity < 0.0001f) return 0;
 
     float4 p_hom = xform_4x4(p_orig, projmatrix);
     float p_w = 1.0f / (p_hom.w + 0.0000001f);
@@ -117,8 +120,18 @@ preprocess_one(int idx, int D, int M, int C,
     if (cov3D_precomp != nullptr) {
         cov3D = cov3D_precomp + idx * 6;
     } else {
-        f3 s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+        f3 s;
         float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        if (RAW) {
+            if (scale_dim == 1) {
+                s.x = s.y = s.z = expf(scales[idx]);
+            } else {
+                s = {expf(scales[3 * idx]), expf(scales[3 * idx + 1]), expf(scales[3 * idx + 2])};
+            }
+            q = act_normalize(q);
+        } else {
+            s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+        }
         cov3d_from_scale_rot(s, vp.scale_modifier, q, cov3Ds + idx * 6);
         cov3D = cov3Ds + idx * 6;
     }
@@ -164,7 +177,7 @@ preprocess_one(int idx, int D, int M, int C,
     rect_min = rmin;
     rect_max = rmax;
 
-    conic_opacity[idx] = {conic.x, conic.y, conic.z, opacities[idx]};
+    conic_opacity[idx] = {conic.x, conic.y, conic.z, opacity};
 
     if (colors_precomp == nullptr) {
         f3 campos = {cam_pos[0], cam_pos[1], cam_pos[2]};
@@ -185,6 +198,7 @@ preprocess_one(int idx, int D, int M, int C,
 // are counted for the tile-bucketed binning (one counter per 128-byte line, tiles numbered
 // view-major).  A Gaussian covering up to 8 tiles adds its own counts; one covering more (near or
 // very flat splats cover thousands) is counted by its whole warp.
+template <bool RAW>
 __global__ void __launch_bounds__(PREPROCESS_THREADS)
 preprocess_kernel(int P, int D, int M, int C,
                   const float* __restrict__ means3D,
@@ -198,7 +212,7 @@ preprocess_kernel(int P, int D, int M, int C,
                   const float* __restrict__ viewmatrices,
                   const float* __restrict__ projmatrices,
                   const float* __restrict__ cam_positions,
-                  ViewParams vp, bool prefiltered,
+                  ViewParams vp, bool prefiltered, int scale_dim,
                   int* __restrict__ radii,
                   float2* __restrict__ means2D,
                   float* __restrict__ depths,
@@ -221,8 +235,8 @@ preprocess_kernel(int P, int D, int M, int C,
     uint2 rmin = make_uint2(0, 0), rmax = make_uint2(0, 0);
     uint32_t touched = 0;
     if (idx < P) {
-        touched = preprocess_one(idx, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
-                                 colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, radii + voff,
+        touched = preprocess_one<RAW>(idx, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
+                                 colors_precomp, viewmatrix, projmatrix, cam_pos, vp, prefiltered, scale_dim, radii + voff,
                                  means2D + voff, depths + voff, cov3Ds, rgb + 3 * voff, clamped + 3 * voff,
                                  conic_opacity + voff, rmin, rmax);
         tiles_touched[voff + idx] = touched;
@@ -262,13 +276,17 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
                       const float* cov3D_precomp, const uint8_t* tile_mask, const float* colors_precomp,
                       const float* viewmatrices, const float* projmatrices, const float* cam_positions,
                       const ViewParams& vp, bool prefiltered, int* radii, GeomState& g,
-                      uint32_t* tile_counts, cudaStream_t stream)
+                      uint32_t* tile_counts, const RawParams* raw, cudaStream_t stream)
 {
     const dim3 grid(ceil_div(P, PREPROCESS_THREADS), vp.views);
-    preprocess_kernel<<<grid, PREPROCESS_THREADS, 0, stream>>>(
-        P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,
-        colors_precomp, viewmatrices, projmatrices, cam_positions, vp, prefiltered, radii, g.means2D, g.depths,
-        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts); count_launch();
+#define SL_LAUNCH_PRE(RR, SD)                                                                                     \
+    preprocess_kernel<RR><<<grid, PREPROCESS_THREADS, 0, stream>>>(                                               \
+        P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,                         \
+        colors_precomp, viewmatrices, projmatrices, cam_positions, vp, prefiltered, SD, radii, g.means2D, g.depths, \
+        g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts)
+    if (raw != nullptr) SL_LAUNCH_PRE(true, raw->scale_dim); else SL_LAUNCH_PRE(false, 3);
+#undef SL_LAUNCH_PRE
+    count_launch();
     return 0;
 }
 

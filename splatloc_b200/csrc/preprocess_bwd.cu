@@ -215,20 +215,19 @@ per_gaussian_backward(int idx, int D, int M, int C,
 
 // dL/dcov3D (summed over the views) -> dL/dscale, dL/drotation.  The map from the covariance gradient
 // is linear and view-independent, so it runs once per Gaussian however many views there are.
+// `s_act`, `q`: the activated scale and rotation.  Returns the gradients w.r.t. (scale_modifier * s_act)
+// -- the modifier's factor is not applied, as in the reference (backward.cu:668-731) -- and w.r.t. q.
 __device__ __forceinline__ void
-cov3d_to_scale_rot_backward(int idx, float scale_modifier, const float* __restrict__ scales,
-                            const float* __restrict__ rotations, const float (&g_cov)[6],
-                            float* __restrict__ dL_dscale, float* __restrict__ dL_drot)
+cov3d_to_scale_rot_backward(float scale_modifier, const f3 s_act, const float4 q, const float (&g_cov)[6],
+                            f3& d_scale, float4& d_rot)
 {
     {
-        const float4 q = reinterpret_cast<const float4*>(rotations)[idx];
         const float r = q.x, x = q.y, y = q.z, z = q.w;
         mat3 R = mat3_cols(
             1.f - 2.f * (y * y + z * z), 2.f * (x * y - r * z), 2.f * (x * z + r * y),
             2.f * (x * y + r * z), 1.f - 2.f * (x * x + z * z), 2.f * (y * z - r * x),
             2.f * (x * z - r * y), 2.f * (y * z + r * x), 1.f - 2.f * (x * x + y * y));
-        const f3 s = {scale_modifier * scales[3 * idx], scale_modifier * scales[3 * idx + 1],
-                      scale_modifier * scales[3 * idx + 2]};
+        const f3 s = {scale_modifier * s_act.x, scale_modifier * s_act.y, scale_modifier * s_act.z};
         mat3 S = mat3_cols(1.0f, 0.0f, 0.0f, 0.0f, 1.0f, 0.0f, 0.0f, 0.0f, 1.0f);
         S.c[0][0] = s.x;
         S.c[1][1] = s.y;
@@ -251,9 +250,9 @@ cov3d_to_scale_rot_backward(int idx, float scale_modifier, const float* __restri
         mat3 Rt = transpose(R);
         mat3 dL_dMt = transpose(dL_dM);
 
-        dL_dscale[3 * idx + 0] = Rt.c[0][0] * dL_dMt.c[0][0] + Rt.c[0][1] * dL_dMt.c[0][1] + Rt.c[0][2] * dL_dMt.c[0][2];
-        dL_dscale[3 * idx + 1] = Rt.c[1][0] * dL_dMt.c[1][0] + Rt.c[1][1] * dL_dMt.c[1][1] + Rt.c[1][2] * dL_dMt.c[1][2];
-        dL_dscale[3 * idx + 2] = Rt.c[2][0] * dL_dMt.c[2][0] + Rt.c[2][1] * dL_dMt.c[2][1] + Rt.c[2][2] * dL_dMt.c[2][2];
+        d_scale.x = Rt.c[0][0] * dL_dMt.c[0][0] + Rt.c[0][1] * dL_dMt.c[0][1] + Rt.c[0][2] * dL_dMt.c[0][2];
+        d_scale.y = Rt.c[1][0] * dL_dMt.c[1][0] + Rt.c[1][1] * dL_dMt.c[1][1] + Rt.c[1][2] * dL_dMt.c[1][2];
+        d_scale.z = Rt.c[2][0] * dL_dMt.c[2][0] + Rt.c[2][1] * dL_dMt.c[2][1] + Rt.c[2][2] * dL_dMt.c[2][2];
 
 #pragma unroll
         for (int rr = 0; rr < 3; ++rr) {
@@ -267,7 +266,7 @@ cov3d_to_scale_rot_backward(int idx, float scale_modifier, const float* __restri
         dq.y = 2 * y * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * z * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * r * (dL_dMt.c[1][2] - dL_dMt.c[2][1]) - 4 * x * (dL_dMt.c[2][2] + dL_dMt.c[1][1]);
         dq.z = 2 * x * (dL_dMt.c[1][0] + dL_dMt.c[0][1]) + 2 * r * (dL_dMt.c[2][0] - dL_dMt.c[0][2]) + 2 * z * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * y * (dL_dMt.c[2][2] + dL_dMt.c[0][0]);
         dq.w = 2 * r * (dL_dMt.c[0][1] - dL_dMt.c[1][0]) + 2 * x * (dL_dMt.c[2][0] + dL_dMt.c[0][2]) + 2 * y * (dL_dMt.c[1][2] + dL_dMt.c[2][1]) - 4 * z * (dL_dMt.c[1][1] + dL_dMt.c[0][0]);
-        reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+        d_rot = dq;
     }
 }
 
@@ -279,7 +278,7 @@ cov3d_to_scale_rot_backward(int idx, float scale_modifier, const float* __restri
 #ifndef SL_PBWD_MULTI_CTAS
 #define SL_PBWD_MULTI_CTAS 3
 #endif
-template <bool MULTI>
+template <bool MULTI, bool RAW>
 __global__ void __launch_bounds__(256, MULTI ? SL_PBWD_MULTI_CTAS : 4)
 preprocess_backward_kernel(int P, int D, int M, int C,
                            const float* __restrict__ means3D, const int* __restrict__ radii,
@@ -292,7 +291,9 @@ preprocess_backward_kernel(int P, int D, int M, int C,
                            float* __restrict__ dL_dmeans, const float* __restrict__ dL_dcolor,
                            size_t color_view_stride, const float* __restrict__ dL_ddepth,
                            float* __restrict__ dL_dcov, float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,
-                           float* __restrict__ dL_drot, float* dL_dtau)
+                           float* __restrict__ dL_drot, float* dL_dtau,
+                           int scale_dim, const float* __restrict__ raw_opacities, const float* __restrict__ features_dc,
+                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dfdc, float* __restrict__ dL_dkp)
 {
     __shared__ float s_pose[8][6];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -338,7 +339,51 @@ preprocess_backward_kernel(int P, int D, int M, int C,
     dL_dmeans[3 * idx + 2] = g_mean.z;
 #pragma unroll
     for (int i = 0; i < 6; i++) dL_dcov[6 * idx + i] = g_cov[i];
-    if (scales != nullptr) cov3d_to_scale_rot_backward(idx, vp.scale_modifier, scales, rotations, g_cov, dL_dscale, dL_drot);
+    if (scales != nullptr) {
+        float4 q = reinterpret_cast<const float4*>(rotations)[idx];
+        f3 s, ds;
+        float4 dq;
+        if (RAW) {
+            // the optimiser's raw parameters: activate as the forward did (common.cuh) ...
+            if (scale_dim == 1) {
+                s.x = s.y = s.z = expf(scales[idx]);
+            } else {
+                s = {expf(scales[3 * idx]), expf(scales[3 * idx + 1]), expf(scales[3 * idx + 2])};
+            }
+            const float4 q_raw = q;
+            q = act_normalize(q_raw);
+            cov3d_to_scale_rot_backward(vp.scale_modifier, s, q, g_cov, ds, dq);
+            // ... and take the gradients back through the activations: exp' = exp, and for y = x / |x|
+            // dx = (dy - y (y . dy)) / |x|
+            ds.x *= s.x; ds.y *= s.y; ds.z *= s.z;
+            if (scale_dim == 1) {
+                dL_dscale[idx] = ds.x + ds.y + ds.z;       // render() repeats the one scale three times
+            } else {
+                dL_dscale[3 * idx + 0] = ds.x; dL_dscale[3 * idx + 1] = ds.y; dL_dscale[3 * idx + 2] = ds.z;
+            }
+            const float n = fmaxf(sqrtf(q_raw.x * q_raw.x + q_raw.y * q_raw.y + q_raw.z * q_raw.z + q_raw.w * q_raw.w), 1e-12f);
+            const float yd = q.x * dq.x + q.y * dq.y + q.z * dq.z + q.w * dq.w;
+            reinterpret_cast<float4*>(dL_drot)[idx] = make_float4((dq.x - q.x * yd) / n, (dq.y - q.y * yd) / n,
+                                                                  (dq.z - q.z * yd) / n, (dq.w - q.w * yd) / n);
+        } else {
+            s = {scales[3 * idx], scales[3 * idx + 1], scales[3 * idx + 2]};
+            cov3d_to_scale_rot_backward(vp.scale_modifier, s, q, g_cov, ds, dq);
+            dL_dscale[3 * idx + 0] = ds.x; dL_dscale[3 * idx + 1] = ds.y; dL_dscale[3 * idx + 2] = ds.z;
+            reinterpret_cast<float4*>(dL_drot)[idx] = dq;
+        }
+    }
+    if (RAW) {
+        // sigmoid' = o (1 - o), in place; colour = max(C0 f_dc + 0.5, 0) (PyTorch's clamp passes the
+        // gradient where the input is >= the bound); the 4th channel is the key-point score itself
+        const float o = act_sigmoid(raw_opacities[idx]);
+        dL_dopacity[idx] = dL_dopacity[idx] * (1.0f - o) * o;
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const float pre = __fadd_rn(__fmul_rn(0.28209479177387814f, features_dc[3 * idx + ch]), 0.5f);
+            dL_dfdc[3 * idx + ch] = pre >= 0.0f ? 0.28209479177387814f * dL_dcolor[idx * C + ch] : 0.0f;
+        }
+        if (C == 4 && dL_dkp != nullptr) dL_dkp[idx] = dL_dcolor[idx * C + 3];
+    }
 }
 
 int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
@@ -348,14 +393,20 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
                                const float* dL_dmean2D, const float* dL_dconic, float* dL_dmean3D,
                                const float* dL_dcolor, size_t color_view_stride, const float* dL_ddepth,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
-                               cudaStream_t stream)
+                               const RawParams* raw, const float* raw_opacities, const float* features_dc,
+                               float* dL_dopacity, float* dL_dfdc, float* dL_dkp, cudaStream_t stream)
 {
-#define SL_LAUNCH_PBWD(MM)                                                                                       \
-    preprocess_backward_kernel<MM><<<ceil_div(P, 256), 256, 0, stream>>>(                                        \
+    const int scale_dim = raw != nullptr ? raw->scale_dim : 3;
+#define SL_LAUNCH_PBWD(MM, RR)                                                                                   \
+    preprocess_backward_kernel<MM, RR><<<ceil_div(P, 256), 256, 0, stream>>>(                                    \
         P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrices, projmatrices,         \
         cam_positions, vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D, \
-        dL_dsh, dL_dscale, dL_drot, dL_dtau)
-    if (vp.views > 1) SL_LAUNCH_PBWD(true); else SL_LAUNCH_PBWD(false);
+        dL_dsh, dL_dscale, dL_drot, dL_dtau, scale_dim, raw_opacities, features_dc, dL_dopacity, dL_dfdc, dL_dkp)
+    if (raw != nullptr) {
+        if (vp.views > 1) SL_LAUNCH_PBWD(true, true); else SL_LAUNCH_PBWD(false, true);
+    } else {
+        if (vp.views > 1) SL_LAUNCH_PBWD(true, false); else SL_LAUNCH_PBWD(false, false);
+    }
 #undef SL_LAUNCH_PBWD
     count_launch();
     return 0;

@@ -255,13 +255,13 @@ __device__ __forceinline__ void cta_bitonic_sort(unsigned long long (&key)[E], u
 }
 
 // Sort one tile's segment (n <= E * THREADS pairs) and write every per-pair output.
-template <int C, int E, int THREADS>
+template <int C, int E, int THREADS, bool RAW>
 __device__ __forceinline__ void sort_and_emit_tile(
     uint32_t tile, uint32_t local_tile, uint2 range, int grid_x, unsigned long long* smem,
     const uint64_t* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
     uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
     const float2* __restrict__ means2D, const float* __restrict__ depths,
-    const float4* __restrict__ conic_opacity, const float* __restrict__ features,
+    const float4* __restrict__ conic_opacity, const float* __restrict__ features, const float* __restrict__ kp,
     PairRecord* __restrict__ records, uint8_t* __restrict__ masks)
 {
     const int tid = threadIdx.x, lane = tid & 31;
@@ -287,14 +287,7 @@ __device__ __forceinline__ void sort_and_emit_tile(
             keys_out[slot] = ((unsigned long long)tile << 32) | (k >> 32);
             const float2 xy = means2D[id];
             const float4 co = conic_opacity[id];
-            float4 f = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (C == 4) {
-                f = reinterpret_cast<const float4*>(features)[id];
-            } else {
-                f.x = features[id * C + 0];
-                if (C > 1) f.y = features[id * C + 1];
-                if (C > 2) f.z = features[id * C + 2];
-            }
+            const float4 f = gather_features<C>(features, kp, RAW, id);
             PairRecord rec;
             rec.xyd = make_float4(xy.x, xy.y, depths[id], __int_as_float((int)id));
             rec.co = co;
@@ -308,7 +301,7 @@ __device__ __forceinline__ void sort_and_emit_tile(
 // CTAs stride over the work list `tiles` (global, view-major tile numbers); a CTA handles segments
 // with min_len < n <= 16 * THREADS and picks the network size from n.  The per-Gaussian arrays are
 // those of the tile's view.
-template <int C, int THREADS>
+template <int C, int THREADS, bool RAW>
 __global__ void __launch_bounds__(THREADS, THREADS == 256 ? SL_SORT_MIN_CTAS : 1)
 tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ tiles, int n_listed, int grid_x,
                  int tiles_per_view, int P, uint32_t min_len,
@@ -316,15 +309,16 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  uint64_t* __restrict__ keys_out, uint32_t* __restrict__ point_list,
                  const float2* __restrict__ means2D, const float* __restrict__ depths,
                  const float4* __restrict__ conic_opacity, const float* __restrict__ features,
-                 size_t feature_view_stride,
+                 size_t feature_view_stride, const float* __restrict__ kp,
                  PairRecord* __restrict__ records, uint8_t* __restrict__ masks, const BinInfo* __restrict__ dev_info)
 {
     extern __shared__ __align__(16) unsigned long long s_key[];
     if (dev_info->overflow) return;
     // n_listed < 0: the host does not know how long the work list is (no read-back): the device does.
     const uint32_t listed = n_listed < 0 ? dev_info->n_large : (uint32_t)n_listed;
-    // grid-stride over the list: the long-segment launch is a few resident CTAs, not one per tile
-    for (uint32_t b = blockIdx.x; b < listed; b += gridDim.x) {
+    // The long-segment launch (1024 threads) is a few resident CTAs striding over its list; the
+    // 256-thread launch has one CTA per tile (a single trip: the loop would cost it registers).
+    for (uint32_t b = blockIdx.x; b < listed; b += (THREADS == 256 ? listed : gridDim.x)) {
         const uint32_t tile = tiles[b];
         const uint2 range = ranges[tile];
         const uint32_t n = range.y - range.x;
@@ -333,8 +327,9 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
         const size_t voff = (size_t)view * P;
         const float* feat = features + view * feature_view_stride;
 #define SL_SORT_CASE(EE)                                                                                         \
-    sort_and_emit_tile<C, EE, THREADS>(tile, local_tile, range, grid_x, s_key, keys_in, vals_in, keys_out, point_list, \
-                                       means2D + voff, depths + voff, conic_opacity + voff, feat, records, masks)
+    sort_and_emit_tile<C, EE, THREADS, RAW>(tile, local_tile, range, grid_x, s_key, keys_in, vals_in, keys_out, \
+                                       point_list, means2D + voff, depths + voff, conic_opacity + voff, feat, kp, \
+                                       records, masks)
         if (n <= 1u * THREADS) SL_SORT_CASE(1);
         else if (n <= 2u * THREADS) SL_SORT_CASE(2);
         else if (n <= 4u * THREADS) SL_SORT_CASE(4);
@@ -365,12 +360,12 @@ int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint
     return 0;
 }
 
-template <int C>
+template <int C, bool RAW>
 static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const uint2* ranges,
                               const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
                               const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                               uint32_t* point_list, const GeomState& g, const float* features,
-                              size_t feature_view_stride, PairRecord* records, uint8_t* masks,
+                              size_t feature_view_stride, const float* kp, PairRecord* records, uint8_t* masks,
                               const BinInfo* dev_info, cudaStream_t stream)
 {
     const int n_tiles = vp.tiles * vp.views;
@@ -381,13 +376,13 @@ static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const
     if (n_large_launch != 0) {
         constexpr int T = 1024;
         const size_t smem = (size_t)TILE_SORT_LARGE * sizeof(unsigned long long);
-        SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
+        SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T, RAW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 "tile sort smem attribute");
         const int listed = n_large_launch < 0 ? n_tiles : n_large_launch;
-        tile_sort_kernel<C, T><<<listed < 148 ? listed : 148, T, smem, stream>>>(
+        tile_sort_kernel<C, T, RAW><<<listed < 148 ? listed : 148, T, smem, stream>>>(
             ranges, large_tiles, n_large_launch < 0 ? -1 : n_large_launch, vp.grid_x, vp.tiles, P,
             (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
-            features, feature_view_stride, records, masks, dev_info);
+            features, feature_view_stride, kp, records, masks, dev_info);
         count_launch();
     }
     constexpr int T = 256;
@@ -395,9 +390,9 @@ static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const
     if (longest > (uint32_t)TILE_SORT_SMALL) longest = (uint32_t)TILE_SORT_SMALL;
     uint32_t pad = T;
     while (pad < longest) pad <<= 1;
-    tile_sort_kernel<C, T><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
+    tile_sort_kernel<C, T, RAW><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
         ranges, tile_order, n_tiles, vp.grid_x, vp.tiles, P, 0u, keys_in, vals_in, keys_out, point_list, g.means2D,
-        g.depths, g.conic_opacity, features, feature_view_stride, records, masks, dev_info);
+        g.depths, g.conic_opacity, features, feature_view_stride, kp, records, masks, dev_info);
     count_launch();
     return 0;
 }
@@ -406,15 +401,21 @@ int launch_tile_sort(int P, int C, uint32_t longest, int n_large_launch, const u
                      const uint32_t* tile_order, const uint32_t* large_tiles, const ViewParams& vp,
                      const uint64_t* keys_in, const uint32_t* vals_in, uint64_t* keys_out,
                      uint32_t* point_list, const GeomState& g, const float* features, size_t feature_view_stride,
-                     PairRecord* records, uint8_t* masks, const BinInfo* dev_info, cudaStream_t stream)
+                     const RawParams* rawp, PairRecord* records, uint8_t* masks, const BinInfo* dev_info,
+                     cudaStream_t stream)
 {
-    if (C == 4)
-        return tile_sort_launches<4>(P, longest, n_large_launch, ranges, tile_order, large_tiles, vp, keys_in, vals_in,
-                                     keys_out, point_list, g, features, feature_view_stride, records, masks, dev_info,
-                                     stream);
-    return tile_sort_launches<3>(P, longest, n_large_launch, ranges, tile_order, large_tiles, vp, keys_in, vals_in,
-                                 keys_out, point_list, g, features, feature_view_stride, records, masks, dev_info,
-                                 stream);
+    const float* kp = rawp != nullptr ? rawp->kp_score : nullptr;
+#define SL_SORT_LAUNCH(CC, RR)                                                                                      \
+    return tile_sort_launches<CC, RR>(P, longest, n_large_launch, ranges, tile_order, large_tiles, vp, keys_in, vals_in, \
+                                      keys_out, point_list, g, features, feature_view_stride, kp, records, masks,    \
+                                      dev_info, stream)
+    if (rawp != nullptr) {
+        if (C == 4) SL_SORT_LAUNCH(4, true);
+        SL_SORT_LAUNCH(3, true);
+    }
+    if (C == 4) SL_SORT_LAUNCH(4, false);
+    SL_SORT_LAUNCH(3, false);
+#undef SL_SORT_LAUNCH
 }
 
 }  // namespace sl
