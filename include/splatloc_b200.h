@@ -283,6 +283,53 @@ int sl_backward_render(int n_views, int P, int R, const float* background, int w
                        float* dL_dmean3D, float* dL_dfeatures_dc, float* dL_dkp_score, float* dL_draw_opacity,
                        float* dL_draw_scaling, float* dL_draw_rotation, int debug, void* stream);
 
+/* ---- optimiser step and densification over the Gaussian store -----------
+ * Replaces, on device arrays the caller owns, what gaussian_splatting/scene/gaussian_model.py does
+ * with PyTorch indexing, torch.cat and optimizer-state surgery between two rasterizer calls.
+ *
+ * sl_adam_step: torch.optim.Adam(l, lr=0.0, eps=1e-15).step() (training_setup, :250-300) for up to 8
+ *   parameter groups in one launch; `step` is the 1-based step count (bias correction).  A group with
+ *   freeze_by_marker != 0 uses a zero gradient for rows whose marker[row] > marker_threshold
+ *   (train_gaussians.py:232-234 zeroes the position gradient of key primitives).
+ * sl_densify_stats: add_densification_stats (:677-679) and the max_radii2D update
+ *   (train_gaussians.py:241-244) for the n_views views of a window: means2D_grad [n_views, P, 3],
+ *   radii [n_views, P]; xyz_gradient_accum, denom, max_radii2D [P] are updated in place.
+ * sl_densify_plan + sl_densify_apply: densify_and_prune(max_grad, min_opacity, extent, max_screen_size)
+ *   (:650-675), i.e. densify_and_clone, densify_and_split (N = 2) and the final prune, as one
+ *   compaction.  _plan writes the selection flags and their prefix sums into `scratch`
+ *   (sl_densify_scratch_bytes(P) bytes) and four device counters totals[4] = {kept originals, clones,
+ *   split Gaussians whose children survive, split Gaussians}; the caller reads them back (the one
+ *   host synchronisation: the new size P' = totals[0] + totals[1] + 2 totals[2] sizes the output
+ *   arrays), provides `noise` [2 * totals[3], 3] standard-normal floats (the reference draws
+ *   torch.normal there; rows k * totals[3] + j belong to child k of the j-th split Gaussian), and
+ *   _apply writes every group's output rows: kept originals in ascending order, then clones, then first
+ *   children, then second children -- the reference's order.  Kept rows keep their Adam moments, new
+ *   rows get zeros; a group with exp_avg_in == NULL carries no moments.  The statistics of the new
+ *   store are all zero (densification_postfix :583-585): the caller zero-fills them.
+ *   use_size_test: max_screen_size was given (the reference then also prunes Gaussians larger than
+ *   0.1 * extent; its screen-size test reads statistics it has just reset and never fires).
+ *   primitive_reg: rows with marker > 0.005 are never pruned (:671-673).  grad_threshold must be > 0. */
+typedef struct {
+    float* param; const float* grad; float* exp_avg; float* exp_avg_sq;
+    int width; float lr; int freeze_by_marker;
+} sl_adam_group;
+typedef struct {
+    const float* param_in; float* param_out;
+    const float* exp_avg_in; float* exp_avg_out; const float* exp_avg_sq_in; float* exp_avg_sq_out;
+    int width;
+} sl_densify_group;
+int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, float beta1, float beta2, float eps,
+                 const float* marker, float marker_threshold, void* stream);
+int sl_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,
+                     float* denom, float* max_radii2D, void* stream);
+size_t sl_densify_scratch_bytes(int P);
+int sl_densify_plan(int P, const float* xyz_gradient_accum, const float* denom, const float* raw_scaling, int scale_dim,
+                    const float* raw_opacity, const float* marker, float grad_threshold, float percent_dense,
+                    float extent, float min_opacity, int use_size_test, int primitive_reg, char* scratch,
+                    size_t scratch_bytes, uint32_t* totals, void* stream);
+int sl_densify_apply(int P, int n_groups, const sl_densify_group* groups, int xyz_group, int scaling_group,
+                     int rotation_group, const char* scratch, const uint32_t* totals, const float* noise, void* stream);
+
 /* Frustum visibility, present[i] in {0,1}.  Replaces
  * CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:71-76,
  * rasterizer_impl.cu:379-391), bound by markVisible (DGR/rasterize_points.cu:215-234). */

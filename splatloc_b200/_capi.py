@@ -16,6 +16,16 @@ ALLOC_FN = C.CFUNCTYPE(C.c_void_p, C.c_void_p, C.c_size_t)
 
 _F = C.c_void_p  # every device pointer travels as an integer address
 
+class AdamGroup(C.Structure):          # sl_adam_group
+    _fields_ = [("param", C.c_void_p), ("grad", C.c_void_p), ("exp_avg", C.c_void_p), ("exp_avg_sq", C.c_void_p),
+                ("width", C.c_int), ("lr", C.c_float), ("freeze_by_marker", C.c_int)]
+
+
+class DensifyGroup(C.Structure):       # sl_densify_group
+    _fields_ = [("param_in", C.c_void_p), ("param_out", C.c_void_p), ("exp_avg_in", C.c_void_p), ("exp_avg_out", C.c_void_p),
+                ("exp_avg_sq_in", C.c_void_p), ("exp_avg_sq_out", C.c_void_p), ("width", C.c_int)]
+
+
 # name -> (restype, argtypes); kept in sync with include/splatloc_b200.h and
 # checked against the header's declarations by tests/test_capi_symbols.py.
 SIGNATURES = {
@@ -137,6 +147,14 @@ SIGNATURES = {
         _F, _F, _F, _F, _F, _F,                      # dL_dmean3D, dL_dfeatures_dc, dL_dkp_score, dL_draw_opacity/scaling/rotation
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
+    "sl_adam_step": (C.c_int, [C.c_int, C.c_int, C.POINTER(AdamGroup), C.c_int, C.c_float, C.c_float, C.c_float,
+                               _F, C.c_float, C.c_void_p]),
+    "sl_densify_stats": (C.c_int, [C.c_int, C.c_int, _F, _F, _F, _F, _F, C.c_void_p]),
+    "sl_densify_scratch_bytes": (C.c_size_t, [C.c_int]),
+    "sl_densify_plan": (C.c_int, [C.c_int, _F, _F, _F, C.c_int, _F, _F, C.c_float, C.c_float, C.c_float, C.c_float,
+                                  C.c_int, C.c_int, _F, C.c_size_t, _F, C.c_void_p]),
+    "sl_densify_apply": (C.c_int, [C.c_int, C.c_int, C.POINTER(DensifyGroup), C.c_int, C.c_int, C.c_int, _F, _F, _F,
+                                   C.c_void_p]),
     "sl_mark_visible": (C.c_int, [C.c_int, _F, _F, _F, _F, C.c_void_p]),
     "sl_knn_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_knn": (C.c_int, [C.c_int, _F, _F, _F, C.c_size_t, C.c_void_p]),

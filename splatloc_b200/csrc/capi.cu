@@ -8,6 +8,7 @@
 // Everything is enqueued on the caller's stream.
 #include <atomic>
 #include <mutex>
+#include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
@@ -732,6 +733,136 @@ int sl_backward_render(int n_views, int P, int R, const float* background, int w
                          accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic,
                          dL_draw_opacity, dL_dcolor, dL_ddepth, dL_dmean3D, dL_dcov3D, nullptr, dL_draw_scaling,
                          dL_draw_rotation, nullptr, debug, stream_, &raw, raw_opacity, dL_dfeatures_dc, dL_dkp_score);
+}
+
+// ---- optimiser step and densification ---------------------------------------
+int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, float beta1, float beta2, float eps,
+                 const float* marker, float marker_threshold, void* stream_)
+{
+    g_error[0] = 0;
+    if (P < 0 || n_groups < 0 || n_groups > STORE_MAX_GROUPS || step < 1 || (n_groups > 0 && groups == nullptr)) {
+        set_error("sl_adam_step: bad arguments (P=%d, groups=%d of at most %d, step=%d)", P, n_groups, STORE_MAX_GROUPS, step);
+        return SL_ERR_ARGUMENT;
+    }
+    if (P == 0 || n_groups == 0) return 0;
+    AdamArgs a;
+    a.n_groups = 0;
+    // torch.optim.Adam forms these scalars in double and hands them to float32 tensor ops
+    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    for (int k = 0; k < n_groups; ++k) {
+        const sl_adam_group& g = groups[k];
+        if (g.width <= 0) continue;
+        if (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq) {
+            set_error("sl_adam_step: group %d has a NULL pointer", k);
+            return SL_ERR_ARGUMENT;
+        }
+        AdamGroup& o = a.group[a.n_groups++];
+        o.param = g.param; o.grad = g.grad; o.exp_avg = g.exp_avg; o.exp_avg_sq = g.exp_avg_sq;
+        o.width = g.width;
+        o.step_size = (float)((double)g.lr / bc1);
+        o.freeze_by_marker = g.freeze_by_marker;
+    }
+    a.one_minus_beta1 = (float)(1.0 - (double)beta1);
+    a.beta2 = beta2;
+    a.one_minus_beta2 = (float)(1.0 - (double)beta2);
+    a.bias_correction2_sqrt = (float)sqrt(bc2);
+    a.eps = eps;
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int rc = launch_adam(a, P, marker, marker_threshold, stream);
+    if (rc) return rc;
+    return check_stage(false, stream, "adam step");
+}
+
+int sl_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,
+                     float* denom, float* max_radii2D, void* stream_)
+{
+    g_error[0] = 0;
+    if (P < 0 || n_views < 1) { set_error("sl_densify_stats: bad sizes"); return SL_ERR_ARGUMENT; }
+    if (P == 0) return 0;
+    if (!means2D_grad || !radii || !xyz_gradient_accum || !denom || !max_radii2D) {
+        set_error("sl_densify_stats: a required pointer is NULL");
+        return SL_ERR_ARGUMENT;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int rc = launch_densify_stats(P, n_views, means2D_grad, radii, xyz_gradient_accum, denom, max_radii2D, stream);
+    if (rc) return rc;
+    return check_stage(false, stream, "densify stats");
+}
+
+size_t sl_densify_scratch_bytes(int P) { return densify_scratch_bytes(P); }
+
+int sl_densify_plan(int P, const float* xyz_gradient_accum, const float* denom, const float* raw_scaling, int scale_dim,
+                    const float* raw_opacity, const float* marker, float grad_threshold, float percent_dense,
+                    float extent, float min_opacity, int use_size_test, int primitive_reg, char* scratch,
+                    size_t scratch_bytes, uint32_t* totals, void* stream_)
+{
+    g_error[0] = 0;
+    if (P < 0 || (scale_dim != 1 && scale_dim != 3)) { set_error("sl_densify_plan: bad sizes"); return SL_ERR_ARGUMENT; }
+    if (!(grad_threshold > 0.f)) {
+        set_error("sl_densify_plan: grad_threshold must be positive (fresh clones carry a zero gradient and must not split)");
+        return SL_ERR_ARGUMENT;
+    }
+    if (!totals) { set_error("sl_densify_plan: totals is NULL"); return SL_ERR_ARGUMENT; }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    if (P == 0) {
+        SL_CUDA(cudaMemsetAsync(totals, 0, 4 * sizeof(uint32_t), stream), "densify plan memset");
+        return 0;
+    }
+    if (!xyz_gradient_accum || !denom || !raw_scaling || !raw_opacity || !scratch) {
+        set_error("sl_densify_plan: a required pointer is NULL");
+        return SL_ERR_ARGUMENT;
+    }
+    if (scratch_bytes < densify_scratch_bytes(P)) {
+        set_error("sl_densify_plan: scratch of %zu bytes is smaller than the %zu required", scratch_bytes, densify_scratch_bytes(P));
+        return SL_ERR_CAPACITY;
+    }
+    DensifyParams dp;
+    dp.grad_threshold = grad_threshold;
+    dp.dense_extent = percent_dense * extent;
+    dp.extent = extent;
+    dp.min_opacity = min_opacity;
+    dp.use_size_test = use_size_test;
+    dp.primitive_reg = primitive_reg;
+    dp.scale_dim = scale_dim;
+    const int rc = launch_densify_plan(dp, P, xyz_gradient_accum, denom, raw_scaling, raw_opacity, marker, scratch, totals, stream);
+    if (rc) return rc;
+    return check_stage(false, stream, "densify plan");
+}
+
+int sl_densify_apply(int P, int n_groups, const sl_densify_group* groups, int xyz_group, int scaling_group,
+                     int rotation_group, const char* scratch, const uint32_t* totals, const float* noise, void* stream_)
+{
+    g_error[0] = 0;
+    if (P < 0 || n_groups < 1 || n_groups > STORE_MAX_GROUPS || !groups) {
+        set_error("sl_densify_apply: bad arguments");
+        return SL_ERR_ARGUMENT;
+    }
+    if (P == 0) return 0;
+    auto ok = [&](int g, int w) { return g >= 0 && g < n_groups && (w == 0 || groups[g].width == w); };
+    if (!ok(xyz_group, 3) || !ok(rotation_group, 4) || !ok(scaling_group, 0) ||
+        (groups[scaling_group].width != 1 && groups[scaling_group].width != 3) || !scratch || !totals || !noise) {
+        set_error("sl_densify_apply: xyz (3), scaling (1 or 3) and rotation (4) groups, scratch, totals and noise are required");
+        return SL_ERR_ARGUMENT;
+    }
+    DensifyArrays arr;
+    arr.n_groups = n_groups;
+    arr.xyz_group = xyz_group; arr.scaling_group = scaling_group; arr.rotation_group = rotation_group;
+    for (int k = 0; k < n_groups; ++k) {
+        const sl_densify_group& g = groups[k];
+        if (g.width > 0 && (!g.param_in || !g.param_out || ((g.exp_avg_in != nullptr) != (g.exp_avg_out != nullptr)) ||
+                            ((g.exp_avg_in != nullptr) != (g.exp_avg_sq_in != nullptr)) ||
+                            ((g.exp_avg_out != nullptr) != (g.exp_avg_sq_out != nullptr)))) {
+            set_error("sl_densify_apply: group %d has inconsistent pointers", k);
+            return SL_ERR_ARGUMENT;
+        }
+        DensifyGroup& o = arr.group[k];
+        o.param_in = g.param_in; o.param_out = g.param_out; o.exp_avg_in = g.exp_avg_in; o.exp_avg_out = g.exp_avg_out;
+        o.exp_avg_sq_in = g.exp_avg_sq_in; o.exp_avg_sq_out = g.exp_avg_sq_out; o.width = g.width;
+    }
+    cudaStream_t stream = (cudaStream_t)stream_;
+    const int rc = launch_densify_apply(arr, P, groups[scaling_group].width, scratch, totals, noise, stream);
+    if (rc) return rc;
+    return check_stage(false, stream, "densify apply");
 }
 
 int sl_mark_visible(int P, const float* means3D, const float* viewmatrix, const float* projmatrix,

@@ -122,4 +122,57 @@ int launch_mapping_loss(int W, int H, int C, const float* image, const float* de
                         float rgb_threshold, bool initialization, float* dL_dimage, float* dL_ddepth, float* out,
                         char* workspace, cudaStream_t stream);
 
+// ---- optimiser step and densification over the Gaussian store (optimizer.cu;
+// reference: gaussian_splatting/scene/gaussian_model.py:250-300, 493-679).
+constexpr int STORE_MAX_GROUPS = 8;      // xyz, f_dc, f_rest, opacity, marker, kp_score, scaling, rotation
+
+struct AdamGroup {
+    float* param;
+    const float* grad;
+    float* exp_avg;
+    float* exp_avg_sq;
+    int width;               // floats per Gaussian
+    float step_size;         // lr / (1 - beta1^step)
+    int freeze_by_marker;    // zero the gradient of rows whose marker exceeds the threshold (xyz group)
+};
+struct AdamArgs {
+    AdamGroup group[STORE_MAX_GROUPS];
+    int n_groups;
+    float one_minus_beta1, beta2, one_minus_beta2, bias_correction2_sqrt, eps;
+};
+int launch_adam(const AdamArgs& args, int P, const float* marker, float marker_threshold, cudaStream_t stream);
+
+int launch_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,
+                         float* denom, float* max_radii2D, cudaStream_t stream);
+
+struct DensifyParams {
+    float grad_threshold;    // max_grad
+    float dense_extent;      // percent_dense * scene extent
+    float extent;
+    float min_opacity;
+    int use_size_test;       // max_screen_size given
+    int primitive_reg;       // rows with marker > 0.005 are never pruned
+    int scale_dim;
+};
+struct DensifyGroup {
+    const float* param_in;
+    float* param_out;
+    const float* exp_avg_in;     // nullptr: this group carries no optimiser state
+    float* exp_avg_out;
+    const float* exp_avg_sq_in;
+    float* exp_avg_sq_out;
+    int width;
+};
+struct DensifyArrays {
+    DensifyGroup group[STORE_MAX_GROUPS];
+    int n_groups;
+    int xyz_group, scaling_group, rotation_group;
+};
+size_t densify_scratch_bytes(int P);
+int launch_densify_plan(const DensifyParams& dp, int P, const float* xyz_gradient_accum, const float* denom,
+                        const float* raw_scaling, const float* raw_opacity, const float* marker, char* scratch,
+                        uint32_t* totals, cudaStream_t stream);
+int launch_densify_apply(const DensifyArrays& arr, int P, int scale_dim, const char* scratch, const uint32_t* totals,
+                         const float* noise, cudaStream_t stream);
+
 }  // namespace sl
