@@ -20,7 +20,8 @@ metric: `sweep` (fwd+bwd Mpix/s against the number of Gaussians, N = 1 only),
 `pose_refine` (config 3: pose-refine iterations/s, query frames sharded over
 the ranks), `multiview` (config 2 with 4 and 8 cameras per launch) and
 `train_window` (config 4: 1296x968, 3 M Gaussians, 4 views per GPU between
-exchanges).  `--sub none` skips them.
+exchanges) and `mapping_iteration` (render() pre-processing and the optimiser
+step fused into kernels).  `--sub none` skips them.
 
 --impl reference runs the UNMODIFIED reference CUDA rasterizer
 (oracle/_ref/libref_raster_c4.so, compiled from /root/reference for sm_100a)
@@ -472,7 +473,6 @@ def run_train_step(args, impl):
         n0 = lib.sl_launch_count() if impl == "ours" else 0
         ms_total, per_step, wall = job.timed(step_eager, args.steps, args.warmup)
         launches = ((lib.sl_launch_count() - n0) * args.steps // (args.steps + args.warmup)) if impl == "ours" else 0
-    clocks = sampler.stop() if sampler is not None else None
     sync_ms = None
     if graphed is not None:
         e2e_ms, _, _ = job.timed(step_e2e_graph, args.steps, args.warmup, after=exchange.wait)
@@ -483,6 +483,7 @@ def run_train_step(args, impl):
     else:
         e2e_ms, _, _ = job.timed(step_e2e_eager, args.steps, args.warmup)
     e2e_eager_ms, _, _ = job.timed(step_e2e_eager, args.steps, args.warmup) if graphed is not None else (None, None, None)
+    clocks = sampler.stop() if sampler is not None else None      # sampled over the resident and the e2e timed loops
 
     # per-stage device times: same steps again with the library's event timers on (kept apart from
     # the headline loop because reading the events back blocks the host between stages)
@@ -716,7 +717,7 @@ def sub_sweep(job, args, impl, points=(100_000, 200_000, 500_000, 1_200_000, 3_0
                                             cam.campos, fw[5], fw[0], fw[6], fw[7], fw[3], False)
             if i % 4 == 0:
                 stat["R"], stat["V"] = fw[0], fw[4]
-        ms, _, _ = job.timed(eager, steps, 3)
+        ms, _, _ = job.timed(eager, steps, 10)     # (the caching allocator settles on this size's chunks first)
         row = {"gaussians": P, "visible": int((stat["V"] > 0).sum()), "pairs": int(stat["R"]),
                "eager_Mpix_per_s": round(W * H / (ms / steps * 1e-3) / 1e6, 1)}
         if impl == "ours":
@@ -727,6 +728,63 @@ def sub_sweep(job, args, impl, points=(100_000, 200_000, 500_000, 1_200_000, 3_0
         del sc
         torch.cuda.empty_cache()
     return rows
+
+
+def sub_mapping_iteration(job, args, sc):
+    """SURVEY 8(f) rows 1 and 4 on the config-2 scene, one view, eager calls through the drop-in API: the
+    reference's mapping iteration around the rasterizer -- render() with its PyTorch pre-processing,
+    backward, torch.optim.Adam over the eight parameter groups -- against render() with the
+    pre-processing inside the kernels (sl_forward_render / sl_backward_render) and the fused Adam
+    kernel (sl_adam_step).  Both use this library's rasterizer; what differs is the work around it."""
+    import math
+    import types
+    from splatloc_b200.gaussian_optimizer import GaussianStoreOptimizer
+    from splatloc_b200.gaussian_renderer import render
+    dev, P = job.dev, int(sc["means3D"].shape[0])
+    C0 = 0.28209479177387814
+    o = sc["opacities"].clamp(1e-4, 1 - 1e-4)
+    raw = dict(_xyz=sc["means3D"], _features_dc=((sc["colors_precomp"][:, :3] - 0.5) / C0).view(P, 1, 3).contiguous(),
+               _kp_score=sc["colors_precomp"][:, 3:4].contiguous(), _opacity=torch.log(o / (1 - o)),
+               _scaling=torch.log(sc["scales"]), _rotation=sc["rotations"] * 1.7)
+    lrs = dict(xyz=1.6e-4, f_dc=2.5e-3, opacity=0.05, kp_score=0.05, scaling=1e-3, rotation=1e-3)
+    key = dict(xyz="_xyz", f_dc="_features_dc", opacity="_opacity", kp_score="_kp_score", scaling="_scaling", rotation="_rotation")
+    cams = [scenes.make_camera(seed=i).to(dev) for i in range(4)]
+    views = [types.SimpleNamespace(FoVx=2 * math.atan(c.tanfovx), FoVy=2 * math.atan(c.tanfovy), image_height=c.H, image_width=c.W,
+                                   world_view_transform=c.viewmatrix, full_proj_transform=c.projmatrix, camera_center=c.campos)
+             for c in cams]
+    pipe = types.SimpleNamespace(convert_SHs_python=True, compute_cov3D_python=False)
+    bg = torch.zeros(3, device=dev)
+    gt = torch.rand(3, cams[0].H, cams[0].W, device=dev)
+    steps, out = max(8, args.steps // 2), {}
+    for mode in ("reference_shaped", "fused"):
+        pc = types.SimpleNamespace(active_sh_degree=0, max_sh_degree=0, _features_rest=torch.zeros((P, 0, 3), device=dev))
+        for k, t in raw.items():
+            setattr(pc, k, t.clone().requires_grad_(True))
+        params = {n: getattr(pc, k) for n, k in key.items()}
+        if mode == "fused":
+            opt = GaussianStoreOptimizer({n: t for n, t in params.items()}, lrs)
+            for n, k in key.items():            # the optimiser updates these tensors in place
+                setattr(pc, k, opt.params[n].requires_grad_(True))
+            params = {n: getattr(pc, k) for n, k in key.items()}
+        else:
+            topt = torch.optim.Adam([{"params": [t], "lr": lrs[n], "name": n} for n, t in params.items()], lr=0.0, eps=1e-15)
+
+        def it(i):
+            pkg = render(views[i % 4], pc, pipe, bg, fuse=mode == "fused")
+            loss = (pkg["render"] - gt).abs().mean() + pkg["kp_prob"].mean() + 0.1 * pkg["depth"].mean()
+            loss.backward()
+            if mode == "fused":
+                opt.step({n: t.grad for n, t in params.items()})
+                for t in params.values():
+                    t.grad = None
+            else:
+                topt.step()
+                topt.zero_grad(set_to_none=True)
+        ms, _, _ = job.timed(it, steps, 5)
+        out[mode + "_ms_per_iteration"] = round(ms / steps, 4)
+    out["note"] = ("render + loss + backward + Adam, eager; reference_shaped = render()'s PyTorch pre-processing "
+                   "(gaussian_renderer/__init__.py:73-102) and torch.optim.Adam around this library's rasterizer")
+    return out
 
 
 def cpu_baseline(budget_s=20.0):
@@ -872,7 +930,7 @@ def main():
         if job.rank == 0:
             print(json.dumps({name: out[name]}), file=sys.stderr, flush=True)
     note("value")
-    subs = {"sweep", "pose_refine", "multiview", "train_window"} if args.sub == "all" else \
+    subs = {"sweep", "pose_refine", "multiview", "train_window", "mapping_iteration"} if args.sub == "all" else \
         (set() if args.sub == "none" else set(args.sub.split(",")))
     if args.points != P_DEFAULT:
         subs = set()
@@ -881,6 +939,9 @@ def main():
         if "multiview" in subs:
             out["multiview"] = sub_multiview(job, args, state["sc"])
             note("multiview")
+        if "mapping_iteration" in subs:
+            out["mapping_iteration"] = sub_mapping_iteration(job, args, state["sc"])
+            note("mapping_iteration")
         state.clear()
         torch.cuda.empty_cache()
         if "pose_refine" in subs:

@@ -288,7 +288,8 @@ int sl_backward_render(int n_views, int P, int R, const float* background, int w
  * with PyTorch indexing, torch.cat and optimizer-state surgery between two rasterizer calls.
  *
  * sl_adam_step: torch.optim.Adam(l, lr=0.0, eps=1e-15).step() (training_setup, :250-300) for up to 8
- *   parameter groups in one launch; `step` is the 1-based step count (bias correction).  A group with
+ *   parameter groups in one launch; `step` is the 1-based step count (bias correction); beta1, beta2 and
+ *   eps are doubles because PyTorch forms 1 - beta and the bias corrections in double.  A group with
  *   freeze_by_marker != 0 uses a zero gradient for rows whose marker[row] > marker_threshold
  *   (train_gaussians.py:232-234 zeroes the position gradient of key primitives).
  * sl_densify_stats: add_densification_stats (:677-679) and the max_radii2D update
@@ -318,7 +319,7 @@ typedef struct {
     const float* exp_avg_in; float* exp_avg_out; const float* exp_avg_sq_in; float* exp_avg_sq_out;
     int width;
 } sl_densify_group;
-int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, float beta1, float beta2, float eps,
+int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, double beta1, double beta2, double eps,
                  const float* marker, float marker_threshold, void* stream);
 int sl_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,
                      float* denom, float* max_radii2D, void* stream);

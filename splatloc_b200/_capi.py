@@ -147,7 +147,7 @@ SIGNATURES = {
         _F, _F, _F, _F, _F, _F,                      # dL_dmean3D, dL_dfeatures_dc, dL_dkp_score, dL_draw_opacity/scaling/rotation
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
-    "sl_adam_step": (C.c_int, [C.c_int, C.c_int, C.POINTER(AdamGroup), C.c_int, C.c_float, C.c_float, C.c_float,
+    "sl_adam_step": (C.c_int, [C.c_int, C.c_int, C.POINTER(AdamGroup), C.c_int, C.c_double, C.c_double, C.c_double,
                                _F, C.c_float, C.c_void_p]),
     "sl_densify_stats": (C.c_int, [C.c_int, C.c_int, _F, _F, _F, _F, _F, C.c_void_p]),
     "sl_densify_scratch_bytes": (C.c_size_t, [C.c_int]),

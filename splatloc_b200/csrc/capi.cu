@@ -736,7 +736,7 @@ int sl_backward_render(int n_views, int P, int R, const float* background, int w
 }
 
 // ---- optimiser step and densification ---------------------------------------
-int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, float beta1, float beta2, float eps,
+int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, double beta1, double beta2, double eps,
                  const float* marker, float marker_threshold, void* stream_)
 {
     g_error[0] = 0;
@@ -748,7 +748,8 @@ int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, flo
     AdamArgs a;
     a.n_groups = 0;
     // torch.optim.Adam forms these scalars in double and hands them to float32 tensor ops
-    const double bc1 = 1.0 - pow((double)beta1, (double)step), bc2 = 1.0 - pow((double)beta2, (double)step);
+    // (hence beta1, beta2, eps arrive as doubles: 1 - (double)0.999f is off by 1.3e-5 of itself)
+    const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
     for (int k = 0; k < n_groups; ++k) {
         const sl_adam_group& g = groups[k];
         if (g.width <= 0) continue;
@@ -762,11 +763,11 @@ int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, flo
         o.step_size = (float)((double)g.lr / bc1);
         o.freeze_by_marker = g.freeze_by_marker;
     }
-    a.one_minus_beta1 = (float)(1.0 - (double)beta1);
-    a.beta2 = beta2;
-    a.one_minus_beta2 = (float)(1.0 - (double)beta2);
+    a.one_minus_beta1 = (float)(1.0 - beta1);
+    a.beta2 = (float)beta2;
+    a.one_minus_beta2 = (float)(1.0 - beta2);
     a.bias_correction2_sqrt = (float)sqrt(bc2);
-    a.eps = eps;
+    a.eps = (float)eps;
     cudaStream_t stream = (cudaStream_t)stream_;
     const int rc = launch_adam(a, P, marker, marker_threshold, stream);
     if (rc) return rc;

@@ -79,7 +79,11 @@ class GaussianStoreOptimizer:
                 raise RuntimeError(f"gradient of {n} must be a float32 CUDA tensor of shape {tuple(p.shape)}")
             self.steps[n] += 1
             by_step.setdefault(self.steps[n], []).append((n, g.contiguous()))
+        # The reference forms its key-primitive mask BEFORE optimizer.step() (train_gaussians.py:232-234), and
+        # the marker is itself a trained group of the same launch: freeze by a snapshot, not by the live tensor.
         marker = self.params.get("marker") if self.primitive_reg else None
+        if marker is not None:
+            marker = marker.clone()
         with torch.cuda.device(self.dev):
             for step, items in by_step.items():
                 arr = (_capi.AdamGroup * len(items))()

@@ -93,10 +93,12 @@ def _can_fuse(pc, pipe, override_color, mask) -> bool:
             and pc._features_dc.numel() == 3 * pc._xyz.shape[0])
 
 
-def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None, mask=None):
+def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=1.0, override_color=None, mask=None,
+           fuse: bool = True):
     """Render the scene (reference: gaussian_renderer/__init__.py:12-141).  `pc` is a GaussianModel (any
     object with `_xyz`, `_features_dc`, `_features_rest`, `_kp_score`, `_opacity`, `_scaling`, `_rotation`,
-    `active_sh_degree`, `max_sh_degree` and the reference's getters)."""
+    `active_sh_degree`, `max_sh_degree` and the reference's getters).  `fuse=False` (not in the
+    reference) keeps the pre-processing as PyTorch ops even where the kernels could do it."""
     if pc._xyz.shape[0] == 0:
         return None
     xyz = pc._xyz
@@ -109,7 +111,7 @@ def render(viewpoint_camera, pc, pipe, bg_color: torch.Tensor, scaling_modifier=
     tanfovy = math.tan(viewpoint_camera.FoVy * 0.5)
     H, W = int(viewpoint_camera.image_height), int(viewpoint_camera.image_width)
 
-    if _can_fuse(pc, pipe, override_color, mask):
+    if fuse and _can_fuse(pc, pipe, override_color, mask):
         rendered_image, depth, opacity, radii = _FusedRender.apply(
             xyz, screenspace_points, pc._features_dc, pc._kp_score, pc._opacity, pc._scaling, pc._rotation, bg_color,
             float(scaling_modifier), viewpoint_camera.world_view_transform, viewpoint_camera.full_proj_transform,

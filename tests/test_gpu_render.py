@@ -76,8 +76,14 @@ def _check(fw, bw, ufw, u2d, leaves, P):
     pairs = [("abs2D", g_abs2D[0], u2d[0]), ("means2D", g_m2D[0], u2d[1]), ("xyz", g_xyz, leaves[0].grad),
              ("features_dc", g_fdc.view(P, 1, 3), leaves[1].grad), ("kp_score", g_kp, leaves[2].grad),
              ("opacity", g_op, leaves[3].grad), ("scaling", g_sc, leaves[4].grad), ("rotation", g_rot, leaves[5].grad)]
+    # isotropic Gaussians have an analytically zero rotation gradient: both routes return rounding noise
+    # there, so no gradient is compared below 1e-4 of the scaling gradient's magnitude
+    floor = 1e-4 * float(leaves[4].grad.abs().max())
+    if leaves[4].shape[1] == 1:
+        assert float(g_rot.abs().max()) <= floor and float(leaves[5].grad.abs().max()) <= floor, "isotropic: rotation gradient"
+        pairs = pairs[:-1]
     for name, a, b in pairs:
-        scale = max(float(b.abs().max()), 1e-30)
+        scale = max(float(b.abs().max()), floor, 1e-30)
         assert _frac_bad(a, b, 1e-4, 1e-5 * 32 * scale) <= 1e-3, f"{name}: max err {float((a - b).abs().max()):.3e} of {scale:.3e}"
         assert torch.isfinite(a).all(), name
 

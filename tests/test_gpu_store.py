@@ -13,9 +13,15 @@ from tests.test_store_cpu import CASES, KEY, initial_state, load
 pytestmark = pytest.mark.gpu
 
 
-def _close(a, b, rtol=5e-6, atol=1e-8):
+def _close(a, b, rtol=5e-6, atol=None):
+    """rtol on the element, plus an absolute floor of a few float32 ulps of the tensor's largest magnitude
+    (an update of size lr lands on parameters near zero with the rounding of the O(1) operands)."""
     a, b = a.detach().double().cpu(), torch.as_tensor(b).double()
-    return a.shape == b.shape and bool(((a - b).abs() <= atol + rtol * b.abs()).all())
+    if a.shape != b.shape:
+        return False
+    if atol is None:
+        atol = 4e-7 * max(float(b.abs().max()), 1e-30) if b.numel() else 0.0
+    return bool(((a - b).abs() <= atol + rtol * b.abs()).all())
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -39,7 +45,7 @@ def test_store_kernels_reproduce_the_reference_fixtures(name):
     assert new_P == g["out_xyz"].shape[0], (new_P, opt.last_densify)
     assert 2 * opt.last_densify["split"] == g["noise"].shape[0]
     for n in S.GROUPS:
-        assert _close(opt.params[n], g["out" + KEY[n]], rtol=5e-6, atol=2e-7), f"densify {n}"
+        assert _close(opt.params[n], g["out" + KEY[n]]), f"densify {n}"
         if opt.params[n].numel():
             assert _close(opt.exp_avg[n], g["out_m" + KEY[n]]) and _close(opt.exp_avg_sq[n], g["out_v" + KEY[n]]), n
     assert not bool(opt.xyz_gradient_accum.any()) and opt.max_radii2D.shape == (new_P,)
@@ -86,7 +92,7 @@ def test_store_kernels_match_oracle_on_a_200k_store(isotropic, max_screen, preg)
             opt.last_densify["split"]) == counts
     assert new_P == out["xyz"].shape[0] and counts[1] > 1000 and counts[2] > 1000
     for n in cpu:
-        assert _close(opt.params[n], out[n], rtol=5e-6, atol=2e-7), f"densify {n}"
+        assert _close(opt.params[n], out[n]), f"densify {n}"
         if out[n].numel():
             assert _close(opt.exp_avg[n], m2[n]) and _close(opt.exp_avg_sq[n], v2[n]), f"moments {n}"
 
