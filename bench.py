@@ -188,6 +188,7 @@ class Job:
         if self.world > 1:
             import datetime
             import torch.distributed as dist
+            os.environ.setdefault("NCCL_DEBUG", "WARN")      # (keeps NCCL's version banner off stdout: one JSON line)
             dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=300))
             self.dist = dist
         self.flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=self.dev)

@@ -28,7 +28,10 @@ def test_oracle_reproduces_the_reference_preprocessing(name):
     raw = raw_tensors(g, requires_grad=True)
     act = render_oracle.preprocess(*raw)
     for t, k in zip(act, ("means3D", "colors_precomp", "opacities", "scales", "rotations")):
-        assert np.array_equal(t.detach().numpy(), g["act_" + k]), k                 # same ops, same bits
+        if k in ("means3D", "colors_precomp"):        # copies, exactly rounded multiplies and adds: same bits anywhere
+            assert np.array_equal(t.detach().numpy(), g["act_" + k]), k
+        else:                                          # exp / sigmoid / normalize: the host's vector maths library may differ by an ulp
+            assert np.allclose(t.detach().numpy(), g["act_" + k], rtol=5e-7, atol=0), k
     grads = [torch.from_numpy(g["gact_" + k]) for k in ("means3D", "colors_precomp", "opacities", "scales", "rotations")]
     torch.autograd.backward(list(act), grads)
     for t, k in zip(raw, ("_xyz", "_features_dc", "_kp_score", "_opacity", "_scaling", "_rotation")):

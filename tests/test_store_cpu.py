@@ -27,9 +27,15 @@ def initial_state(g, device="cpu"):
     return params, m, v, lrs
 
 
-def close(a, b, rtol=2e-6, atol=1e-9):
+def close(a, b, rtol=2e-6, atol=None):
+    """rtol on the element plus a floor of a few float32 ulps of the tensor's largest magnitude (an update of
+    size lr lands on parameters near zero with the rounding of O(1) operands; hosts differ by an ulp there)."""
     a, b = np.asarray(a, dtype=np.float64), np.asarray(b, dtype=np.float64)
-    return a.shape == b.shape and bool(np.all(np.abs(a - b) <= atol + rtol * np.abs(b)))
+    if a.shape != b.shape:
+        return False
+    if atol is None:
+        atol = 4e-7 * float(np.abs(b).max()) if b.size else 0.0
+    return bool(np.all(np.abs(a - b) <= atol + rtol * np.abs(b)))
 
 
 @pytest.mark.parametrize("name", CASES)
@@ -55,7 +61,7 @@ def test_oracle_reproduces_the_reference_store_updates(name):
     assert counts[0] + counts[1] + 2 * counts[2] == g["out_xyz"].shape[0]
     assert counts[1] > 0 and counts[2] > 0 and counts[0] < P, counts           # every branch exercised
     for n in S.GROUPS:
-        assert close(out[n].numpy(), g["out" + KEY[n]], rtol=2e-6, atol=1e-7), f"densify {n}"
+        assert close(out[n].numpy(), g["out" + KEY[n]]), f"densify {n}"
         if out[n].numel():
             assert close(m2[n].numpy(), g["out_m" + KEY[n]]) and close(v2[n].numpy(), g["out_v" + KEY[n]]), f"densify moments {n}"
     assert not g["out_accum"].any() and not g["out_denom"].any() and not g["out_max_radii2D"].any()
