@@ -495,8 +495,14 @@ def run_train_step(args, impl):
         prof = _capi.profile_read()
         lib.sl_profile_enable(0)
 
-    R, radii = step_eager(0, reduce=False)
-    V = int((radii > 0).sum())
+    # visible Gaussians and pairs of each of the cycled views; the byte counts below use their means,
+    # like the times they are divided by (steps cycle through the N_CAMERAS views)
+    per_cam = []
+    for i in range(N_CAMERAS):
+        Ri, radii = step_eager(i, reduce=False)
+        per_cam.append((int((radii > 0).sum()), int(Ri)))
+    V = round(sum(v for v, _ in per_cam) / N_CAMERAS)
+    R = round(sum(r for _, r in per_cam) / N_CAMERAS)
     torch.cuda.synchronize()
     ms_step = ms_total / args.steps
     mpix = lambda ms_sum: round(N * n_ranks / (ms_sum / args.steps * 1e-3) / 1e6, 3)   # noqa: E731
@@ -515,7 +521,7 @@ def run_train_step(args, impl):
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "impl": impl,
         "config": {"workload": WORKLOAD, "gaussians": P, "channels": C, "image": [W, H], "views_per_gpu_per_step": 1,
-                   "visible": V, "pairs": R,
+                   "visible": V, "pairs": R, "visible_pairs_per_view": per_cam,
                    "submission": "one CUDA-graph replay per step (splatloc_b200.graphs)" if graphed is not None else "eager calls",
                    "l2": f"flushed between timed steps ({L2_FLUSH_BYTES >> 20} MiB memset, untimed)",
                    "parallelism": parallelism},
