@@ -401,6 +401,15 @@ long long sl_launch_count(void);
  *       1 when a tile's list is longer than the 16384 pairs one CTA sorts. */
 void sl_set_binning_mode(int mode);
 
+/* How the forward blend kernel brings a tile's pair records on chip (no reference counterpart; the
+ * reference gathers per-Gaussian data into shared memory per 256-entry batch, forward.cu:899-908).
+ * PROCESS-WIDE, like the binning mode; both give identical results:
+ *   0 = default: every lane loads the record of one list entry that survives the per-patch reach mask
+ *       (three 16-byte loads), survivors are parked in a warp-private shared buffer;
+ *   1 = the copy engine stages whole 32-record chunks (cp.async.bulk, completion on an mbarrier, two
+ *       stages per warp).  Kept for the A/B in profiles/README.md; measured slower on the B200. */
+void sl_set_record_stream(int mode);
+
 /* Per-stage device timing with CUDA events recorded on the caller's stream
  * around each stage of sl_forward / sl_backward.  sl_profile_enable(1) resets
  * and starts accumulation, sl_profile_enable(0) stops it.  sl_profile_read

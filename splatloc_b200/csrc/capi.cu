@@ -69,6 +69,7 @@ static Profiler g_prof;
 static std::atomic<long long> g_launches{0};
 static std::atomic<int> g_binning_mode{0};  // sl_set_binning_mode(): 0 default, 1 radix sort, 2 tile buckets
 constexpr int kDefaultBinningMode = 2;
+static std::atomic<int> g_record_stream{0};  // sl_set_record_stream(): 0 per-lane loads of survivors, 1 bulk-copy staging
 
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
@@ -190,6 +191,8 @@ void sl_set_binning_mode(int mode)
 {
     g_binning_mode.store(mode >= 1 && mode <= 2 ? mode : 0, std::memory_order_relaxed);
 }
+
+void sl_set_record_stream(int mode) { g_record_stream.store(mode == 1 ? 1 : 0, std::memory_order_relaxed); }
 
 int sl_profile_stage_count(void) { return ST_COUNT; }
 
@@ -428,7 +431,8 @@ static int forward_impl(sl_alloc_fn geometry_alloc, void* geometry_ctx,
     {
         StageTimer t(ST_BLEND_FWD, stream);
         rc = launch_blend_forward(P, C, vp, img.ranges, img.tile_order, bin.records, bin.masks, background, out_color,
-                                  out_depth, out_alpha, img.n_contrib, n_touched, stream);
+                                  out_depth, out_alpha, img.n_contrib, n_touched,
+                                  g_record_stream.load(std::memory_order_relaxed), stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "blend forward");

@@ -80,7 +80,7 @@ int launch_build_records(int R, int P, int C, const uint64_t* sorted_keys, const
 int launch_blend_forward(int P, int C, const ViewParams& vp, const uint2* ranges, const uint32_t* tile_order,
                          const PairRecord* records, const uint8_t* masks, const float* bg, float* out_color,
                          float* out_depth, float* out_alpha, uint32_t* n_contrib, int* n_touched,
-                         cudaStream_t stream);
+                         int record_stream, cudaStream_t stream);
 
 // K7: backward blending (reference: BACKWARD::render, backward.cu:1018-1209).
 // Per view: dL_dmean2D / dL_dabsmean2D [views, P, 3], dL_dconic [views, P, 4], dL_ddepth [views, P],

@@ -118,6 +118,24 @@ def test_baseline_configs_match_reference_cuda(name, case):
     assert not bad, f"{name}: R={b['R']}\n" + "\n".join(bad)
 
 
+@pytest.mark.parametrize("case", [CASES[2], CASES[4], CASES[8], dict(P=200000, seed=1)],
+                         ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items() if k != "bg"))
+def test_bulk_copy_record_stream_gives_the_same_frame(case):
+    """sl_set_record_stream(1): the forward blend stages whole record chunks with cp.async.bulk instead of
+    per-lane loads of the survivors (kept for the A/B in profiles/); every output must be identical."""
+    from splatloc_b200 import _capi
+    ours = _ours()
+    d = H.scene_inputs(**case)
+    a = H.run_backend(ours, d, backward=False)
+    _capi.load().sl_set_record_stream(1)
+    try:
+        b = H.run_backend(ours, d, backward=False)
+    finally:
+        _capi.load().sl_set_record_stream(0)
+    for k in ("color", "depth", "alpha", "n_contrib", "radii"):
+        assert torch.equal(a[k], b[k]), k
+
+
 def test_empty_and_invisible():
     ours = _ours()
     # P == 0 -> zero outputs, R == 0
