@@ -238,6 +238,31 @@ int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
                       float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                       int debug, void* stream);
 
+/* sl_backward_batch_push = sl_backward_batch + the multi-GPU gradient exchange of a multi-view training
+ * step fused into its last kernel (no reference counterpart: the reference has no distributed code;
+ * SURVEY.md 8(e) "phase 2").  `exchange_multicast` is a MULTICAST device address (NVSwitch / NVLS; e.g.
+ * torch.distributed._symmetric_memory's `multicast_ptr`) of an exchange buffer of [P, 16] floats that
+ * exists on every GPU of the job: every Gaussian this call saw adds its row
+ *     {dL_dmean3D xyz, dL_dopacity | dL_dscale xyz, 1 | dL_drot wxyz | dL_dcolor c0..c3}
+ * into ALL GPUs' buffers with multimem.red from the epilogue of the per-Gaussian backward, so after a
+ * cross-GPU barrier every buffer holds the sum over all GPUs' views (float 7 of a row: in how many
+ * views the Gaussian was visible).  The caller zeroes the buffers and places the barriers
+ * (splatloc_b200/exchange.py).  NULL: plain sl_backward_batch.  Needs colors_precomp and
+ * scales / rotations (no SH, no precomputed covariance). */
+int sl_backward_batch_push(int n_views, int P, int D, int M, int R, int C,
+                           const float* background, int width, int height,
+                           const float* means3D, const float* shs, const float* colors_precomp,
+                           const float* scales, float scale_modifier, const float* rotations,
+                           const float* cov3D_precomp, const float* viewmatrices, const float* projmatrices,
+                           const float* cam_positions, float tan_fovx, float tan_fovy, const int* radii,
+                           char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                           const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                           const float* dL_dpix_alpha,
+                           float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                           float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                           float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                           float* exchange_multicast, int debug, void* stream);
+
 /* ---- render() with its pre-processing inside ----------------------------
  * SplatLoc's render() (gaussian_splatting/gaussian_renderer/__init__.py:12-141) turns the optimiser's
  * raw parameters into rasterizer inputs with PyTorch ops on every call -- opacity = sigmoid(_opacity),

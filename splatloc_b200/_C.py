@@ -342,14 +342,16 @@ def rasterize_gaussians_backward_batch(background, means3D, radii, colors, scale
                                        cov3D_precomp, viewmatrices, projmatrices, tan_fovx, tan_fovy,
                                        dL_dout_color, dL_dout_depth, dL_dout_alpha, sh, degree, campos,
                                        geomBuffer, R, binningBuffer, imageBuffer, out_alpha, debug,
-                                       want_pose=False, pose_only=False):
+                                       want_pose=False, pose_only=False, exchange_multicast: int | None = None):
     """Backward of `rasterize_gaussians_batch` (sl_backward_batch).  Upstream gradients are (V, C, H, W),
     (V, 1, H, W), (V, 1, H, W).
     -> (dL_dabsmeans2D (V, P, 3), dL_dmeans2D (V, P, 3), dL_dcolors, dL_dopacity (P, 1), dL_dmeans3D (P, 3),
         dL_dcov3D (P, 6), dL_dsh (P, M, 3), dL_dscales (P, 3), dL_drotations (P, 4)) [+ dL_dtau (V, 6)]
     The per-Gaussian gradients are summed over the views; dL_dcolors is (P, C) (summed) with precomputed
     colours and (V, P, 3) with SH.  `pose_only`: only dL_dtau is computed (a fixed map); the per-Gaussian
-    gradients come back as None."""
+    gradients come back as None.  `exchange_multicast`: multicast address of a multi-GPU exchange buffer
+    (splatloc_b200.exchange): the summed gradients are also pushed into every GPU's buffer from the last
+    kernel (sl_backward_batch_push)."""
     lib = _capi.load()
     dev = means3D.device
     P = int(means3D.shape[0])
@@ -390,7 +392,8 @@ def rasterize_gaussians_backward_batch(background, means3D, radii, colors, scale
         g_color = g_color_view if with_sh else g_color_sum
         g_tau = torch.zeros((V, 6), dtype=torch.float32, device=dev) if want_pose else None
         if P != 0:
-            rc = lib.sl_backward_batch(
+            push = () if exchange_multicast is None else (int(exchange_multicast),)
+            rc = (lib.sl_backward_batch if exchange_multicast is None else lib.sl_backward_batch_push)(
                 V, P, int(degree), M, int(R), n_ch, _ptr(background), W, H,
                 _ptr(means3D), _ptr(sh), _ptr(colors), _ptr(scales), float(scale_modifier), _ptr(rotations),
                 _ptr(cov3D_precomp), _ptr(viewmatrices), _ptr(projmatrices), _ptr(campos),
@@ -399,7 +402,7 @@ def rasterize_gaussians_backward_batch(background, means3D, radii, colors, scale
                 _ptr(out_alpha), _ptr(dL_dout_color), _ptr(dL_dout_depth), _ptr(dL_dout_alpha),
                 g_mean2D.data_ptr(), g_abs2D.data_ptr(), g_conic.data_ptr(), g_opac.data_ptr(),
                 g_color.data_ptr(), g_depth.data_ptr(), _ptr(g_mean3D), _ptr(g_cov3D),
-                _ptr(g_sh), _ptr(g_scale), _ptr(g_rot), _ptr(g_tau),
+                _ptr(g_sh), _ptr(g_scale), _ptr(g_rot), _ptr(g_tau), *push,
                 int(bool(debug)), _stream(dev))
             _capi.check(rc)
     colors_out = g_color.view(V, P, 3) if with_sh else g_color.view(P, n_ch)

@@ -126,6 +126,20 @@ SIGNATURES = {
         _F, _F, _F, _F,                              # dL_dsh, dL_dscale, dL_drot, dL_dtau
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
+    "sl_backward_batch_push": (C.c_int, [
+        C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # n_views, P, D, M, R, C
+        _F, C.c_int, C.c_int,                        # background, width, height
+        _F, _F, _F,                                  # means3D, shs, colors_precomp
+        _F, C.c_float, _F,                           # scales, scale_modifier, rotations
+        _F, _F, _F,                                  # cov3D_precomp, viewmatrices, projmatrices
+        _F, C.c_float, C.c_float, _F,                # cam_positions, tan_fovx, tan_fovy, radii
+        _F, _F, _F,                                  # geometry, binning, image chunks
+        _F, _F, _F, _F,                              # accum_alphas, dL_dpix, dL_dpix_depth, dL_dpix_alpha
+        _F, _F, _F, _F,                              # dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity
+        _F, _F, _F, _F,                              # dL_dcolor, dL_ddepth, dL_dmean3D, dL_dcov3D
+        _F, _F, _F, _F,                              # dL_dsh, dL_dscale, dL_drot, dL_dtau
+        _F, C.c_int, C.c_void_p,                     # exchange_multicast, debug, stream
+    ]),
     "sl_forward_render": (C.c_int, [
         ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p, ALLOC_FN, C.c_void_p,
         C.c_int, C.c_int, _F, C.c_int, C.c_int,      # n_views, P, background, width, height

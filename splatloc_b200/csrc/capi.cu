@@ -567,7 +567,7 @@ static int backward_impl(int n_views, int P, int D, int M, int R, int C,
                       float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
                       float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                       int debug, void* stream_, const RawParams* raw, const float* raw_opacities,
-                      float* dL_dfdc, float* dL_dkp)
+                      float* dL_dfdc, float* dL_dkp, float* push_mc = nullptr)
 {
     g_error[0] = 0;
     cudaStream_t stream = (cudaStream_t)stream_;
@@ -632,7 +632,7 @@ static int backward_impl(int n_views, int P, int D, int M, int R, int C,
                                         dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D,
                                         pose_only ? nullptr : dL_dsh, dL_dscale, dL_drot, dL_dtau,
                                         pose_only ? nullptr : raw, raw_opacities, colors_precomp, dL_dopacity, dL_dfdc,
-                                        dL_dkp, stream);
+                                        dL_dkp, pose_only ? nullptr : push_mc, stream);
     }
     if (rc) return rc;
     SL_STAGE(dbg, stream, "preprocess backward");
@@ -659,6 +659,34 @@ int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
                          dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
                          dL_ddepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, debug, stream_, nullptr,
                          nullptr, nullptr, nullptr);
+}
+
+int sl_backward_batch_push(int n_views, int P, int D, int M, int R, int C,
+                           const float* background, int width, int height,
+                           const float* means3D, const float* shs, const float* colors_precomp,
+                           const float* scales, float scale_modifier, const float* rotations,
+                           const float* cov3D_precomp, const float* viewmatrices, const float* projmatrices,
+                           const float* cam_positions, float tan_fovx, float tan_fovy, const int* radii,
+                           char* geometry_chunk, char* binning_chunk, char* image_chunk,
+                           const float* accum_alphas, const float* dL_dpix, const float* dL_dpix_depth,
+                           const float* dL_dpix_alpha,
+                           float* dL_dmean2D, float* dL_dabsmean2D, float* dL_dconic, float* dL_dopacity,
+                           float* dL_dcolor, float* dL_ddepth, float* dL_dmean3D, float* dL_dcov3D,
+                           float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
+                           float* exchange_multicast, int debug, void* stream_)
+{
+    if (exchange_multicast != nullptr && (shs != nullptr || scales == nullptr || colors_precomp == nullptr)) {
+        g_error[0] = 0;
+        set_error("sl_backward_batch_push: the exchange rows hold colours_precomp / scale / rotation gradients "
+                  "(no SH, no precomputed covariance)");
+        return SL_ERR_ARGUMENT;
+    }
+    return backward_impl(n_views, P, D, M, R, C, background, width, height, means3D, shs, colors_precomp, scales,
+                         scale_modifier, rotations, cov3D_precomp, viewmatrices, projmatrices, cam_positions, tan_fovx,
+                         tan_fovy, radii, geometry_chunk, binning_chunk, image_chunk, accum_alphas, dL_dpix,
+                         dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
+                         dL_ddepth, dL_dmean3D, dL_dcov3D, dL_dsh, dL_dscale, dL_drot, dL_dtau, debug, stream_, nullptr,
+                         nullptr, nullptr, nullptr, exchange_multicast);
 }
 
 // ---- render() with its pre-processing inside --------------------------------

@@ -167,6 +167,18 @@ __device__ __forceinline__ float4 act_normalize(float4 q)
     return make_float4(q.x / d, q.y / d, q.z / d, q.w / d);
 }
 
+// ---- multi-GPU gradient exchange fused into the per-Gaussian backward (csrc/preprocess_bwd.cu) ----
+// One row of EXCHANGE_ROW floats per Gaussian: {dL/dmean xyz, dL/dopacity | dL/dscale xyz, seen |
+// dL/drot wxyz | dL/dcolour c0..c3}; "seen" counts the views (over all GPUs) in which the Gaussian was
+// visible.  `mc` is a MULTICAST address (NVSwitch, NVLS) that maps the same row of every GPU's exchange
+// buffer: one multimem.red adds the four floats into all of them inside the switch.
+constexpr int EXCHANGE_ROW = 16;
+__device__ __forceinline__ void multimem_red_add_v4(float* mc, float a, float b, float c, float d)
+{
+    asm volatile("multimem.red.relaxed.sys.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                 ::"l"(mc), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
 __host__ __device__ __forceinline__ size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
 static inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

@@ -96,6 +96,8 @@ int launch_blend_backward(int P, int C, const ViewParams& vp, const uint2* range
 // parameters, `dL_dcolor` arrives as the gradient of the activated colour (P, C) and every gradient is
 // taken through its activation: dL_dscale, dL_drot, dL_dopacity (in place) become gradients of the raw
 // parameters, dL_dfdc (P, 3) receives the gradient of f_dc and dL_dkp (P) the 4th colour channel's.
+// `push_mc` != nullptr: multicast address of the [P, EXCHANGE_ROW] exchange rows (common.cuh); the summed
+// gradients of every Gaussian this call saw are added into all GPUs' buffers from the kernel's epilogue.
 // K8+K9 fused: per-Gaussian backward (reference: BACKWARD::preprocess, backward.cu:1810-1876).  One
 // thread carries a Gaussian through all views and stores each gradient once (the sum over the views).
 // dL_dmean3D == nullptr: only the camera-pose gradients dL_dtau [views, 6] are wanted.
@@ -107,7 +109,7 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
                                const float* dL_dcolor, size_t color_view_stride, const float* dL_ddepth,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                                const RawParams* raw, const float* raw_opacities, const float* features_dc,
-                               float* dL_dopacity, float* dL_dfdc, float* dL_dkp, cudaStream_t stream);
+                               float* dL_dopacity, float* dL_dfdc, float* dL_dkp, float* push_mc, cudaStream_t stream);
 
 // K11-K15: mean squared distance to the 3 nearest neighbours (reference: SimpleKNN::knn,
 // simple_knn.cu:186-221).  `scratch` must hold knn_scratch_bytes(P) bytes.

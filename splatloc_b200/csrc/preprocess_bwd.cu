@@ -293,7 +293,8 @@ preprocess_backward_kernel(int P, int D, int M, int C,
                            float* __restrict__ dL_dcov, float* __restrict__ dL_dsh, float* __restrict__ dL_dscale,
                            float* __restrict__ dL_drot, float* dL_dtau,
                            int scale_dim, const float* __restrict__ raw_opacities, const float* __restrict__ features_dc,
-                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dfdc, float* __restrict__ dL_dkp)
+                           float* __restrict__ dL_dopacity, float* __restrict__ dL_dfdc, float* __restrict__ dL_dkp,
+                           float* push_mc)
 {
     __shared__ float s_pose[8][6];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -333,7 +334,9 @@ preprocess_backward_kernel(int P, int D, int M, int C,
             __syncthreads();
         }
     }
-    if (!seen || dL_dmeans == nullptr) return;   // dL_dmeans == nullptr: only the pose gradients were wanted
+    if (dL_dmeans == nullptr) return;            // only the pose gradients were wanted
+    if (push_mc == nullptr && !seen) return;     // (with the exchange every lane stays for the staged push)
+    if (seen) {
     dL_dmeans[3 * idx + 0] = g_mean.x;
     dL_dmeans[3 * idx + 1] = g_mean.y;
     dL_dmeans[3 * idx + 2] = g_mean.z;
@@ -384,6 +387,52 @@ preprocess_backward_kernel(int P, int D, int M, int C,
         }
         if (C == 4 && dL_dkp != nullptr) dL_dkp[idx] = dL_dcolor[idx * C + 3];
     }
+    }   // seen
+    // Multi-GPU training step: instead of a separate all-reduce of the gradient block afterwards, the
+    // finished gradients of every Gaussian some view of THIS GPU saw go straight into every GPU's
+    // exchange buffer through the switch (common.cuh).  Rows no GPU saw are never touched: the traffic
+    // is the visible fraction of the block, and it leaves while the rest of the kernel is still
+    // computing.  The rows are staged through shared memory so that one warp instruction adds whole
+    // 64-byte rows (lanes 4j .. 4j+3: the four quarters of one row; 16-byte accesses scattered over
+    // 32 rows per instruction measured 4x slower on the link).
+    if (push_mc != nullptr && scales != nullptr) {
+        extern __shared__ __align__(16) float s_rows[];           // [256][EXCHANGE_ROW] + [256] flags
+        float* mine = s_rows + (size_t)threadIdx.x * EXCHANGE_ROW;
+        uint32_t* s_seen = reinterpret_cast<uint32_t*>(s_rows + 256 * EXCHANGE_ROW);
+        s_seen[threadIdx.x] = seen ? 1u : 0u;
+        if (seen) {
+            const float4 rq = reinterpret_cast<const float4*>(dL_drot)[idx];
+            float sx, sy = 0.f, sz = 0.f;
+            if (RAW && scale_dim == 1) {
+                sx = dL_dscale[idx];
+            } else {
+                sx = dL_dscale[3 * idx]; sy = dL_dscale[3 * idx + 1]; sz = dL_dscale[3 * idx + 2];
+            }
+            float c0, c1, c2, c3 = 0.f;
+            if (RAW) {
+                c0 = dL_dfdc[3 * idx]; c1 = dL_dfdc[3 * idx + 1]; c2 = dL_dfdc[3 * idx + 2];
+                if (C == 4 && dL_dkp != nullptr) c3 = dL_dkp[idx];
+            } else {
+                c0 = dL_dcolor[idx * C]; c1 = dL_dcolor[idx * C + 1]; c2 = dL_dcolor[idx * C + 2];
+                if (C == 4) c3 = dL_dcolor[idx * C + 3];
+            }
+            reinterpret_cast<float4*>(mine)[0] = make_float4(g_mean.x, g_mean.y, g_mean.z, dL_dopacity[idx]);
+            reinterpret_cast<float4*>(mine)[1] = make_float4(sx, sy, sz, 1.0f);
+            reinterpret_cast<float4*>(mine)[2] = rq;
+            reinterpret_cast<float4*>(mine)[3] = make_float4(c0, c1, c2, c3);
+        }
+        __syncwarp();
+        const int warp_row0 = threadIdx.x & ~31;                   // first row of this warp in the stage
+        const size_t gauss0 = (size_t)blockIdx.x * blockDim.x + warp_row0;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int r = 8 * k + (lane >> 2), q = lane & 3;       // row within the warp, quarter of the row
+            if (s_seen[warp_row0 + r]) {
+                const float4 v = reinterpret_cast<const float4*>(s_rows + (size_t)(warp_row0 + r) * EXCHANGE_ROW)[q];
+                multimem_red_add_v4(push_mc + (gauss0 + r) * EXCHANGE_ROW + 4 * q, v.x, v.y, v.z, v.w);
+            }
+        }
+    }
 }
 
 int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D, const int* radii,
@@ -394,14 +443,16 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
                                const float* dL_dcolor, size_t color_view_stride, const float* dL_ddepth,
                                float* dL_dcov3D, float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                                const RawParams* raw, const float* raw_opacities, const float* features_dc,
-                               float* dL_dopacity, float* dL_dfdc, float* dL_dkp, cudaStream_t stream)
+                               float* dL_dopacity, float* dL_dfdc, float* dL_dkp, float* push_mc, cudaStream_t stream)
 {
     const int scale_dim = raw != nullptr ? raw->scale_dim : 3;
+    const size_t smem = push_mc != nullptr ? (size_t)256 * (EXCHANGE_ROW + 1) * sizeof(float) : 0;
 #define SL_LAUNCH_PBWD(MM, RR)                                                                                   \
-    preprocess_backward_kernel<MM, RR><<<ceil_div(P, 256), 256, 0, stream>>>(                                    \
+    preprocess_backward_kernel<MM, RR><<<ceil_div(P, 256), 256, smem, stream>>>(                                 \
         P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrices, projmatrices,         \
         cam_positions, vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D, \
-        dL_dsh, dL_dscale, dL_drot, dL_dtau, scale_dim, raw_opacities, features_dc, dL_dopacity, dL_dfdc, dL_dkp)
+        dL_dsh, dL_dscale, dL_drot, dL_dtau, scale_dim, raw_opacities, features_dc, dL_dopacity, dL_dfdc, dL_dkp, \
+        push_mc)
     if (raw != nullptr) {
         if (vp.views > 1) SL_LAUNCH_PBWD(true, true); else SL_LAUNCH_PBWD(false, true);
     } else {

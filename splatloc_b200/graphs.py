@@ -36,15 +36,18 @@ _EMPTY = torch.Tensor([])
 class GraphedViewStep:
     def __init__(self, params: dict, H: int, W: int, tanfovx: float, tanfovy: float, bg: torch.Tensor,
                  max_pairs: int, sh_degree: int = 0, scale_modifier: float = 1.0, host_images: torch.Tensor | None = None,
-                 warmup: int = 3, n_views: int = 1):
+                 warmup: int = 3, n_views: int = 1, exchange_multicast: int | None = None):
         """`params`: tensors `means3D`, `opacities`, `scales`, `rotations` and `colors_precomp` (P, C) or
         `shs` (P, M, 3); after every replay their `.grad` is this step's gradient (a view of the step's
         own packed block, `self.grad_block` -- overwritten by the next replay, not accumulated).
         `max_pairs`: (tile, Gaussian) pair capacity of one replay, all views together.
         `host_images`: optional pinned tensor of V * (C + 2) * H * W floats (for V = 1: (C + 2, H, W));
         the images are copied into it inside the graph, overlapped with the backward, laid out
-        [colour of all views | depth | alpha], and are complete when the replay is."""
+        [colour of all views | depth | alpha], and are complete when the replay is.
+        `exchange_multicast`: multicast address of a multi-GPU exchange buffer (splatloc_b200.exchange);
+        every replay then adds this step's summed gradients into all GPUs' buffers from its last kernel."""
         self.params = params
+        self.exchange_multicast = exchange_multicast
         dev = params["means3D"].device
         self.H, self.W, self.V = int(H), int(W), int(n_views)
         self.max_pairs = int(max_pairs)
@@ -110,7 +113,8 @@ class GraphedViewStep:
         bw = _C.rasterize_gaussians_backward_batch(
             self.bg, means3D, radii, colors, scales, rot, self.scale_modifier, _EMPTY, self.viewmatrices,
             self.projmatrices, self.tanfovx, self.tanfovy, self.upstream_color, self.upstream_depth, self.upstream_alpha,
-            shs, self.sh_degree, self.cam_positions, geom, R, binning, img, alpha, False)
+            shs, self.sh_degree, self.cam_positions, geom, R, binning, img, alpha, False,
+            exchange_multicast=self.exchange_multicast)
         if self.host_images is not None:
             torch.cuda.current_stream().wait_stream(self._side)
         self._fw, self._bw = fw, bw

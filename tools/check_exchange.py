@@ -1,0 +1,104 @@
+"""GPU box, under torchrun (N >= 2): the gradient exchange fused into the backward (splatloc_b200.exchange,
+sl_backward_batch_push) against an NCCL all-reduce of the same gradients, then its cost per step.
+
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29503 tools/check_exchange.py
+"""
+import datetime
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import torch.distributed as dist
+
+from splatloc_b200 import scenes
+from splatloc_b200.exchange import NvlsGradientExchange
+from splatloc_b200.graphs import GraphedViewStep
+
+
+def main():
+    rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    os.environ.setdefault("NCCL_DEBUG", "WARN")
+    dist.init_process_group("nccl", device_id=dev, timeout=datetime.timedelta(seconds=120))
+    P, C = int(os.environ.get("CHECK_P", 500_000)), 4
+    sc = {k: v.to(dev) for k, v in scenes.make_scene(P, seed=0, channels=C).items()}
+    params = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "colors_precomp", "scales", "rotations")}
+    bg = torch.zeros(C, device=dev)
+    cams = [scenes.make_camera(seed=100 * rank + i).to(dev) for i in range(4)]
+    H, W = cams[0].H, cams[0].W
+    ups = [torch.cat(scenes.make_pixel_grads(100 * rank + i, C, H, W, normalised=False), 0).to(dev) for i in range(4)]
+    xch = NvlsGradientExchange(P, dev)
+    steps = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000,
+                             exchange_multicast=xch.multicast_ptr(b)) for b in (0, 1)]
+    plain = GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000)
+    xch.zero(0); xch.zero(1)
+    torch.cuda.synchronize(); dist.barrier()
+    worst = 0.0
+    for i in range(4):
+        b = i % 2
+        for st in (steps[b], plain):
+            st.set_camera(cams[i].viewmatrix, cams[i].projmatrix, cams[i].campos)
+            st.upstream.copy_(ups[i])
+        xch.zero(1 - b)
+        steps[b].replay()
+        xch.barrier()
+        plain.replay()
+        ref = plain.trainable_grads().clone()
+        seen = (plain.radii > 0).float()
+        dist.all_reduce(ref)
+        dist.all_reduce(seen)
+        got = NvlsGradientExchange.unpack(xch.rows(b))
+        off = 0
+        for name, w in (("means3D", 3), ("opacities", 1), ("scales", 3), ("rotations", 4), ("colors_precomp", C)):
+            n = (P * w + 3) // 4 * 4
+            want = ref[off:off + P * w].view(P, w)
+            off += n
+            err = float((got[name] - want).abs().max()); scale = float(want.abs().max())
+            worst = max(worst, err / max(scale, 1e-30))
+            assert err <= 2e-5 * 16 * scale, (name, err, scale)
+        assert torch.equal(got["seen"], seen), "visibility counts"
+        assert int(steps[b].overflow) == 0
+    if rank == 0:
+        print(f"{world} ranks: fused exchange == NCCL all-reduce of the same gradients (worst relative difference {worst:.2e}, "
+              f"visibility counts exact)", flush=True)
+
+    # cost: one view per step, L2 flushed; (a) no exchange, (b) fused push + barrier, (c) NCCL all-reduce after the step
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+    def timed(fn, n=30):
+        for i in range(5): fn(i)
+        torch.cuda.synchronize(); dist.barrier()
+        ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+        for i in range(n):
+            flush.zero_(); ev[i][0].record(); fn(i); ev[i][1].record()
+        torch.cuda.synchronize(); dist.barrier()
+        t = torch.tensor([sum(a.elapsed_time(b) for a, b in ev) / n], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t)
+    def load(st, i):
+        st.viewmatrices[0].copy_(cams[i % 4].viewmatrix); st.projmatrices[0].copy_(cams[i % 4].projmatrix)
+        st.cam_positions[0].copy_(cams[i % 4].campos); st.upstream.copy_(ups[i % 4])
+    def local(i):
+        load(plain, i); plain.replay()
+    def fused(i):
+        b = i % 2; load(steps[b], i); xch.zero(1 - b); steps[b].replay(); xch.barrier()
+    def nccl(i):
+        load(plain, i); plain.replay(); dist.all_reduce(plain.trainable_grads())
+    def push_only(i):
+        b = i % 2; load(steps[b], i); steps[b].replay()
+    def barrier_only(i):
+        xch.barrier()
+    def zero_only(i):
+        xch.zero(i % 2)
+    t0, t1, t2 = timed(local), timed(fused), timed(nccl)
+    t3, t4, t5 = timed(push_only), timed(barrier_only), timed(zero_only)
+    if rank == 0:
+        print(f"   step with the pushes but no barrier / zeroing {t3:.4f} | barrier alone {t4:.4f} | zeroing one buffer {t5:.4f}", flush=True)
+    if rank == 0:
+        print(f"{world} ranks, ms per step: no exchange {t0:.4f} | fused push + barrier {t1:.4f} | NCCL all-reduce after the step {t2:.4f}", flush=True)
+    torch.cuda.synchronize(); dist.barrier(); dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
