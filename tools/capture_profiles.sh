@@ -15,10 +15,17 @@ timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --c
 python bench.py --impl reference $A --steps 3 --warmup 3 > $out/${tag}_plain_short_ref.log 2>&1 &&
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file $out/${tag}_launches_ref.csv \
     python bench.py --impl reference $A --steps 3 --warmup 3 > $out/${tag}_ncu_ref.log 2>&1
-BENCH_E2E_EAGER=1 python bench.py $A --steps 3 --warmup 3 > $out/${tag}_plain_short_eager.log 2>&1 &&
-BENCH_E2E_EAGER=1 timeout 900 ncu --set full --clock-control none --import-source on \
-    -k regex:'(preprocess_kernel|tile_scan_kernel|scatter_pairs_kernel|tile_sort_kernel|blend_forward_kernel|blend_backward_kernel|preprocess_backward_kernel)' \
-    -s 21 -c 7 -o $out/${tag}_full_ours -f python bench.py $A --steps 3 --warmup 3 > $out/${tag}_ncu_full.log 2>&1
+# one full cycle of the eight bench views (eager launches; the first 8 steps are warm-up): 8 x 7 kernels
+BENCH_E2E_EAGER=1 python bench.py $A --steps 8 --warmup 8 > $out/${tag}_plain_short_eager.log 2>&1 &&
+BENCH_E2E_EAGER=1 timeout 1200 ncu --set full --clock-control none --import-source on \
+    -k regex:'(preprocess_kernel|tile_scan_kernel|scatter_pairs_kernel|tile_sort_kernel<4, 256|blend_forward_kernel|blend_backward_kernel|preprocess_backward_kernel)' \
+    -s 56 -c 56 -o /tmp/${tag}_full_ours -f python bench.py $A --steps 8 --warmup 8 > $out/${tag}_ncu_full.log 2>&1
+# gpurun brings back at most 64 MiB: export the raw metric page and the per-kernel source pages here, drop the report
+ncu -i /tmp/${tag}_full_ours.ncu-rep --page raw --csv > $out/${tag}_full_ours_raw.csv 2>/dev/null
+for k in blend_backward blend_forward tile_sort scatter_pairs preprocess_kernel preprocess_backward; do
+    ncu -i /tmp/${tag}_full_ours.ncu-rep --page source --csv --kernel-name regex:$k --launch-skip 0 --launch-count 1 2>/dev/null \
+        | python tools/ncu_regions.py > $out/${tag}_regions_$k.txt
+done
 tail -c 300 $out/${tag}_ncu_full.log
 head -c 400 $out/${tag}_plain_ours.json
 head -c 300 $out/${tag}_plain_ref.json
