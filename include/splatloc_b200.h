@@ -263,6 +263,19 @@ int sl_backward_batch_push(int n_views, int P, int D, int M, int R, int C,
                            float* dL_dsh, float* dL_dscale, float* dL_drot, float* dL_dtau,
                            float* exchange_multicast, int debug, void* stream);
 
+/* Split-phase cross-GPU barrier for that exchange (no reference counterpart).  `flags` are `world`
+ * uint32 counters at the same offset of every GPU's exchange allocation, zero at start; flags[r] counts
+ * the steps rank r has arrived at.  sl_exchange_arrive (enqueue after sl_backward_batch_push on the same
+ * stream) adds 1 to flags[rank] on ALL GPUs through `flags_multicast`, ordered after the rows already
+ * pushed.  sl_exchange_wait (enqueue before the rows of the PREVIOUS step are read, and before this
+ * step's sl_backward_batch_push) makes the stream wait until every rank has arrived as many times as
+ * this GPU has waited (`waits`: one uint32 in this GPU's memory, zero at start, incremented by the wait
+ * when `advance` != 0; advance == 0 waits for all arrivals up to now without counting: the flush after
+ * the last step).  A wait gives up after `timeout_ms` and sets *status = 1 (status may be NULL). */
+int sl_exchange_arrive(unsigned int* flags_multicast, int rank, void* stream);
+int sl_exchange_wait(const unsigned int* flags, int world, unsigned int* waits, int advance, int timeout_ms,
+                     int* status, void* stream);
+
 /* ---- render() with its pre-processing inside ----------------------------
  * SplatLoc's render() (gaussian_splatting/gaussian_renderer/__init__.py:12-141) turns the optimiser's
  * raw parameters into rasterizer inputs with PyTorch ops on every call -- opacity = sigmoid(_opacity),

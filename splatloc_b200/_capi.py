@@ -126,6 +126,8 @@ SIGNATURES = {
         _F, _F, _F, _F,                              # dL_dsh, dL_dscale, dL_drot, dL_dtau
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
+    "sl_exchange_arrive": (C.c_int, [_F, C.c_int, C.c_void_p]),                    # flags_multicast, rank, stream
+    "sl_exchange_wait": (C.c_int, [_F, C.c_int, _F, C.c_int, C.c_int, _F, C.c_void_p]),  # flags, world, waits, advance, timeout_ms, status, stream
     "sl_backward_batch_push": (C.c_int, [
         C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # n_views, P, D, M, R, C
         _F, C.c_int, C.c_int,                        # background, width, height

@@ -689,6 +689,30 @@ int sl_backward_batch_push(int n_views, int P, int D, int M, int R, int C,
                          nullptr, nullptr, nullptr, exchange_multicast);
 }
 
+int sl_exchange_arrive(unsigned int* flags_multicast, int rank, void* stream_)
+{
+    g_error[0] = 0;
+    if (flags_multicast == nullptr || rank < 0) {
+        set_error("sl_exchange_arrive: flags_multicast is required and rank must be >= 0");
+        return SL_ERR_ARGUMENT;
+    }
+    sl::launch_exchange_arrive(flags_multicast, rank, (cudaStream_t)stream_);
+    return check_stage(false, (cudaStream_t)stream_, "sl_exchange_arrive");
+}
+
+int sl_exchange_wait(const unsigned int* flags, int world, unsigned int* waits, int advance, int timeout_ms,
+                     int* status, void* stream_)
+{
+    g_error[0] = 0;
+    if (flags == nullptr || waits == nullptr || world < 1 || world > 1024 || timeout_ms < 0) {
+        set_error("sl_exchange_wait: flags and waits are required, 1 <= world <= 1024, timeout_ms >= 0");
+        return SL_ERR_ARGUMENT;
+    }
+    sl::launch_exchange_wait(flags, world, waits, advance, (unsigned long long)timeout_ms * 1000000ull, status,
+                             (cudaStream_t)stream_);
+    return check_stage(false, (cudaStream_t)stream_, "sl_exchange_wait");
+}
+
 // ---- render() with its pre-processing inside --------------------------------
 static int check_render_args(const char* who, int scale_dim, const float* features_dc, const float* raw_opacity,
                              const float* raw_scaling, const float* raw_rotation)

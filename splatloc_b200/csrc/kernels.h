@@ -177,4 +177,9 @@ int launch_densify_plan(const DensifyParams& dp, int P, const float* xyz_gradien
 int launch_densify_apply(const DensifyArrays& arr, int P, int scale_dim, const char* scratch, const uint32_t* totals,
                          const float* noise, cudaStream_t stream);
 
+// ---- split-phase cross-GPU barrier of the fused gradient exchange (exchange.cu; no reference counterpart).
+int launch_exchange_arrive(uint32_t* flags_multicast, int rank, cudaStream_t stream);
+int launch_exchange_wait(const uint32_t* flags, int world, uint32_t* waits, int advance, unsigned long long timeout_ns,
+                         int* status, cudaStream_t stream);
+
 }  // namespace sl

@@ -19,7 +19,23 @@ that produces the data, no extra kernel, no SMs on the receiving side.
         grads = xch.rows(b)        # (P, 16): mean xyz, opacity | scale xyz, seen | rot wxyz | colour c0..c3
 
 Two buffers alternate because a GPU that leaves the barrier early starts pushing the next step while a
-slower one still reads this step's sums.  Built on torch.distributed._symmetric_memory (allocation,
+slower one still reads this step's sums.
+
+Split-phase form (`arrive` / `wait_previous`; `GraphedViewStep(..., exchange=xch, exchange_buffer=b)`
+places them): the full barrier at the end of a step makes every GPU wait for the step's slowest view
+and squeezes all incoming rows through the link at once.  Instead, a step ends with `arrive()` ("my rows
+have been sent", one release-ordered multimem.red on a per-rank counter) and the NEXT step calls
+`wait_previous()` after its forward pass, right before its own backward pushes: the sums of step i are
+read during step i + 1 -- like an all-reduce overlapped with the next step -- and a GPU only ever waits
+when it is more than a forward pass ahead of the slowest one.
+
+    steps = [GraphedViewStep(..., exchange=xch, exchange_buffer=b, consume=apply_sums) for b in (0, 1)]
+    for i, view in enumerate(views):
+        steps[i % 2].replay()   # forward | wait for step i-1 | consume(rows(1-b)), zero them | backward + push | arrive
+    xch.wait_all()              # the last step's sums: xch.rows((len(views) - 1) % 2)
+
+Why two buffers are enough: rank r zeroes buffer 1-b before its arrive of step i, and nobody pushes step
+i + 1 (into 1-b) before having waited for everyone's arrive of step i.  Built on torch.distributed._symmetric_memory (allocation,
 rendezvous, multicast mapping, signal-pad barrier); raises if the box has no multicast support.
 """
 from __future__ import annotations
@@ -27,7 +43,10 @@ from __future__ import annotations
 import torch
 import torch.distributed as dist
 
+from . import _capi
+
 ROW = 16      # floats per Gaussian (csrc/common.cuh: EXCHANGE_ROW)
+_FLAG_WORDS = 1024   # per-rank arrival counters behind the two buffers (one uint32 each; world <= 1024)
 
 
 class NvlsGradientExchange:
@@ -35,11 +54,17 @@ class NvlsGradientExchange:
         import torch.distributed._symmetric_memory as symm
         self.P, self.device, self.timeout_ms = int(P), torch.device(device), int(timeout_ms)
         group = group if group is not None else dist.group.WORLD
-        self._buf = symm.empty(2 * self.P * ROW, dtype=torch.float32, device=self.device)
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        if self.world > _FLAG_WORDS:
+            raise ValueError(f"at most {_FLAG_WORDS} ranks")
+        self._buf = symm.empty(2 * self.P * ROW + _FLAG_WORDS, dtype=torch.float32, device=self.device)
         self._hdl = symm.rendezvous(self._buf, group.group_name)
         if not self._hdl.multicast_ptr:
             raise RuntimeError("symmetric memory came up without a multicast mapping (no NVSwitch / NVLS on this box)")
         self._buf.zero_()
+        self._flags = self._buf[2 * self.P * ROW:]                      # this GPU's copy of the arrival counters
+        self._waits = torch.zeros(1, dtype=torch.int32, device=self.device)   # waits this GPU has done
+        self._status = torch.zeros(1, dtype=torch.int32, device=self.device)  # 1: a wait timed out
         torch.cuda.synchronize(self.device)
         self._hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
 
@@ -57,6 +82,40 @@ class NvlsGradientExchange:
     def barrier(self) -> None:
         """Cross-GPU barrier on the current stream (no host synchronisation)."""
         self._hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
+
+    def reset(self) -> None:
+        """Collective: all ranks idle, both buffers zero (after warm-up or capture runs left partial sums)."""
+        torch.cuda.synchronize(self.device)
+        self._hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
+        self.zero(0)
+        self.zero(1)
+        torch.cuda.synchronize(self.device)
+        self._hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
+
+    # ---- split-phase barrier (csrc/exchange.cu) -------------------------------------------------
+    def arrive(self) -> None:
+        """On the current stream, after a step's push: tell every GPU this rank's rows of the step are out."""
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _capi.check(_capi.load().sl_exchange_arrive(int(self._hdl.multicast_ptr) + 2 * self.P * ROW * 4, self.rank, stream))
+
+    def wait_previous(self) -> None:
+        """On the current stream: wait until every rank has arrived at all steps before this one (the n-th
+        call waits for n - 1 arrivals per rank; the first returns at once)."""
+        self._wait(1)
+
+    def wait_all(self) -> None:
+        """On the current stream: wait until every rank has arrived at every step this GPU has started."""
+        self._wait(0)
+
+    def _wait(self, advance: int) -> None:
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _capi.check(_capi.load().sl_exchange_wait(self._flags.data_ptr(), self.world, self._waits.data_ptr(), advance,
+                                                  self.timeout_ms, self._status.data_ptr(), stream))
+
+    @property
+    def timed_out(self) -> bool:
+        """True if a wait gave up after `timeout_ms` (synchronises the stream's device)."""
+        return bool(int(self._status))
 
     @staticmethod
     def unpack(rows: torch.Tensor) -> dict:

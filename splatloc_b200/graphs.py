@@ -36,7 +36,8 @@ _EMPTY = torch.Tensor([])
 class GraphedViewStep:
     def __init__(self, params: dict, H: int, W: int, tanfovx: float, tanfovy: float, bg: torch.Tensor,
                  max_pairs: int, sh_degree: int = 0, scale_modifier: float = 1.0, host_images: torch.Tensor | None = None,
-                 warmup: int = 3, n_views: int = 1, exchange_multicast: int | None = None):
+                 warmup: int = 3, n_views: int = 1, exchange_multicast: int | None = None,
+                 exchange=None, exchange_buffer: int = 0, consume=None):
         """`params`: tensors `means3D`, `opacities`, `scales`, `rotations` and `colors_precomp` (P, C) or
         `shs` (P, M, 3); after every replay their `.grad` is this step's gradient (a view of the step's
         own packed block, `self.grad_block` -- overwritten by the next replay, not accumulated).
@@ -45,8 +46,15 @@ class GraphedViewStep:
         the images are copied into it inside the graph, overlapped with the backward, laid out
         [colour of all views | depth | alpha], and are complete when the replay is.
         `exchange_multicast`: multicast address of a multi-GPU exchange buffer (splatloc_b200.exchange);
-        every replay then adds this step's summed gradients into all GPUs' buffers from its last kernel."""
+        every replay then adds this step's summed gradients into all GPUs' buffers from its last kernel.
+        `exchange` (an `NvlsGradientExchange`) with `exchange_buffer` b: the same push into buffer b, with the
+        split-phase barrier inside the captured step -- forward | wait for every GPU's rows of the PREVIOUS
+        step | `consume(exchange.rows(1 - b))` if given, then those rows are zeroed (beside the backward) |
+        backward + push | arrive.  Alternate two such steps (b = 0, 1); see splatloc_b200/exchange.py."""
         self.params = params
+        self.exchange, self.exchange_buffer, self.consume = exchange, int(exchange_buffer), consume
+        if exchange is not None:
+            exchange_multicast = exchange.multicast_ptr(self.exchange_buffer)
         self.exchange_multicast = exchange_multicast
         dev = params["means3D"].device
         self.H, self.W, self.V = int(H), int(W), int(n_views)
@@ -71,6 +79,7 @@ class GraphedViewStep:
         if host_images is not None and host_images.numel() != V * (C + 2) * N:
             raise ValueError(f"host_images must hold {V * (C + 2) * N} floats")
         self._side = torch.cuda.Stream(device=dev) if host_images is not None else None
+        self._zero_side = torch.cuda.Stream(device=dev) if exchange is not None else None
         self.graph = None
         self.color = self.depth = self.alpha = self.radii = self.overflow = None
         self.grad_block = None           # the packed gradient block of the captured backward (flat float32)
@@ -110,6 +119,15 @@ class GraphedViewStep:
             self._side.wait_stream(main)
             with torch.cuda.stream(self._side):
                 self.host_images.view(-1).copy_(color._base, non_blocking=True)
+        xch = self.exchange
+        if xch is not None:
+            other = 1 - self.exchange_buffer
+            xch.wait_previous()                      # every GPU's rows of the previous step are in rows(other)
+            if self.consume is not None:
+                self.consume(xch.rows(other))
+            self._zero_side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self._zero_side):
+                xch.zero(other)                      # nobody pushes into it before having seen this step's arrive
         bw = _C.rasterize_gaussians_backward_batch(
             self.bg, means3D, radii, colors, scales, rot, self.scale_modifier, _EMPTY, self.viewmatrices,
             self.projmatrices, self.tanfovx, self.tanfovy, self.upstream_color, self.upstream_depth, self.upstream_alpha,
@@ -117,6 +135,9 @@ class GraphedViewStep:
             exchange_multicast=self.exchange_multicast)
         if self.host_images is not None:
             torch.cuda.current_stream().wait_stream(self._side)
+        if xch is not None:
+            torch.cuda.current_stream().wait_stream(self._zero_side)
+            xch.arrive()
         self._fw, self._bw = fw, bw
         if V == 1:
             self.color, self.depth, self.alpha, self.radii = color[0], depth[0], alpha[0], radii[0]

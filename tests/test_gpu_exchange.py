@@ -22,3 +22,5 @@ def test_fused_exchange_equals_nccl_all_reduce_on_two_gpus():
     r = subprocess.run(cmd, cwd=ROOT, env=env, capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert "fused exchange == NCCL all-reduce" in r.stdout
+    # the same sums through the split-phase barrier (arrive / wait inside the replayed step), ranks skewed
+    assert "split-phase exchange == NCCL all-reduce" in r.stdout

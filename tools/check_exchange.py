@@ -64,6 +64,52 @@ def main():
         print(f"{world} ranks: fused exchange == NCCL all-reduce of the same gradients (worst relative difference {worst:.2e}, "
               f"visibility counts exact)", flush=True)
 
+    # split-phase form: forward | wait for the previous step | consume + zero | backward + push | arrive, all inside
+    # the replay; the sums of step i are read during step i + 1.  Ranks are skewed on purpose.
+    snap = torch.zeros(P, 16, device=dev)
+    split = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000, exchange=xch,
+                             exchange_buffer=b, consume=lambda rows: snap.copy_(rows)) for b in (0, 1)]
+    xch.reset()
+    n_steps, refs, seens, snaps = 7, [], [], []
+    for i in range(n_steps):
+        plain.set_camera(cams[i % 4].viewmatrix, cams[i % 4].projmatrix, cams[i % 4].campos)
+        plain.upstream.copy_(ups[i % 4])
+        plain.replay()
+        ref, seen = plain.trainable_grads().clone(), (plain.radii > 0).float()
+        dist.all_reduce(ref); dist.all_reduce(seen)
+        refs.append(ref); seens.append(seen)
+    torch.cuda.synchronize(); dist.barrier()
+    for i in range(n_steps):
+        st = split[i % 2]
+        st.set_camera(cams[i % 4].viewmatrix, cams[i % 4].projmatrix, cams[i % 4].campos)
+        st.upstream.copy_(ups[i % 4])
+        torch.cuda._sleep(int(3e5) * ((rank + i) % 3))           # up to ~0.3 ms of skew between the ranks
+        st.replay()
+        snaps.append(snap.clone())                                # sums of step i - 1 (zeros at i = 0)
+    xch.wait_all()
+    snaps.append(xch.rows((n_steps - 1) % 2).clone())
+    torch.cuda.synchronize()
+    assert not xch.timed_out, "a split-phase wait timed out"
+    assert float(snaps[0].abs().max()) == 0.0
+    worst2 = 0.0
+    for i in range(n_steps):
+        got = NvlsGradientExchange.unpack(snaps[i + 1])
+        off = 0
+        for name, w in (("means3D", 3), ("opacities", 1), ("scales", 3), ("rotations", 4), ("colors_precomp", C)):
+            n = (P * w + 3) // 4 * 4
+            want = refs[i][off:off + P * w].view(P, w)
+            off += n
+            err = float((got[name] - want).abs().max()); scale = float(want.abs().max())
+            worst2 = max(worst2, err / max(scale, 1e-30))
+            assert err <= 2e-5 * 16 * scale, ("split-phase", i, name, err, scale)
+        assert torch.equal(got["seen"], seens[i]), ("split-phase visibility counts", i)
+    if rank == 0:
+        print(f"{world} ranks: split-phase exchange == NCCL all-reduce over {n_steps} skewed steps (worst relative difference "
+              f"{worst2:.2e}, visibility counts exact)", flush=True)
+    split_plain = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000, exchange=xch,
+                                   exchange_buffer=b) for b in (0, 1)]
+    xch.reset()
+
     # cost: one view per step, L2 flushed; (a) no exchange, (b) fused push + barrier, (c) NCCL all-reduce after the step
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
     def timed(fn, n=30):
@@ -85,6 +131,8 @@ def main():
         b = i % 2; load(steps[b], i); xch.zero(1 - b); steps[b].replay(); xch.barrier()
     def nccl(i):
         load(plain, i); plain.replay(); dist.all_reduce(plain.trainable_grads())
+    def fused_split(i):
+        b = i % 2; load(split_plain[b], i); split_plain[b].replay()
     def push_only(i):
         b = i % 2; load(steps[b], i); steps[b].replay()
     def barrier_only(i):
@@ -92,11 +140,15 @@ def main():
     def zero_only(i):
         xch.zero(i % 2)
     t0, t1, t2 = timed(local), timed(fused), timed(nccl)
+    t6 = timed(fused_split)
+    xch.wait_all(); torch.cuda.synchronize(); assert not xch.timed_out
+    xch.reset()
     t3, t4, t5 = timed(push_only), timed(barrier_only), timed(zero_only)
     if rank == 0:
         print(f"   step with the pushes but no barrier / zeroing {t3:.4f} | barrier alone {t4:.4f} | zeroing one buffer {t5:.4f}", flush=True)
     if rank == 0:
-        print(f"{world} ranks, ms per step: no exchange {t0:.4f} | fused push + barrier {t1:.4f} | NCCL all-reduce after the step {t2:.4f}", flush=True)
+        print(f"{world} ranks, ms per step: no exchange {t0:.4f} | fused push + barrier {t1:.4f} | fused push, split-phase barrier "
+              f"{t6:.4f} | NCCL all-reduce after the step {t2:.4f}", flush=True)
     torch.cuda.synchronize(); dist.barrier(); dist.destroy_process_group()
 
 
