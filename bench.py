@@ -188,7 +188,8 @@ class Job:
         if self.world > 1:
             import datetime
             import torch.distributed as dist
-            os.environ.setdefault("NCCL_DEBUG", "WARN")      # (keeps NCCL's version banner off stdout: one JSON line)
+            os.environ.setdefault("NCCL_DEBUG", "WARN")
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # NCCL's version banner and warnings: off stdout (one JSON line)
             dist.init_process_group("nccl", device_id=self.dev, timeout=datetime.timedelta(seconds=300))
             self.dist = dist
         self.flush = torch.empty(L2_FLUSH_BYTES, dtype=torch.uint8, device=self.dev)
@@ -476,6 +477,10 @@ def run_train_step(args, impl):
                 # overlapped all-reduce)
                 fused_split = [GraphedViewStep(leaves, H, W, c0.tanfovx, c0.tanfovy, bg, max_pairs=int(1.25 * max_R) + 4096,
                                                exchange=xch, exchange_buffer=b) for b in (0, 1)]
+                # and with the rows sent by a kernel of their own (sl_exchange_push) beside the NEXT step's forward:
+                # plain backward, nothing of the exchange on the critical path but the wait that ends a step
+                fused_later = [GraphedViewStep(leaves, H, W, c0.tanfovx, c0.tanfovy, bg, max_pairs=int(1.25 * max_R) + 4096,
+                                               exchange=xch, exchange_buffer=b, exchange_mode="next_step") for b in (0, 1)]
                 side = torch.cuda.Stream(device=dev)
             except Exception as e:      # noqa: BLE001
                 fused = None
@@ -497,6 +502,14 @@ def run_train_step(args, impl):
             st = fused_split[i % 2]
             load_into(st, i)
             st.replay()          # forward | wait for step i - 1's rows | zero them | backward + push | arrive
+
+        later = {"last": 0}
+
+        def step_resident_graph_fused_later(i):
+            st = fused_later[i % 2]
+            load_into(st, i)
+            st.replay()          # [zero | push step i - 1's rows | arrive] beside [forward | backward], then wait
+            later["last"] = i % 2
 
         def step_resident_graph_fused(i):
             b = i % 2
@@ -528,7 +541,7 @@ def run_train_step(args, impl):
         e2e_ms, _, _ = job.timed(step_e2e_graph, args.steps, args.warmup, after=exchange.wait)
         e2e_unpiped_ms, _, _ = job.timed(step_e2e_graph_unpipelined, args.steps, args.warmup, after=exchange.wait)
         assert int(graphed.overflow) == 0, "bench: the graphed step's pair capacity was exceeded"
-        fused_ms = fused_split_ms = None
+        fused_ms = fused_split_ms = fused_later_ms = None
         headline_exchange = "nccl_overlapped"
         if use_dist:
             sync_ms, _, _ = job.timed(step_resident_graph_sync, args.steps, args.warmup)
@@ -541,12 +554,22 @@ def run_train_step(args, impl):
                                                                     after=xch.wait_all)
                 assert int(fused_split[0].overflow) == 0 and int(fused_split[1].overflow) == 0
                 assert not xch.timed_out, "bench: a split-phase exchange wait timed out"
+                xch.reset()
+                fused_later_ms, fused_later_per_step, _ = job.timed(step_resident_graph_fused_later, args.steps, args.warmup,
+                                                                    after=lambda: xch.flush_deferred(later["last"]))
+                assert int(fused_later[0].overflow) == 0 and int(fused_later[1].overflow) == 0
+                assert not xch.timed_out, "bench: a deferred-push exchange wait timed out"
                 nccl_ms = ms_total
                 # the headline is the fastest of the exchanges (same on all ranks: max-reduced times)
                 if fused_ms < ms_total:
                     ms_total, per_step, headline_exchange = fused_ms, fused_per_step, "fused_push"
+                    launches = fused[0].kernels_per_replay * args.steps
                 if fused_split_ms < ms_total:
                     ms_total, per_step, headline_exchange = fused_split_ms, fused_split_per_step, "fused_push_split_barrier"
+                    launches = fused_split[0].kernels_per_replay * args.steps
+                if fused_later_ms < ms_total:
+                    ms_total, per_step, headline_exchange = fused_later_ms, fused_later_per_step, "push_beside_next_forward"
+                    launches = fused_later[0].kernels_per_replay * args.steps
     else:
         e2e_ms, _, _ = job.timed(step_e2e_eager, args.steps, args.warmup)
     e2e_eager_ms, _, _ = job.timed(step_e2e_eager, args.steps, args.warmup) if graphed is not None else (None, None, None)
@@ -574,7 +597,15 @@ def run_train_step(args, impl):
     mpix = lambda ms_sum: round(N * n_ranks / (ms_sum / args.steps * 1e-3) / 1e6, 3)   # noqa: E731
 
     parallelism = f"views sharded over {n_ranks} GPU(s)"
-    if use_dist and graphed is not None and headline_exchange != "nccl_overlapped":
+    if use_dist and graphed is not None and headline_exchange == "push_beside_next_forward":
+        parallelism += (", gradient exchange by this library's own NVLS kernel: every Gaussian a GPU's view saw adds its row "
+                        "(15 trainable floats + a visibility count) into all GPUs' exchange buffers with multimem.red through "
+                        "the NVSwitch (sl_exchange_push, splatloc_b200.exchange), launched inside the replayed step on a second "
+                        "stream beside the NEXT step's forward; split-phase device-side barrier (arrive after the push, wait at "
+                        "the end of that step), so the sums of step i are complete at the end of step i + 1 (as with the "
+                        "overlapped all-reduce); the last step's push and wait are inside the timed region; NCCL only for the "
+                        "comparison figures in `exchange`")
+    elif use_dist and graphed is not None and headline_exchange != "nccl_overlapped":
         parallelism += (", gradient exchange fused into the per-Gaussian backward: every Gaussian a GPU's view saw adds its "
                         "row (15 trainable floats + a visibility count) into all GPUs' exchange buffers with multimem.red "
                         "through the NVSwitch (splatloc_b200.exchange, sl_backward_batch_push); ")
@@ -624,6 +655,8 @@ def run_train_step(args, impl):
                                "fused_push_ms_per_step": round(fused_ms / args.steps, 4) if fused_ms is not None else None,
                                "fused_push_split_barrier_ms_per_step": (round(fused_split_ms / args.steps, 4)
                                                                         if fused_split_ms is not None else None),
+                               "push_beside_next_forward_ms_per_step": (round(fused_later_ms / args.steps, 4)
+                                                                        if fused_later_ms is not None else None),
                                "headline": headline_exchange,
                                "nccl_bytes": int(graphed.grad_block.trainable_numel) * 4,
                                "fused_push_bytes_sent": "64 B per Gaussian this GPU's view saw (multimem.red through the switch)"}

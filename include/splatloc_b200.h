@@ -273,8 +273,30 @@ int sl_backward_batch_push(int n_views, int P, int D, int M, int R, int C,
  * when `advance` != 0; advance == 0 waits for all arrivals up to now without counting: the flush after
  * the last step).  A wait gives up after `timeout_ms` and sets *status = 1 (status may be NULL). */
 int sl_exchange_arrive(unsigned int* flags_multicast, int rank, void* stream);
-int sl_exchange_wait(const unsigned int* flags, int world, unsigned int* waits, int advance, int timeout_ms,
-                     int* status, void* stream);
+/* `ahead`: 0 as described; 1: every rank must ALSO have arrived at the step this wait is part of (for
+ * the deferred push below, whose arrive comes first in a step and its wait last). */
+int sl_exchange_wait(const unsigned int* flags, int world, unsigned int* waits, int ahead, int advance,
+                     int timeout_ms, int* status, void* stream);
+
+/* The push as a launch of its own (no reference counterpart): sends the rows sl_backward_batch_push would
+ * have sent, from finished gradient arrays, so that a caller can push step i's rows on a second stream
+ * while step i + 1 renders.  `source` is a sl_exchange_source in DEVICE memory (read when the kernel
+ * runs, so a captured launch can be bound afterwards); source->radii == NULL: nothing is sent.
+ * Gradients as sl_backward_batch returns them with colors_precomp and scales / rotations.
+ * `max_ctas`: CTAs of the push kernel (256 threads each, striding over the Gaussians); 0: 48, which on a
+ * B200 sends 500 k rows' visible fraction in well under a 640x480 step while leaving the concurrent
+ * forward its SMs (measured: 8 CTAs take longer than the step, 148 and more slow the forward down). */
+typedef struct {
+    const int* radii;            /* [n_views, P]: a Gaussian is sent if any view has radii > 0 */
+    const float* dL_dmean3D;     /* [P, 3] */
+    const float* dL_dopacity;    /* [P]    */
+    const float* dL_dscale;      /* [P, 3] ([P] if scale_dim == 1) */
+    const float* dL_drot;        /* [P, 4], 16-byte aligned */
+    const float* dL_dcolor;      /* [P, C] */
+    int n_views;
+    int scale_dim;
+} sl_exchange_source;
+int sl_exchange_push(const sl_exchange_source* source, int P, int C, float* exchange_multicast, int max_ctas, void* stream);
 
 /* ---- render() with its pre-processing inside ----------------------------
  * SplatLoc's render() (gaussian_splatting/gaussian_renderer/__init__.py:12-141) turns the optimiser's

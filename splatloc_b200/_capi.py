@@ -127,7 +127,8 @@ SIGNATURES = {
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
     "sl_exchange_arrive": (C.c_int, [_F, C.c_int, C.c_void_p]),                    # flags_multicast, rank, stream
-    "sl_exchange_wait": (C.c_int, [_F, C.c_int, _F, C.c_int, C.c_int, _F, C.c_void_p]),  # flags, world, waits, advance, timeout_ms, status, stream
+    "sl_exchange_wait": (C.c_int, [_F, C.c_int, _F, C.c_int, C.c_int, C.c_int, _F, C.c_void_p]),  # flags, world, waits, ahead, advance, timeout_ms, status, stream
+    "sl_exchange_push": (C.c_int, [_F, C.c_int, C.c_int, _F, C.c_int, C.c_void_p]),   # source (device), P, C, exchange_multicast, max_ctas, stream
     "sl_backward_batch_push": (C.c_int, [
         C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,  # n_views, P, D, M, R, C
         _F, C.c_int, C.c_int,                        # background, width, height

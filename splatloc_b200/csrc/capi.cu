@@ -700,17 +700,32 @@ int sl_exchange_arrive(unsigned int* flags_multicast, int rank, void* stream_)
     return check_stage(false, (cudaStream_t)stream_, "sl_exchange_arrive");
 }
 
-int sl_exchange_wait(const unsigned int* flags, int world, unsigned int* waits, int advance, int timeout_ms,
+int sl_exchange_wait(const unsigned int* flags, int world, unsigned int* waits, int ahead, int advance, int timeout_ms,
                      int* status, void* stream_)
 {
     g_error[0] = 0;
-    if (flags == nullptr || waits == nullptr || world < 1 || world > 1024 || timeout_ms < 0) {
-        set_error("sl_exchange_wait: flags and waits are required, 1 <= world <= 1024, timeout_ms >= 0");
+    if (flags == nullptr || waits == nullptr || world < 1 || world > 1024 || timeout_ms < 0 || ahead < 0 || ahead > 1) {
+        set_error("sl_exchange_wait: flags and waits are required, 1 <= world <= 1024, ahead 0 or 1, timeout_ms >= 0");
         return SL_ERR_ARGUMENT;
     }
-    sl::launch_exchange_wait(flags, world, waits, advance, (unsigned long long)timeout_ms * 1000000ull, status,
+    sl::launch_exchange_wait(flags, world, waits, ahead, advance, (unsigned long long)timeout_ms * 1000000ull, status,
                              (cudaStream_t)stream_);
     return check_stage(false, (cudaStream_t)stream_, "sl_exchange_wait");
+}
+
+static_assert(sizeof(sl_exchange_source) == sizeof(sl::ExchangeSource), "sl_exchange_source mirrors sl::ExchangeSource");
+
+int sl_exchange_push(const sl_exchange_source* source, int P, int C, float* exchange_multicast, int max_ctas, void* stream_)
+{
+    g_error[0] = 0;
+    if (source == nullptr || exchange_multicast == nullptr || P < 0 || (C != 3 && C != 4)) {
+        set_error("sl_exchange_push: source and exchange_multicast are required, C must be 3 or 4 (got %d)", C);
+        return SL_ERR_ARGUMENT;
+    }
+    if (P == 0) return 0;
+    sl::launch_exchange_push(reinterpret_cast<const sl::ExchangeSource*>(source), P, C, exchange_multicast,
+                             max_ctas > 0 ? max_ctas : 48, (cudaStream_t)stream_);
+    return check_stage(false, (cudaStream_t)stream_, "sl_exchange_push");
 }
 
 // ---- render() with its pre-processing inside --------------------------------

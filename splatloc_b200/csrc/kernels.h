@@ -179,7 +179,18 @@ int launch_densify_apply(const DensifyArrays& arr, int P, int scale_dim, const c
 
 // ---- split-phase cross-GPU barrier of the fused gradient exchange (exchange.cu; no reference counterpart).
 int launch_exchange_arrive(uint32_t* flags_multicast, int rank, cudaStream_t stream);
-int launch_exchange_wait(const uint32_t* flags, int world, uint32_t* waits, int advance, unsigned long long timeout_ns,
-                         int* status, cudaStream_t stream);
+int launch_exchange_wait(const uint32_t* flags, int world, uint32_t* waits, int ahead, int advance,
+                         unsigned long long timeout_ns, int* status, cudaStream_t stream);
+struct ExchangeSource {      // mirrors sl_exchange_source (include/splatloc_b200.h); lives in device memory
+    const int* radii;        // [n_views, P]; nullptr: nothing to send
+    const float* dL_dmean3D;
+    const float* dL_dopacity;
+    const float* dL_dscale;
+    const float* dL_drot;
+    const float* dL_dcolor;
+    int n_views;
+    int scale_dim;           // 3, or 1: one scale gradient per Gaussian
+};
+int launch_exchange_push(const ExchangeSource* src, int P, int C, float* push_mc, int ctas, cudaStream_t stream);
 
 }  // namespace sl

@@ -35,7 +35,14 @@ when it is more than a forward pass ahead of the slowest one.
     xch.wait_all()              # the last step's sums: xch.rows((len(views) - 1) % 2)
 
 Why two buffers are enough: rank r zeroes buffer 1-b before its arrive of step i, and nobody pushes step
-i + 1 (into 1-b) before having waited for everyone's arrive of step i.  Built on torch.distributed._symmetric_memory (allocation,
+i + 1 (into 1-b) before having waited for everyone's arrive of step i.
+
+Deferred form (`GraphedViewStep(..., exchange=xch, exchange_buffer=b, exchange_mode="next_step")`): the
+rows of step i leave in a kernel of their own (`push_source`, sl_exchange_push) on a second stream at the
+start of step i + 1, under that step's latency-bound binning kernels, followed by `arrive`; step i + 1
+ends with `wait_current()`, after which rows(i % 2) hold the sums of step i.  The backward is the plain
+one; nothing of the exchange is on the critical path except the final wait.  `flush_deferred(b)` sends
+and waits for the last step's rows.  Built on torch.distributed._symmetric_memory (allocation,
 rendezvous, multicast mapping, signal-pad barrier); raises if the box has no multicast support.
 """
 from __future__ import annotations
@@ -64,6 +71,8 @@ class NvlsGradientExchange:
         self._buf.zero_()
         self._flags = self._buf[2 * self.P * ROW:]                      # this GPU's copy of the arrival counters
         self._waits = torch.zeros(1, dtype=torch.int32, device=self.device)   # waits this GPU has done
+        self._sources = torch.zeros(2, 8, dtype=torch.int64, device=self.device)   # two sl_exchange_source structs
+        self._channels = 0
         self._status = torch.zeros(1, dtype=torch.int32, device=self.device)  # 1: a wait timed out
         torch.cuda.synchronize(self.device)
         self._hdl.barrier(channel=0, timeout_ms=self.timeout_ms)
@@ -101,16 +110,50 @@ class NvlsGradientExchange:
     def wait_previous(self) -> None:
         """On the current stream: wait until every rank has arrived at all steps before this one (the n-th
         call waits for n - 1 arrivals per rank; the first returns at once)."""
-        self._wait(1)
+        self._wait(0, 1)
+
+    def wait_current(self) -> None:
+        """On the current stream: wait until every rank has arrived at this step too (the n-th call waits for
+        n arrivals per rank): the deferred form, whose arrive comes first in a step."""
+        self._wait(1, 1)
 
     def wait_all(self) -> None:
-        """On the current stream: wait until every rank has arrived at every step this GPU has started."""
-        self._wait(0)
+        """On the current stream: wait until every rank has arrived as often as this GPU has waited."""
+        self._wait(0, 0)
 
-    def _wait(self, advance: int) -> None:
+    def _wait(self, ahead: int, advance: int) -> None:
         stream = torch.cuda.current_stream(self.device).cuda_stream
-        _capi.check(_capi.load().sl_exchange_wait(self._flags.data_ptr(), self.world, self._waits.data_ptr(), advance,
+        _capi.check(_capi.load().sl_exchange_wait(self._flags.data_ptr(), self.world, self._waits.data_ptr(), ahead, advance,
                                                   self.timeout_ms, self._status.data_ptr(), stream))
+
+    # ---- deferred push (sl_exchange_push) --------------------------------------------------------
+    def bind_source(self, b: int, radii: torch.Tensor, dL_dmean3D: torch.Tensor, dL_dopacity: torch.Tensor,
+                    dL_dscale: torch.Tensor, dL_drot: torch.Tensor, dL_dcolor: torch.Tensor) -> None:
+        """The gradient arrays whose rows `push_source(b)` sends into buffer b: radii (V, P) int32 and the
+        outputs of the batch backward (colours precomputed).  Launches captured earlier see the binding."""
+        P = self.P
+        if radii.dtype != torch.int32 or radii.numel() % P or dL_dcolor.numel() % P or dL_dcolor.numel() // P not in (3, 4):
+            raise ValueError("bind_source: radii must be (V, P) int32 and dL_dcolor (P, 3 or 4)")
+        for t in (radii, dL_dmean3D, dL_dopacity, dL_dscale, dL_drot, dL_dcolor):
+            if not t.is_contiguous() or t.device != self.device:
+                raise ValueError("bind_source: contiguous tensors on the exchange's device")
+        self._channels = dL_dcolor.numel() // P
+        words = [radii.data_ptr(), dL_dmean3D.data_ptr(), dL_dopacity.data_ptr(), dL_dscale.data_ptr(), dL_drot.data_ptr(),
+                 dL_dcolor.data_ptr(), (radii.numel() // P) | ((dL_dscale.numel() // P) << 32), 0]
+        self._sources[b].copy_(torch.tensor(words, dtype=torch.int64))
+        torch.cuda.synchronize(self.device)
+
+    def push_source(self, b: int, max_ctas: int = 0) -> None:
+        """On the current stream: add the rows of source b (nothing if unbound) into buffer b on all GPUs."""
+        stream = torch.cuda.current_stream(self.device).cuda_stream
+        _capi.check(_capi.load().sl_exchange_push(self._sources[b].data_ptr(), self.P, self._channels or 4, self.multicast_ptr(b),
+                                                  max_ctas, stream))
+
+    def flush_deferred(self, b: int) -> None:
+        """After the last step of a deferred sequence (it used buffer b): send its rows, wait for everyone's."""
+        self.push_source(b)
+        self.arrive()
+        self._wait(1, 1)
 
     @property
     def timed_out(self) -> bool:

@@ -37,7 +37,8 @@ class GraphedViewStep:
     def __init__(self, params: dict, H: int, W: int, tanfovx: float, tanfovy: float, bg: torch.Tensor,
                  max_pairs: int, sh_degree: int = 0, scale_modifier: float = 1.0, host_images: torch.Tensor | None = None,
                  warmup: int = 3, n_views: int = 1, exchange_multicast: int | None = None,
-                 exchange=None, exchange_buffer: int = 0, consume=None):
+                 exchange=None, exchange_buffer: int = 0, consume=None, exchange_mode: str = "backward",
+                 exchange_push_ctas: int = 0):
         """`params`: tensors `means3D`, `opacities`, `scales`, `rotations` and `colors_precomp` (P, C) or
         `shs` (P, M, 3); after every replay their `.grad` is this step's gradient (a view of the step's
         own packed block, `self.grad_block` -- overwritten by the next replay, not accumulated).
@@ -50,10 +51,19 @@ class GraphedViewStep:
         `exchange` (an `NvlsGradientExchange`) with `exchange_buffer` b: the same push into buffer b, with the
         split-phase barrier inside the captured step -- forward | wait for every GPU's rows of the PREVIOUS
         step | `consume(exchange.rows(1 - b))` if given, then those rows are zeroed (beside the backward) |
-        backward + push | arrive.  Alternate two such steps (b = 0, 1); see splatloc_b200/exchange.py."""
+        backward + push | arrive.  Alternate two such steps (b = 0, 1); see splatloc_b200/exchange.py.
+        `exchange_mode="next_step"`: the rows leave in a kernel of their own at the start of the NEXT replay
+        (of the step built with the other `exchange_buffer`), on a second stream beside its forward:
+        [zero rows(b) | push the other step's rows | arrive] beside [forward | backward], then wait and
+        `consume(exchange.rows(1 - b))`: the sums of the previous step.  `exchange_push_ctas`: CTAs of that
+        push kernel (0: the library's default, few enough to leave the forward its SMs; < 0: no push at all,
+        to measure the protocol alone)."""
         self.params = params
         self.exchange, self.exchange_buffer, self.consume = exchange, int(exchange_buffer), consume
-        if exchange is not None:
+        if exchange_mode not in ("backward", "next_step"):
+            raise ValueError("exchange_mode: 'backward' or 'next_step'")
+        self.exchange_mode, self.exchange_push_ctas = exchange_mode, int(exchange_push_ctas)
+        if exchange is not None and exchange_mode == "backward":
             exchange_multicast = exchange.multicast_ptr(self.exchange_buffer)
         self.exchange_multicast = exchange_multicast
         dev = params["means3D"].device
@@ -104,6 +114,14 @@ class GraphedViewStep:
 
     def _step(self):
         p, V = self.params, self.V
+        deferred = self.exchange if self.exchange_mode == "next_step" else None
+        if deferred is not None:
+            self._zero_side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(self._zero_side):
+                deferred.zero(self.exchange_buffer)              # read at the end of the previous replay
+                if self.exchange_push_ctas >= 0:                 # the previous step's rows, from the other step's arrays
+                    deferred.push_source(1 - self.exchange_buffer, self.exchange_push_ctas)
+                deferred.arrive()
         shs = p.get("shs")
         colors = p.get("colors_precomp")
         shs = _EMPTY if shs is None else shs.detach()
@@ -119,7 +137,7 @@ class GraphedViewStep:
             self._side.wait_stream(main)
             with torch.cuda.stream(self._side):
                 self.host_images.view(-1).copy_(color._base, non_blocking=True)
-        xch = self.exchange
+        xch = self.exchange if self.exchange_mode == "backward" else None
         if xch is not None:
             other = 1 - self.exchange_buffer
             xch.wait_previous()                      # every GPU's rows of the previous step are in rows(other)
@@ -138,6 +156,11 @@ class GraphedViewStep:
         if xch is not None:
             torch.cuda.current_stream().wait_stream(self._zero_side)
             xch.arrive()
+        if deferred is not None:
+            torch.cuda.current_stream().wait_stream(self._zero_side)
+            deferred.wait_current()                  # every GPU's rows of the previous step have landed
+            if self.consume is not None:
+                self.consume(deferred.rows(1 - self.exchange_buffer))
         self._fw, self._bw = fw, bw
         if V == 1:
             self.color, self.depth, self.alpha, self.radii = color[0], depth[0], alpha[0], radii[0]
@@ -158,6 +181,10 @@ class GraphedViewStep:
             t = p.get(name)
             if t is not None and t.requires_grad:
                 t.grad = g.view(t.shape)
+        if self.exchange is not None and self.exchange_mode == "next_step":
+            if p.get("colors_precomp") is None:
+                raise ValueError("the exchange rows hold colors_precomp gradients (no SH)")
+            self.exchange.bind_source(self.exchange_buffer, self._fw[4], g_means3D, g_opac, g_scales, g_rot, g_colors)
 
     def set_camera(self, viewmatrix: torch.Tensor, projmatrix: torch.Tensor, campos: torch.Tensor, view: int = 0) -> None:
         """Copy a camera (reference convention: transposed world-to-view, full projection, centre) into

@@ -24,3 +24,5 @@ def test_fused_exchange_equals_nccl_all_reduce_on_two_gpus():
     assert "fused exchange == NCCL all-reduce" in r.stdout
     # the same sums through the split-phase barrier (arrive / wait inside the replayed step), ranks skewed
     assert "split-phase exchange == NCCL all-reduce" in r.stdout
+    # and with the rows sent by sl_exchange_push beside the next step's forward
+    assert "deferred-push exchange == NCCL all-reduce" in r.stdout

@@ -17,6 +17,7 @@ from splatloc_b200.graphs import GraphedViewStep
 
 
 def main():
+    quick = os.environ.get("CHECK_QUICK")      # timing of the deferred form only
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -106,6 +107,41 @@ def main():
     if rank == 0:
         print(f"{world} ranks: split-phase exchange == NCCL all-reduce over {n_steps} skewed steps (worst relative difference "
               f"{worst2:.2e}, visibility counts exact)", flush=True)
+    # deferred form: the rows of step i leave in their own kernel beside the forward of step i + 1
+    snap2 = torch.zeros(P, 16, device=dev)
+    later = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000, exchange=xch,
+                             exchange_buffer=b, exchange_mode="next_step", consume=lambda rows: snap2.copy_(rows)) for b in (0, 1)]
+    xch.reset()
+    snaps = []
+    for i in range(n_steps):
+        st = later[i % 2]
+        st.set_camera(cams[i % 4].viewmatrix, cams[i % 4].projmatrix, cams[i % 4].campos)
+        st.upstream.copy_(ups[i % 4])
+        torch.cuda._sleep(int(3e5) * ((rank + 2 * i) % 3))
+        st.replay()
+        snaps.append(snap2.clone())                               # sums of step i - 1 (i = 0: whatever the arrays held)
+    xch.flush_deferred((n_steps - 1) % 2)
+    snaps.append(xch.rows((n_steps - 1) % 2).clone())
+    torch.cuda.synchronize()
+    assert not xch.timed_out, "a deferred-push wait timed out"
+    worst3 = 0.0
+    for i in range(n_steps):
+        got = NvlsGradientExchange.unpack(snaps[i + 1])
+        off = 0
+        for name, w in (("means3D", 3), ("opacities", 1), ("scales", 3), ("rotations", 4), ("colors_precomp", C)):
+            n = (P * w + 3) // 4 * 4
+            want = refs[i][off:off + P * w].view(P, w)
+            off += n
+            err = float((got[name] - want).abs().max()); scale = float(want.abs().max())
+            worst3 = max(worst3, err / max(scale, 1e-30))
+            assert err <= 2e-5 * 16 * scale, ("deferred push", i, name, err, scale)
+        assert torch.equal(got["seen"], seens[i]), ("deferred push visibility counts", i)
+    if rank == 0:
+        print(f"{world} ranks: deferred-push exchange == NCCL all-reduce over {n_steps} skewed steps (worst relative difference "
+              f"{worst3:.2e}, visibility counts exact)", flush=True)
+    later_plain = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000, exchange=xch,
+                                   exchange_buffer=b, exchange_mode="next_step") for b in (0, 1)]
+    xch.reset()
     split_plain = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000, exchange=xch,
                                    exchange_buffer=b) for b in (0, 1)]
     xch.reset()
@@ -133,6 +169,8 @@ def main():
         load(plain, i); plain.replay(); dist.all_reduce(plain.trainable_grads())
     def fused_split(i):
         b = i % 2; load(split_plain[b], i); split_plain[b].replay()
+    def fused_later(i):
+        b = i % 2; load(later_plain[b], i); later_plain[b].replay()
     def push_only(i):
         b = i % 2; load(steps[b], i); steps[b].replay()
     def barrier_only(i):
@@ -143,12 +181,15 @@ def main():
     t6 = timed(fused_split)
     xch.wait_all(); torch.cuda.synchronize(); assert not xch.timed_out
     xch.reset()
+    t7 = timed(fused_later)
+    xch.flush_deferred(1); torch.cuda.synchronize()   # the last timed step (i = 29) used buffer 1; assert not xch.timed_out
+    xch.reset()
     t3, t4, t5 = timed(push_only), timed(barrier_only), timed(zero_only)
     if rank == 0:
         print(f"   step with the pushes but no barrier / zeroing {t3:.4f} | barrier alone {t4:.4f} | zeroing one buffer {t5:.4f}", flush=True)
     if rank == 0:
         print(f"{world} ranks, ms per step: no exchange {t0:.4f} | fused push + barrier {t1:.4f} | fused push, split-phase barrier "
-              f"{t6:.4f} | NCCL all-reduce after the step {t2:.4f}", flush=True)
+              f"{t6:.4f} | rows pushed beside the next forward {t7:.4f} | NCCL all-reduce after the step {t2:.4f}", flush=True)
     torch.cuda.synchronize(); dist.barrier(); dist.destroy_process_group()
 
 
