@@ -184,7 +184,14 @@ class GraphedViewStep:
         if self.exchange is not None and self.exchange_mode == "next_step":
             if p.get("colors_precomp") is None:
                 raise ValueError("the exchange rows hold colors_precomp gradients (no SH)")
-            self.exchange.bind_source(self.exchange_buffer, self._fw[4], g_means3D, g_opac, g_scales, g_rot, g_colors)
+            self.bind_exchange_source()
+
+    def bind_exchange_source(self) -> None:
+        """`exchange_mode="next_step"`: make this step's gradient arrays the ones the OTHER step's replay pushes
+        into buffer `exchange_buffer` (done at construction; call again after another pair of steps has been
+        built on the same exchange)."""
+        (_, _, g_colors, g_opac, g_means3D, _, _, g_scales, g_rot) = self._bw[:9]
+        self.exchange.bind_source(self.exchange_buffer, self._fw[4], g_means3D, g_opac, g_scales, g_rot, g_colors)
 
     def set_camera(self, viewmatrix: torch.Tensor, projmatrix: torch.Tensor, campos: torch.Tensor, view: int = 0) -> None:
         """Copy a camera (reference convention: transposed world-to-view, full projection, centre) into
