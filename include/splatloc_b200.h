@@ -470,6 +470,13 @@ void sl_set_binning_mode(int mode);
  *       stages per warp).  Kept for the A/B in profiles/README.md; measured slower on the B200. */
 void sl_set_record_stream(int mode);
 
+/* Programmatic dependent launches between the stages of a call (no reference counterpart).  PROCESS-WIDE.
+ * 1 (default): every stage kernel is launched so that its CTAs may become resident while the previous
+ * stage's last CTAs still run; they block on entry until that stage has completed, so results are
+ * unchanged -- what is saved is the drain / launch / ramp-up between the dependent kernels of a step.
+ * 0: plain stream-ordered launches. */
+void sl_set_chained_launches(int on);
+
 /* Per-stage device timing with CUDA events recorded on the caller's stream
  * around each stage of sl_forward / sl_backward.  sl_profile_enable(1) resets
  * and starts accumulation, sl_profile_enable(0) stops it.  sl_profile_read

@@ -186,6 +186,7 @@ SIGNATURES = {
     "sl_launch_count": (C.c_longlong, []),
     "sl_set_binning_mode": (None, [C.c_int]),
     "sl_set_record_stream": (None, [C.c_int]),
+    "sl_set_chained_launches": (None, [C.c_int]),
     "sl_profile_enable": (None, [C.c_int]),
     "sl_profile_stage_count": (C.c_int, []),
     "sl_profile_stage_name": (C.c_char_p, [C.c_int]),
@@ -210,6 +211,8 @@ def load() -> C.CDLL:
             fn.argtypes = args
         if os.environ.get("SPLATLOC_B200_BINNING"):      # tuning experiments: see sl_set_binning_mode
             lib.sl_set_binning_mode(int(os.environ["SPLATLOC_B200_BINNING"]))
+        if os.environ.get("SPLATLOC_B200_CHAINED_LAUNCHES"):  # A/B: see sl_set_chained_launches
+            lib.sl_set_chained_launches(int(os.environ["SPLATLOC_B200_CHAINED_LAUNCHES"]))
         if os.environ.get("SPLATLOC_B200_RECORD_STREAM"):  # A/B: see sl_set_record_stream
             lib.sl_set_record_stream(int(os.environ["SPLATLOC_B200_RECORD_STREAM"]))
         _lib = lib

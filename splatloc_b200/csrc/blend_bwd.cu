@@ -74,6 +74,8 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
                       size_t color_view_stride,
                       float* __restrict__ dL_ddepth)      // (views,P,1)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     __shared__ PairRecord s_rec[BLEND_WARPS][BLEND_CHUNK];
     __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];
     __shared__ float s_w[BLEND_WARPS][BWD_ROWS * BWD_STRIDE];          // alpha * T per (row, pixel)
@@ -321,12 +323,12 @@ int launch_blend_backward(int P, int C, const ViewParams& vp, const uint2* range
 {
     const int tiles = vp.tiles * vp.views;
     if (C == 4)
-        blend_backward_kernel<4><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
+        launch_chained(blend_backward_kernel<4>, dim3(tiles * BLEND_SUBS), dim3(BLEND_THREADS), 0, stream,
             ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, vp.tiles, P, bg, out_alpha, n_contrib, dL_dpix,
             dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
             color_view_stride, dL_ddepth);
     else if (C == 3)
-        blend_backward_kernel<3><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(
+        launch_chained(blend_backward_kernel<3>, dim3(tiles * BLEND_SUBS), dim3(BLEND_THREADS), 0, stream,
             ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, vp.tiles, P, bg, out_alpha, n_contrib, dL_dpix,
             dL_dpix_depth, dL_dpix_alpha, dL_dmean2D, dL_dabsmean2D, dL_dconic, dL_dopacity, dL_dcolor,
             color_view_stride, dL_ddepth);

@@ -32,6 +32,8 @@ blend_forward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restric
                      float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
                      int* __restrict__ n_touched)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     __shared__ PairRecord s_rec[BLEND_WARPS][BLEND_CHUNK];
     __shared__ uint8_t s_lane[BLEND_WARPS][BLEND_CHUNK];   // chunk-relative index of each parked record
 
@@ -204,6 +206,8 @@ blend_forward_bulk_kernel(const uint2* __restrict__ ranges, const uint32_t* __re
                           float* __restrict__ out_alpha, uint32_t* __restrict__ n_contrib,
                           int* __restrict__ n_touched)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     constexpr int STAGES = 2;
     __shared__ __align__(128) PairRecord s_stage[BLEND_WARPS][STAGES][BLEND_CHUNK];
     __shared__ __align__(8) unsigned long long s_bar[BLEND_WARPS][STAGES];
@@ -333,7 +337,7 @@ int launch_blend_forward(int P, int C, const ViewParams& vp, const uint2* ranges
 {
     const int tiles = vp.tiles * vp.views;
 #define SL_LAUNCH_FWD(KK, CC, TT)                                                                                \
-    KK<CC, TT><<<tiles * BLEND_SUBS, BLEND_THREADS, 0, stream>>>(                                                \
+    launch_chained(KK<CC, TT>, dim3(tiles * BLEND_SUBS), dim3(BLEND_THREADS), 0, stream,                         \
         ranges, tile_order, records, masks, vp.W, vp.H, vp.grid_x, vp.tiles, P, bg, out_color, out_depth, out_alpha, \
         n_contrib, n_touched)
     if (C != 3 && C != 4) {

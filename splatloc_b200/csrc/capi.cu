@@ -71,7 +71,10 @@ static std::atomic<int> g_binning_mode{0};  // sl_set_binning_mode(): 0 default,
 constexpr int kDefaultBinningMode = 2;
 static std::atomic<int> g_record_stream{0};  // sl_set_record_stream(): 0 per-lane loads of survivors, 1 bulk-copy staging
 
+static std::atomic<int> g_chained{1};        // sl_set_chained_launches(): programmatic dependent launches between the stages
+
 void count_launch(int n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
+bool chained_launches_enabled() { return g_chained.load(std::memory_order_relaxed) != 0; }
 
 struct StageTimer {
     int st;
@@ -191,6 +194,8 @@ void sl_set_binning_mode(int mode)
 {
     g_binning_mode.store(mode >= 1 && mode <= 2 ? mode : 0, std::memory_order_relaxed);
 }
+
+void sl_set_chained_launches(int on) { g_chained.store(on ? 1 : 0, std::memory_order_relaxed); }
 
 void sl_set_record_stream(int mode) { g_record_stream.store(mode == 1 ? 1 : 0, std::memory_order_relaxed); }
 

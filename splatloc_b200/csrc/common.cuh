@@ -11,6 +11,7 @@
 // third_party/glm/glm/detail/type_mat3x3.inl:486-520) so that nvcc's default
 // fused-multiply-add contraction produces the same roundings.
 #pragma once
+#include <utility>
 #include <cstdint>
 #include <cstddef>
 #include <cuda_runtime.h>
@@ -49,6 +50,37 @@ int check_stage(bool debug, cudaStream_t stream, const char* what);
 
 // Counts this library's own kernel launches (read back through sl_launch_count()).
 void count_launch(int n = 1);
+
+// ---- chained launches (programmatic dependent launch) ------------------------------------------
+// The stages of a step form one dependent chain of short kernels; between two of them the GPU would
+// drain, take the next launch and ramp up again.  Launched through launch_chained() a kernel's CTAs may
+// become resident while the previous kernel of the stream is still running its last CTAs; they block
+// in chain_wait() -- the first statement of every such kernel, before ANY global access -- until that
+// kernel has finished and its writes are visible, and let the next kernel's CTAs in behind them with
+// chain_release().  Off (sl_set_chained_launches(0)) the same kernels are launched plainly and both
+// calls are no-ops.
+bool chained_launches_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void chain_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void chain_release() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_chained(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream,
+                                  Args&&... args)
+{
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = chained_launches_enabled() ? 1 : 0;
+    return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+#endif
 
 // --------------------------------------------------------------- small maths
 struct f3 { float x, y, z; };

@@ -223,6 +223,8 @@ preprocess_kernel(int P, int D, int M, int C,
                   uint32_t* __restrict__ tiles_touched,
                   uint32_t* __restrict__ tile_counts)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     constexpr uint32_t SOLO_MAX = 8;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
@@ -280,7 +282,7 @@ int launch_preprocess(int P, int D, int M, int C, const float* means3D, const fl
 {
     const dim3 grid(ceil_div(P, PREPROCESS_THREADS), vp.views);
 #define SL_LAUNCH_PRE(RR, SD)                                                                                     \
-    preprocess_kernel<RR><<<grid, PREPROCESS_THREADS, 0, stream>>>(                                               \
+    launch_chained(preprocess_kernel<RR>, grid, dim3(PREPROCESS_THREADS), 0, stream,                              \
         P, D, M, C, means3D, scales, rotations, opacities, shs, cov3D_precomp, tile_mask,                         \
         colors_precomp, viewmatrices, projmatrices, cam_positions, vp, prefiltered, SD, radii, g.means2D, g.depths, \
         g.cov3D, g.rgb, g.clamped, g.conic_opacity, g.tiles_touched, tile_counts)

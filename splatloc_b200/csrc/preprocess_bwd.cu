@@ -296,6 +296,8 @@ preprocess_backward_kernel(int P, int D, int M, int C,
                            float* __restrict__ dL_dopacity, float* __restrict__ dL_dfdc, float* __restrict__ dL_dkp,
                            float* push_mc)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     __shared__ float s_pose[8][6];
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -448,7 +450,7 @@ int launch_preprocess_backward(int P, int D, int M, int C, const float* means3D,
     const int scale_dim = raw != nullptr ? raw->scale_dim : 3;
     const size_t smem = push_mc != nullptr ? (size_t)256 * (EXCHANGE_ROW + 1) * sizeof(float) : 0;
 #define SL_LAUNCH_PBWD(MM, RR)                                                                                   \
-    preprocess_backward_kernel<MM, RR><<<ceil_div(P, 256), 256, smem, stream>>>(                                 \
+    launch_chained(preprocess_backward_kernel<MM, RR>, dim3(ceil_div(P, 256)), dim3(256), smem, stream,          \
         P, D, M, C, means3D, radii, shs, clamped, scales, rotations, cov3D, viewmatrices, projmatrices,         \
         cam_positions, vp, dL_dmean2D, dL_dconic, dL_dmean3D, dL_dcolor, color_view_stride, dL_ddepth, dL_dcov3D, \
         dL_dsh, dL_dscale, dL_drot, dL_dtau, scale_dim, raw_opacities, features_dc, dL_dopacity, dL_dfdc, dL_dkp, \

@@ -34,6 +34,8 @@ tile_scan_kernel(uint32_t* tile_counts, uint2* __restrict__ ranges, uint32_t* __
                  uint32_t* __restrict__ large_tiles, BinInfo* __restrict__ info, int n_tiles,
                  uint32_t max_pairs, uint32_t max_tile_pairs, int* status)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     constexpr int NT = 1024;
     __shared__ uint32_t s_warp[32];
     __shared__ uint32_t s_hist[NT];
@@ -135,6 +137,8 @@ scatter_pairs_kernel(int P, const float2* __restrict__ means2D, const float* __r
                      const uint2* __restrict__ ranges, uint32_t* cursors,
                      uint64_t* __restrict__ keys, uint32_t* __restrict__ vals, const BinInfo* __restrict__ info)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     constexpr uint32_t SOLO_MAX = 8;
     if (info->overflow) return;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -312,6 +316,8 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
                  size_t feature_view_stride, const float* __restrict__ kp,
                  PairRecord* __restrict__ records, uint8_t* __restrict__ masks, const BinInfo* __restrict__ dev_info)
 {
+    chain_wait();        // launched with launch_chained(): nothing before the previous stage is complete
+    chain_release();
     extern __shared__ __align__(16) unsigned long long s_key[];
     if (dev_info->overflow) return;
     // n_listed < 0: the host does not know how long the work list is (no read-back): the device does.
@@ -342,7 +348,7 @@ tile_sort_kernel(const uint2* __restrict__ ranges, const uint32_t* __restrict__ 
 int launch_tile_scan(uint32_t* tile_counts, uint2* ranges, uint32_t* tile_order, uint32_t* large_tiles, BinInfo* info,
                      int n_tiles, uint32_t max_pairs, uint32_t max_tile_pairs, int* status, cudaStream_t stream)
 {
-    tile_scan_kernel<<<1, 1024, 0, stream>>>(tile_counts, ranges, tile_order, large_tiles, info, n_tiles, max_pairs,
+    launch_chained(tile_scan_kernel, dim3(1), dim3(1024), 0, stream, tile_counts, ranges, tile_order, large_tiles, info, n_tiles, max_pairs,
                                              max_tile_pairs, status);
     count_launch();
     return 0;
@@ -353,7 +359,7 @@ int launch_scatter_pairs(int P, const GeomState& g, const int* radii, const uint
                          uint32_t* vals, const BinInfo* dev_info, cudaStream_t stream)
 {
     const dim3 grid(ceil_div(P, 256), vp.views);
-    scatter_pairs_kernel<<<grid, 256, 0, stream>>>(P, g.means2D, g.depths, g.tiles_touched, radii, tile_mask,
+    launch_chained(scatter_pairs_kernel, grid, dim3(256), 0, stream, P, g.means2D, g.depths, g.tiles_touched, radii, tile_mask,
                                                    vp.grid_x, vp.grid_y, vp.tiles, ranges, cursors, keys, vals,
                                                    dev_info);
     count_launch();
@@ -379,7 +385,7 @@ static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const
         SL_CUDA(cudaFuncSetAttribute(tile_sort_kernel<C, T, RAW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem),
                 "tile sort smem attribute");
         const int listed = n_large_launch < 0 ? n_tiles : n_large_launch;
-        tile_sort_kernel<C, T, RAW><<<listed < 148 ? listed : 148, T, smem, stream>>>(
+        launch_chained(tile_sort_kernel<C, T, RAW>, dim3(listed < 148 ? listed : 148), dim3(T), smem, stream,
             ranges, large_tiles, n_large_launch < 0 ? -1 : n_large_launch, vp.grid_x, vp.tiles, P,
             (uint32_t)TILE_SORT_SMALL, keys_in, vals_in, keys_out, point_list, g.means2D, g.depths, g.conic_opacity,
             features, feature_view_stride, kp, records, masks, dev_info);
@@ -390,7 +396,7 @@ static int tile_sort_launches(int P, uint32_t longest, int n_large_launch, const
     if (longest > (uint32_t)TILE_SORT_SMALL) longest = (uint32_t)TILE_SORT_SMALL;
     uint32_t pad = T;
     while (pad < longest) pad <<= 1;
-    tile_sort_kernel<C, T, RAW><<<n_tiles, T, (size_t)pad * sizeof(unsigned long long), stream>>>(
+    launch_chained(tile_sort_kernel<C, T, RAW>, dim3(n_tiles), dim3(T), (size_t)pad * sizeof(unsigned long long), stream,
         ranges, tile_order, n_tiles, vp.grid_x, vp.tiles, P, 0u, keys_in, vals_in, keys_out, point_list, g.means2D,
         g.depths, g.conic_opacity, features, feature_view_stride, kp, records, masks, dev_info);
     count_launch();
