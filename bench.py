@@ -890,6 +890,28 @@ def sub_sweep(job, args, impl, points=(100_000, 200_000, 500_000, 1_200_000, 3_0
     return rows
 
 
+def sub_knn(job, args, impl, points=(200_000, 1_200_000, 5_000_000)):
+    """SURVEY 8(d) metric (iii): distCUDA2 (simple_knn: mean squared distance to the 3 nearest neighbours,
+    reference: simple_knn.cu:186-221) wall time and Mpoints/s on seeded point clouds, N = 1; device-resident
+    points, CUDA events, L2 flushed between calls.  32 algorithmic bytes per point (read xyz, write one float,
+    one key/value sort in and out)."""
+    be, _, _ = load_backend(impl)
+    rows = []
+    for P in points:
+        pts = scenes.make_knn_points(P, seed=P % 7).to(job.dev)
+        out = {}
+
+        def call(i):
+            out["d"] = be.distCUDA2(pts)
+        ms, _, _ = job.timed(call, 10, 3)
+        t = ms / 10
+        rows.append({"points": P, "ms": round(t, 4), "Mpoints_per_s": round(P / (t * 1e-3) / 1e6, 1),
+                     "GBps_algorithmic": round(32 * P / (t * 1e-3) / 1e9, 1), "mean_dist2": float(out["d"].mean())})
+        del pts
+        torch.cuda.empty_cache()
+    return rows
+
+
 def sub_mapping_iteration(job, args, sc):
     """SURVEY 8(f) rows 1 and 4 on the config-2 scene, one view, eager calls through the drop-in API: the
     reference's mapping iteration around the rasterizer -- render() with its PyTorch pre-processing,
@@ -1069,7 +1091,7 @@ def main():
     ap.add_argument("--workload", choices=["train_step", "pose_refine", "mapping_loss"], default="train_step")
     ap.add_argument("--frames", type=int, default=8, help="pose_refine: query frames per GPU (one launch renders them all)")
     ap.add_argument("--sub", default="all",
-                    help="sub-records of the default line: all, none, or a comma list of sweep,pose_refine,multiview,train_window")
+                    help="sub-records of the default line: all, none, or a comma list of sweep,pose_refine,multiview,train_window,mapping_iteration,knn")
     args = ap.parse_args()
     claim_stdout()
     args.warmup = max(args.warmup, 3)
@@ -1111,7 +1133,7 @@ def main():
         if job.rank == 0:
             print(json.dumps({name: out[name]}), file=sys.stderr, flush=True)
     note("value")
-    subs = {"sweep", "pose_refine", "multiview", "train_window", "mapping_iteration"} if args.sub == "all" else \
+    subs = {"sweep", "pose_refine", "multiview", "train_window", "mapping_iteration", "knn"} if args.sub == "all" else \
         (set() if args.sub == "none" else set(args.sub.split(",")))
     if args.points != P_DEFAULT:
         subs = set()
@@ -1135,6 +1157,8 @@ def main():
     torch.cuda.empty_cache()
     if "sweep" in subs and job.world == 1:
         out["sweep"] = sub_sweep(job, args, args.impl)
+    if "knn" in subs and job.world == 1:
+        out["knn"] = sub_knn(job, args, args.impl)
     if args.impl == "ours" and job.rank == 0 and job.world == 1 and not args.no_cpu_baseline:   # rank 0 at N = 1 only
         out["cpu_baseline"] = cpu_baseline(budget_s=args.cpu_budget)
     if job.rank == 0:
