@@ -938,34 +938,65 @@ def sub_mapping_iteration(job, args, sc):
     bg = torch.zeros(3, device=dev)
     gt = torch.rand(3, cams[0].H, cams[0].W, device=dev)
     steps, out = max(8, args.steps // 2), {}
-    for mode in ("reference_shaped", "fused"):
-        pc = types.SimpleNamespace(active_sh_degree=0, max_sh_degree=0, _features_rest=torch.zeros((P, 0, 3), device=dev))
-        for k, t in raw.items():
-            setattr(pc, k, t.clone().requires_grad_(True))
-        params = {n: getattr(pc, k) for n, k in key.items()}
-        if mode == "fused":
-            opt = GaussianStoreOptimizer({n: t for n, t in params.items()}, lrs)
-            for n, k in key.items():            # the optimiser updates these tensors in place
-                setattr(pc, k, opt.params[n].requires_grad_(True))
-            params = {n: getattr(pc, k) for n, k in key.items()}
-        else:
-            topt = torch.optim.Adam([{"params": [t], "lr": lrs[n], "name": n} for n, t in params.items()], lr=0.0, eps=1e-15)
 
-        def it(i):
-            pkg = render(views[i % 4], pc, pipe, bg, fuse=mode == "fused")
-            loss = (pkg["render"] - gt).abs().mean() + pkg["kp_prob"].mean() + 0.1 * pkg["depth"].mean()
-            loss.backward()
+    # the colour-refinement loop's loss (train_gaussians.py:283-286): PyTorch formulation of loss_utils.py:61-102
+    # (five depth-wise 11 x 11 convolutions) against the fused kernel pair (sl_ssim_forward / sl_ssim_backward)
+    import torch.nn.functional as F
+    from splatloc_b200.ssim_loss import gaussian_window, l1_ssim_loss
+    w1 = gaussian_window().to(dev)
+    w2 = (w1[:, None] @ w1[None, :]).expand(3, 1, 11, 11).contiguous()
+
+    def torch_l1_ssim(x, y, lam=0.2):
+        conv = lambda t: F.conv2d(t[None], w2, padding=5, groups=3)[0]      # noqa: E731
+        mu1, mu2 = conv(x), conv(y)
+        s1, s2, s12 = conv(x * x) - mu1 * mu1, conv(y * y) - mu2 * mu2, conv(x * y) - mu1 * mu2
+        m = ((2 * mu1 * mu2 + 1e-4) * (2 * s12 + 9e-4)) / ((mu1 * mu1 + mu2 * mu2 + 1e-4) * (s1 + s2 + 9e-4))
+        return (1.0 - lam) * (x - y).abs().mean() + lam * (1.0 - m.mean())
+
+    losses = {"mapping": {m: (lambda pkg: (pkg["render"] - gt).abs().mean() + pkg["kp_prob"].mean() + 0.1 * pkg["depth"].mean())
+                          for m in ("reference_shaped", "fused")},
+              "refinement": {"reference_shaped": lambda pkg: torch_l1_ssim(pkg["render"], gt),
+                             "fused": lambda pkg: l1_ssim_loss(pkg["render"], gt, 0.2)}}
+    for kind, prefix in (("mapping", ""), ("refinement", "refinement_")):
+        for mode in ("reference_shaped", "fused"):
+            pc = types.SimpleNamespace(active_sh_degree=0, max_sh_degree=0, _features_rest=torch.zeros((P, 0, 3), device=dev))
+            for k, t in raw.items():
+                setattr(pc, k, t.clone().requires_grad_(True))
+            params = {n: getattr(pc, k) for n, k in key.items()}
             if mode == "fused":
-                opt.step({n: t.grad for n, t in params.items()})
-                for t in params.values():
-                    t.grad = None
+                opt = GaussianStoreOptimizer({n: t for n, t in params.items()}, lrs)
+                for n, k in key.items():            # the optimiser updates these tensors in place
+                    setattr(pc, k, opt.params[n].requires_grad_(True))
+                params = {n: getattr(pc, k) for n, k in key.items()}
             else:
-                topt.step()
-                topt.zero_grad(set_to_none=True)
-        ms, _, _ = job.timed(it, steps, 5)
-        out[mode + "_ms_per_iteration"] = round(ms / steps, 4)
+                topt = torch.optim.Adam([{"params": [t], "lr": lrs[n], "name": n} for n, t in params.items()], lr=0.0, eps=1e-15)
+            loss_fn = losses[kind][mode]
+
+            def it(i):
+                pkg = render(views[i % 4], pc, pipe, bg, fuse=mode == "fused")
+                loss_fn(pkg).backward()
+                if mode == "fused":
+                    opt.step({n: t.grad for n, t in params.items() if t.grad is not None})
+                    for t in params.values():
+                        t.grad = None
+                else:
+                    topt.step()
+                    topt.zero_grad(set_to_none=True)
+            ms, _, _ = job.timed(it, steps, 5)
+            out[prefix + mode + "_ms_per_iteration"] = round(ms / steps, 4)
+
+    # the loss alone, forward + backward on a (3, H, W) image
+    img = torch.rand(3, cams[0].H, cams[0].W, device=dev)
+    for name, fn in (("torch_ops", torch_l1_ssim), ("fused", lambda x, y: l1_ssim_loss(x, y, 0.2))):
+        def it_loss(i):
+            x = img.detach().requires_grad_(True)
+            fn(x, gt).backward()
+        ms, _, _ = job.timed(it_loss, steps, 5)
+        out["l1_ssim_loss_" + name + "_ms"] = round(ms / steps, 4)
     out["note"] = ("render + loss + backward + Adam, eager; reference_shaped = render()'s PyTorch pre-processing "
-                   "(gaussian_renderer/__init__.py:73-102) and torch.optim.Adam around this library's rasterizer")
+                   "(gaussian_renderer/__init__.py:73-102), the loss as PyTorch ops and torch.optim.Adam around this library's "
+                   "rasterizer; refinement_* = the colour-refinement iteration (train_gaussians.py:270-295) with the "
+                   "(1 - 0.2) L1 + 0.2 (1 - SSIM) loss; l1_ssim_loss_*: that loss alone, forward + backward")
     return out
 
 

@@ -445,6 +445,27 @@ int sl_mapping_loss(int width, int height, int channels, const float* image, con
                     const float* exposure_b, float rgb_boundary_threshold, int initialization, float* dL_dimage,
                     float* dL_ddepth, float* out, void* workspace, void* stream);
 
+/* ---- SSIM + L1 photometric loss (SSIM variant) ---------------------------
+ * The loss of SplatLoc's colour-refinement loop (train_gaussians.py:283-286),
+ *   loss = (1 - lambda_dssim) * l1_loss(image, gt) + lambda_dssim * (1 - ssim(image, gt)),
+ * with ssim as gaussian_splatting/utils/loss_utils.py:61-102 computes it: depth-wise 11 x 11 Gaussian
+ * window (sigma 1.5, the outer product of `window11`, the 11 normalised 1-D taps, HOST memory), zero
+ * padding, C1 = 0.01^2, C2 = 0.03^2, mean over all channels * H * W elements.
+ * sl_ssim_forward: img1, img2 (channels, H, W) on the device -> out[2] (device) = {mean ssim,
+ *   mean |img1 - img2|}, and `maps` (3 * channels * H * W floats, device): the partial derivatives of the
+ *   SSIM map the backward filters.  workspace: sl_ssim_workspace_bytes() bytes, no initialisation needed.
+ * sl_ssim_backward: dL_dimg1 = upstream * (scale_ssim * d(sum of the ssim map)/d img1
+ *                                          + scale_l1 * sign(img1 - img2));
+ *   `upstream`: device pointer to one float (NULL = 1).  For the loss above with means:
+ *   scale_ssim = -lambda / (channels * H * W), scale_l1 = (1 - lambda) / (channels * H * W).
+ * Sums are accumulated in double in a fixed order: results are run-to-run identical. */
+size_t sl_ssim_workspace_bytes(int width, int height, int channels);
+int sl_ssim_forward(int width, int height, int channels, const float* img1, const float* img2,
+                    const float* window11, float* maps, float* out, void* workspace, void* stream);
+int sl_ssim_backward(int width, int height, int channels, const float* img1, const float* img2,
+                     const float* window11, const float* maps, const float* upstream, float scale_ssim,
+                     float scale_l1, float* dL_dimg1, void* stream);
+
 /* ---- instrumentation (no counterpart in the reference, which has no tracing,
  * SURVEY.md section 5) ------------------------------------------------------ */
 

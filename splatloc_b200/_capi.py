@@ -126,6 +126,10 @@ SIGNATURES = {
         _F, _F, _F, _F,                              # dL_dsh, dL_dscale, dL_drot, dL_dtau
         C.c_int, C.c_void_p,                         # debug, stream
     ]),
+    "sl_ssim_workspace_bytes": (C.c_size_t, [C.c_int, C.c_int, C.c_int]),
+    "sl_ssim_forward": (C.c_int, [C.c_int, C.c_int, C.c_int, _F, _F, C.POINTER(C.c_float), _F, _F, _F, C.c_void_p]),
+    "sl_ssim_backward": (C.c_int, [C.c_int, C.c_int, C.c_int, _F, _F, C.POINTER(C.c_float), _F, _F, C.c_float, C.c_float,
+                                   _F, C.c_void_p]),
     "sl_exchange_arrive": (C.c_int, [_F, C.c_int, C.c_void_p]),                    # flags_multicast, rank, stream
     "sl_exchange_wait": (C.c_int, [_F, C.c_int, _F, C.c_int, C.c_int, C.c_int, _F, C.c_void_p]),  # flags, world, waits, ahead, advance, timeout_ms, status, stream
     "sl_exchange_push": (C.c_int, [_F, C.c_int, C.c_int, _F, C.c_int, C.c_void_p]),   # source (device), P, C, exchange_multicast, max_ctas, stream

@@ -169,6 +169,48 @@ int sl_mapping_loss(int width, int height, int channels, const float* image, con
     return check_stage(false, stream, "mapping loss");
 }
 
+size_t sl_ssim_workspace_bytes(int width, int height, int channels)
+{
+    return (width > 0 && height > 0 && channels > 0) ? ssim_workspace_bytes(width, height, channels) : 0;
+}
+
+static int check_ssim_shape(const char* who, int width, int height, int channels)
+{
+    g_error[0] = 0;
+    if (width <= 0 || height <= 0 || channels <= 0 || channels > 65535) {
+        set_error("%s: bad image shape (%d, %d, %d)", who, channels, height, width);
+        return SL_ERR_ARGUMENT;
+    }
+    return 0;
+}
+
+int sl_ssim_forward(int width, int height, int channels, const float* img1, const float* img2, const float* window11,
+                    float* maps, float* out, void* workspace, void* stream_)
+{
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (int rc = check_ssim_shape("sl_ssim_forward", width, height, channels)) return rc;
+    if (!img1 || !img2 || !window11 || !maps || !out || !workspace) {
+        set_error("sl_ssim_forward: null pointer argument");
+        return SL_ERR_ARGUMENT;
+    }
+    launch_ssim_forward(width, height, channels, img1, img2, window11, maps, out, static_cast<char*>(workspace), stream);
+    return check_stage(false, stream, "ssim forward");
+}
+
+int sl_ssim_backward(int width, int height, int channels, const float* img1, const float* img2, const float* window11,
+                     const float* maps, const float* upstream, float scale_ssim, float scale_l1, float* dL_dimg1,
+                     void* stream_)
+{
+    cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+    if (int rc = check_ssim_shape("sl_ssim_backward", width, height, channels)) return rc;
+    if (!img1 || !img2 || !window11 || !maps || !dL_dimg1) {
+        set_error("sl_ssim_backward: null pointer argument");
+        return SL_ERR_ARGUMENT;
+    }
+    launch_ssim_backward(width, height, channels, img1, img2, window11, maps, upstream, scale_ssim, scale_l1, dL_dimg1, stream);
+    return check_stage(false, stream, "ssim backward");
+}
+
 long long sl_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 void sl_profile_enable(int on)

@@ -124,6 +124,17 @@ int launch_mapping_loss(int W, int H, int C, const float* image, const float* de
                         float rgb_threshold, bool initialization, float* dL_dimage, float* dL_ddepth, float* out,
                         char* workspace, cudaStream_t stream);
 
+// SURVEY 8(f) row 2, SSIM variant: (1 - lambda) L1 + lambda (1 - SSIM) of the colour-refinement loop
+// (reference: gaussian_splatting/utils/loss_utils.py:61-102, train_gaussians.py:283-286); ssim_loss.cu.
+// `window11`: the 11 taps of the 1-D Gaussian window, in HOST memory.  maps: [3, C, H, W] partial derivatives
+// of the SSIM map kept for the backward; out: {mean ssim, mean |img1 - img2|} on the device.
+size_t ssim_workspace_bytes(int W, int H, int C);
+int launch_ssim_forward(int W, int H, int C, const float* img1, const float* img2, const float* window11, float* maps,
+                        float* out, char* workspace, cudaStream_t stream);
+int launch_ssim_backward(int W, int H, int C, const float* img1, const float* img2, const float* window11,
+                         const float* maps, const float* upstream, float scale_ssim, float scale_l1, float* dL_dimg1,
+                         cudaStream_t stream);
+
 // ---- optimiser step and densification over the Gaussian store (optimizer.cu;
 // reference: gaussian_splatting/scene/gaussian_model.py:250-300, 493-679).
 constexpr int STORE_MAX_GROUPS = 8;      // xyz, f_dc, f_rest, opacity, marker, kp_score, scaling, rotation
