@@ -734,9 +734,12 @@ def _window_cameras(job, n, seed0, dev, **kw):
             torch.stack([c.campos for c in cams]), cams[0])
 
 
-def _graphed_window(job, sc, V, W, H, cam_sets, steps, warmup, exchange=None):
+def _graphed_window(job, sc, V, W, H, cam_sets, steps, warmup, exchange=None, push_exchange=False):
     """fwd+bwd of V views per replay (batch entry points inside one CUDA graph), cycling over `cam_sets`;
-    returns (ms per window: max over ranks, pairs of the first window, kernels per replay)."""
+    returns (ms per window: max over ranks, pairs of the first window, kernels per replay).
+    `exchange`: called on the trainable gradients after every replay (NCCL).  `push_exchange`: instead, two
+    alternating steps whose rows leave through sl_exchange_push beside the next window's forward
+    (splatloc_b200.exchange, GraphedViewStep exchange_mode="next_step"); the last push and wait are timed."""
     from splatloc_b200 import _C
     from splatloc_b200.graphs import GraphedViewStep
     dev, C = job.dev, int(sc["colors_precomp"].shape[1])
@@ -748,24 +751,42 @@ def _graphed_window(job, sc, V, W, H, cam_sets, steps, warmup, exchange=None):
                                                sc["rotations"], 1.0, EMPTY, EMPTY.bool(), vm, pm, c0.tanfovx, c0.tanfovy,
                                                H, W, EMPTY, 0, cp, False, False)[0])
     params = {k: sc[k].clone().requires_grad_(True) for k in ("means3D", "opacities", "colors_precomp", "scales", "rotations")}
-    step = GraphedViewStep(params, H, W, c0.tanfovx, c0.tanfovy, bg, max_pairs=int(1.25 * max(Rs)) + 4096, n_views=V)
+    xch = None
+    if push_exchange:
+        from splatloc_b200.exchange import NvlsGradientExchange
+        xch = NvlsGradientExchange(int(sc["means3D"].shape[0]), dev)
+        pair = [GraphedViewStep(params, H, W, c0.tanfovx, c0.tanfovy, bg, max_pairs=int(1.25 * max(Rs)) + 4096, n_views=V,
+                                exchange=xch, exchange_buffer=b, exchange_mode="next_step") for b in (0, 1)]
+        for st in pair:
+            st.bind_exchange_source()
+        xch.reset()
+        step = pair[0]
+    else:
+        step = GraphedViewStep(params, H, W, c0.tanfovx, c0.tanfovy, bg, max_pairs=int(1.25 * max(Rs)) + 4096, n_views=V)
     ups = [torch.cat([torch.stack([scenes.make_pixel_grads(7 * s + v, C, H, W)[k] for v in range(V)]).reshape(-1)
                       for k in range(3)]).to(dev) for s in range(len(cam_sets))]
 
-    def fn(i):
-        vm, pm, cp, _ = cam_sets[i % len(cam_sets)]
-        step.viewmatrices.copy_(vm)
-        step.projmatrices.copy_(pm)
-        step.cam_positions.copy_(cp)
-        step.upstream_flat.copy_(ups[i % len(cam_sets)])
-        step.replay()
-        if exchange is not None:
-            exchange(step.trainable_grads())
+    last = {"b": 0}
 
-    total, per, _ = job.timed(fn, steps, warmup)
+    def fn(i):
+        st = step if xch is None else pair[i % 2]
+        vm, pm, cp, _ = cam_sets[i % len(cam_sets)]
+        st.viewmatrices.copy_(vm)
+        st.projmatrices.copy_(pm)
+        st.cam_positions.copy_(cp)
+        st.upstream_flat.copy_(ups[i % len(cam_sets)])
+        st.replay()
+        last["b"] = i % 2
+        if exchange is not None:
+            exchange(st.trainable_grads())
+
+    total, per, _ = job.timed(fn, steps, warmup, after=(lambda: xch.flush_deferred(last["b"])) if xch is not None else None)
     assert int(step.overflow) == 0, "bench: pair capacity of the multi-view step exceeded"
+    if xch is not None:
+        assert int(pair[1].overflow) == 0 and not xch.timed_out, "bench: multi-view exchange overflow / timeout"
+        del pair
     k = step.kernels_per_replay
-    del step
+    del step, xch
     return total / steps, Rs[0], k
 
 
@@ -794,6 +815,22 @@ def sub_train_window(job, args):
     rec = {"workload": "multiview_window_3M_1296x968_c4", "gaussians": P, "image": [W, H], "views_per_gpu_per_exchange": V,
            "views_total": V * job.world, "ms_per_window": round(ms, 3), "Mpix_per_s": round(W * H * V * job.world / (ms * 1e-3) / 1e6, 1),
            "pairs_per_window": R, "exchange_bytes": trainable_grad_numel(P, 4, 0) * 4 if ex is not None else 0}
+    if job.dist is not None and not os.environ.get("BENCH_NO_FUSED_EXCHANGE"):
+        # the same window with this library's own exchange: visible rows pushed through the switch beside the next
+        # window's forward (the sums of window i are complete at the end of window i + 1); headline = the faster
+        ok = 1.0
+        try:
+            torch.cuda.empty_cache()
+            ms_push, _, _ = _graphed_window(job, sc, V, W, H, sets, max(4, args.steps // 4), 2, push_exchange=True)
+        except Exception as e:      # noqa: BLE001
+            ok, ms_push = 0.0, None
+            rec["push_exchange_error"] = f"{type(e).__name__}: {str(e)[:160]}"
+        if job.max_over_ranks(1.0 - ok) == 0.0:
+            rec["exchange"] = {"nccl_after_the_window_ms": round(ms, 3), "push_beside_next_forward_ms": round(ms_push, 3),
+                               "headline": "push_beside_next_forward" if ms_push < ms else "nccl_after_the_window"}
+            if ms_push < ms:
+                rec["ms_per_window"] = round(ms_push, 3)
+                rec["Mpix_per_s"] = round(W * H * V * job.world / (ms_push * 1e-3) / 1e6, 1)
     del sc
     torch.cuda.empty_cache()
     return rec
