@@ -136,6 +136,28 @@ def test_bulk_copy_record_stream_gives_the_same_frame(case):
         assert torch.equal(a[k], b[k]), k
 
 
+@pytest.mark.parametrize("case", [CASES[2], CASES[4], dict(P=200000, seed=1)],
+                         ids=lambda c: "-".join(f"{k}{v}" for k, v in c.items() if k != "bg"))
+def test_chained_launches_do_not_change_results(case):
+    """sl_set_chained_launches: with programmatic dependent launches every stage kernel may become resident
+    before the previous stage has finished and blocks on entry until it has; plain launches must give the
+    same frame, the same sorted lists, and gradients that differ by atomic ordering only."""
+    from splatloc_b200 import _capi
+    ours = _ours()
+    d = H.scene_inputs(**case)
+    a = H.run_backend(ours, d)
+    _capi.load().sl_set_chained_launches(0)
+    try:
+        b = H.run_backend(ours, d)
+    finally:
+        _capi.load().sl_set_chained_launches(1)
+    for k in ("color", "depth", "alpha", "n_contrib", "radii", "point_list", "point_list_keys", "ranges"):
+        if k in a:
+            assert torch.equal(a[k], b[k]), k
+    assert a["R"] == b["R"]
+    assert not H.compare(a, b)
+
+
 def test_empty_and_invisible():
     ours = _ours()
     # P == 0 -> zero outputs, R == 0
