@@ -243,7 +243,7 @@ int sl_backward_batch(int n_views, int P, int D, int M, int R, int C,
  * SURVEY.md 8(e) "phase 2").  `exchange_multicast` is a MULTICAST device address (NVSwitch / NVLS; e.g.
  * torch.distributed._symmetric_memory's `multicast_ptr`) of an exchange buffer of [P, 16] floats that
  * exists on every GPU of the job: every Gaussian this call saw adds its row
- *     {dL_dmean3D xyz, dL_dopacity | dL_dscale xyz, 1 | dL_drot wxyz | dL_dcolor c0..c3}
+ *     {dL_dmean3D xyz, dL_dopacity | dL_dscale xyz, n | dL_drot wxyz | dL_dcolor c0..c3}   (n: this call's views that saw it)
  * into ALL GPUs' buffers with multimem.red from the epilogue of the per-Gaussian backward, so after a
  * cross-GPU barrier every buffer holds the sum over all GPUs' views (float 7 of a row: in how many
  * views the Gaussian was visible).  The caller zeroes the buffers and places the barriers

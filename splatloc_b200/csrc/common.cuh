@@ -202,7 +202,7 @@ __device__ __forceinline__ float4 act_normalize(float4 q)
 // ---- multi-GPU gradient exchange fused into the per-Gaussian backward (csrc/preprocess_bwd.cu) ----
 // One row of EXCHANGE_ROW floats per Gaussian: {dL/dmean xyz, dL/dopacity | dL/dscale xyz, seen |
 // dL/drot wxyz | dL/dcolour c0..c3}; "seen" counts the views (over all GPUs) in which the Gaussian was
-// visible.  `mc` is a MULTICAST address (NVSwitch, NVLS) that maps the same row of every GPU's exchange
+// visible: every push adds the number of its own views that saw it.  `mc` is a MULTICAST address (NVSwitch, NVLS) that maps the same row of every GPU's exchange
 // buffer: one multimem.red adds the four floats into all of them inside the switch.
 constexpr int EXCHANGE_ROW = 16;
 __device__ __forceinline__ void multimem_red_add_v4(float* mc, float a, float b, float c, float d)

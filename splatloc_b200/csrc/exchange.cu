@@ -60,7 +60,7 @@ __global__ void exchange_wait_kernel(const uint32_t* flags, int world, uint32_t*
 // epilogue.  `src` lives in DEVICE memory so that a captured launch can be bound later to gradient
 // arrays that did not exist at capture time; src->radii == nullptr: nothing to send.  Same rows and
 // the same 64-byte staging as preprocess_bwd.cu: a Gaussian that any of the `n_views` views saw
-// (radii [n_views, P]) adds {dL_dmean xyz, dL_dopacity | dL_dscale xyz, 1 | dL_drot | dL_dcolour}.
+// (radii [n_views, P]) adds {dL_dmean xyz, dL_dopacity | dL_dscale xyz, views that saw it | dL_drot | dL_dcolour}.
 __global__ void __launch_bounds__(256) exchange_push_kernel(const ExchangeSource* src, int P, int C, float* push_mc)
 {
     __shared__ __align__(16) float s_rows[256 * EXCHANGE_ROW];
@@ -72,9 +72,10 @@ __global__ void __launch_bounds__(256) exchange_push_kernel(const ExchangeSource
     float* mine = s_rows + (size_t)threadIdx.x * EXCHANGE_ROW;
     for (size_t base = (size_t)blockIdx.x * 256; base < (size_t)P; base += (size_t)gridDim.x * 256) {
         const size_t idx = base + threadIdx.x;
-        bool seen = false;
+        int n_seen = 0;                              // views in which this Gaussian was visible
         if (idx < (size_t)P)
-            for (int v = 0; v < s.n_views; ++v) seen |= s.radii[(size_t)v * P + idx] > 0;
+            for (int v = 0; v < s.n_views; ++v) n_seen += s.radii[(size_t)v * P + idx] > 0;
+        const bool seen = n_seen > 0;
         s_seen[threadIdx.x] = seen ? 1u : 0u;
         if (seen) {
             float sx, sy = 0.f, sz = 0.f, c3 = 0.f;
@@ -86,7 +87,7 @@ __global__ void __launch_bounds__(256) exchange_push_kernel(const ExchangeSource
             if (C == 4) c3 = s.dL_dcolor[idx * C + 3];
             reinterpret_cast<float4*>(mine)[0] = make_float4(s.dL_dmean3D[3 * idx], s.dL_dmean3D[3 * idx + 1],
                                                              s.dL_dmean3D[3 * idx + 2], s.dL_dopacity[idx]);
-            reinterpret_cast<float4*>(mine)[1] = make_float4(sx, sy, sz, 1.0f);
+            reinterpret_cast<float4*>(mine)[1] = make_float4(sx, sy, sz, (float)n_seen);
             reinterpret_cast<float4*>(mine)[2] = reinterpret_cast<const float4*>(s.dL_drot)[idx];
             reinterpret_cast<float4*>(mine)[3] = make_float4(s.dL_dcolor[idx * C], s.dL_dcolor[idx * C + 1],
                                                              s.dL_dcolor[idx * C + 2], c3);

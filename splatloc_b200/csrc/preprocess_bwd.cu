@@ -305,6 +305,7 @@ preprocess_backward_kernel(int P, int D, int M, int C,
     f3 g_mean = {0.f, 0.f, 0.f};
     float g_cov[6] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
     bool seen = false;
+    int n_seen = 0;                                  // views in which this Gaussian was visible
     const int n_views = MULTI ? vp.views : 1;
     for (int v = 0; v < n_views; ++v) {
         const size_t vP = (size_t)v * P;
@@ -316,6 +317,7 @@ preprocess_backward_kernel(int P, int D, int M, int C,
                                   dL_dmean2D + 3 * vP, dL_dconics + 4 * vP, dL_dcolor + v * color_view_stride,
                                   dL_ddepth + vP, dL_dsh, MULTI ? !seen : true, g_mean, g_cov, want_pose, pose);
             seen = true;
+            ++n_seen;
         }
         if (want_pose) {
             // 6 floats per view: warp shuffle, then shared memory across the 8 warps
@@ -419,7 +421,7 @@ preprocess_backward_kernel(int P, int D, int M, int C,
                 if (C == 4) c3 = dL_dcolor[idx * C + 3];
             }
             reinterpret_cast<float4*>(mine)[0] = make_float4(g_mean.x, g_mean.y, g_mean.z, dL_dopacity[idx]);
-            reinterpret_cast<float4*>(mine)[1] = make_float4(sx, sy, sz, 1.0f);
+            reinterpret_cast<float4*>(mine)[1] = make_float4(sx, sy, sz, (float)n_seen);
             reinterpret_cast<float4*>(mine)[2] = rq;
             reinterpret_cast<float4*>(mine)[3] = make_float4(c0, c1, c2, c3);
         }

@@ -26,3 +26,5 @@ def test_fused_exchange_equals_nccl_all_reduce_on_two_gpus():
     assert "split-phase exchange == NCCL all-reduce" in r.stdout
     # and with the rows sent by sl_exchange_push beside the next step's forward
     assert "deferred-push exchange == NCCL all-reduce" in r.stdout
+    # several views per GPU per step: summed gradients, and the rows' visibility slot counts views
+    assert "two views per GPU per step == NCCL all-reduce" in r.stdout

@@ -139,6 +139,56 @@ def main():
     if rank == 0:
         print(f"{world} ranks: deferred-push exchange == NCCL all-reduce over {n_steps} skewed steps (worst relative difference "
               f"{worst3:.2e}, visibility counts exact)", flush=True)
+    # two views per GPU per step (batch entry points): the rows' visibility slot counts VIEWS
+    def load2(st, i):
+        for v in range(2):
+            c = cams[(2 * i + v) % 4]
+            st.set_camera(c.viewmatrix, c.projmatrix, c.campos, view=v)
+        u = [ups[(2 * i + v) % 4] for v in range(2)]
+        st.upstream_color.copy_(torch.stack([x[:C] for x in u]))
+        st.upstream_depth.copy_(torch.stack([x[C:C + 1] for x in u]))
+        st.upstream_alpha.copy_(torch.stack([x[C + 1:] for x in u]))
+    plain2 = GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=5_000_000, n_views=2)
+    later2 = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=5_000_000, n_views=2, exchange=xch,
+                              exchange_buffer=b, exchange_mode="next_step", consume=lambda rows: snap2.copy_(rows)) for b in (0, 1)]
+    fused2 = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=5_000_000, n_views=2, exchange=xch,
+                              exchange_buffer=b, consume=lambda rows: snap.copy_(rows)) for b in (0, 1)]
+    refs2, seens2 = [], []
+    for i in range(3):
+        load2(plain2, i)
+        plain2.replay()
+        ref, seen = plain2.trainable_grads().clone(), (plain2.radii > 0).float().sum(0)
+        dist.all_reduce(ref); dist.all_reduce(seen)
+        refs2.append(ref); seens2.append(seen)
+    for name, pair, sn, flush in (("push in the backward", fused2, snap, lambda: xch.wait_all()),
+                                  ("push beside the next forward", later2, snap2, lambda: xch.flush_deferred(0))):
+        for st in pair:
+            if st.exchange_mode == "next_step":
+                st.bind_exchange_source()
+        xch.reset()
+        got2 = []
+        for i in range(3):
+            load2(pair[i % 2], i)
+            pair[i % 2].replay()
+            got2.append(sn.clone())
+        flush()
+        got2.append(xch.rows(0).clone())            # the last step (i = 2) used buffer 0
+        torch.cuda.synchronize()
+        assert not xch.timed_out
+        for i in range(3):
+            got = NvlsGradientExchange.unpack(got2[i + 1])
+            off = 0
+            for nm, w in (("means3D", 3), ("opacities", 1), ("scales", 3), ("rotations", 4), ("colors_precomp", C)):
+                n = (P * w + 3) // 4 * 4
+                want = refs2[i][off:off + P * w].view(P, w)
+                off += n
+                err = float((got[nm] - want).abs().max()); scale = float(want.abs().max())
+                assert err <= 2e-5 * 16 * scale, ("two views per step", name, i, nm, err, scale)
+            assert torch.equal(got["seen"], seens2[i]), ("two views per step: view counts", name, i)
+    if rank == 0:
+        print(f"{world} ranks: two views per GPU per step == NCCL all-reduce, view counts exact (both push forms)", flush=True)
+    del plain2, later2, fused2
+    torch.cuda.empty_cache()
     later_plain = [GraphedViewStep(params, H, W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000, exchange=xch,
                                    exchange_buffer=b, exchange_mode="next_step") for b in (0, 1)]
     xch.reset()
