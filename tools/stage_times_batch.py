@@ -5,7 +5,7 @@ import torch
 from splatloc_b200 import _C, _capi, scenes
 
 dev = torch.device("cuda", 0)
-P, C = 500_000, 4
+P, C = int(os.environ.get("STAGE_P", 500_000)), 4
 sc = {k: v.to(dev) for k, v in scenes.make_scene(P, seed=0, channels=C).items()}
 bg = torch.zeros(C, device=dev)
 E = torch.Tensor([])
