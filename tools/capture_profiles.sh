@@ -29,3 +29,18 @@ done
 tail -c 300 $out/${tag}_ncu_full.log
 head -c 400 $out/${tag}_plain_ours.json
 head -c 300 $out/${tag}_plain_ref.json
+# the fused L1 + SSIM loss at the bench image size (forward, reduce, backward)
+cat > /tmp/ssim_run.py <<'PY'
+import sys; sys.path.insert(0, ".")
+import torch
+from splatloc_b200.ssim_loss import l1_ssim_loss
+g = torch.Generator().manual_seed(0)
+gt = torch.rand((3, 480, 640), generator=g).cuda(); img = (gt + 0.05 * torch.randn((3, 480, 640), generator=g).cuda()).clamp(0, 1)
+for _ in range(3):
+    x = img.clone().requires_grad_(True); l1_ssim_loss(x, gt, 0.2).backward()
+torch.cuda.synchronize(); print("ok")
+PY
+python /tmp/ssim_run.py > $out/${tag}_ssim_plain.log 2>&1 &&
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:ssim_ -s 6 -c 3 -o /tmp/${tag}_full_ssim -f \
+    python /tmp/ssim_run.py > $out/${tag}_ncu_ssim.log 2>&1
+ncu -i /tmp/${tag}_full_ssim.ncu-rep --page raw --csv > $out/${tag}_full_ssim_raw.csv 2>/dev/null
