@@ -453,7 +453,8 @@ int sl_mapping_loss(int width, int height, int channels, const float* image, con
  * padding, C1 = 0.01^2, C2 = 0.03^2, mean over all channels * H * W elements.
  * sl_ssim_forward: img1, img2 (channels, H, W) on the device -> out[2] (device) = {mean ssim,
  *   mean |img1 - img2|}, and `maps` (3 * channels * H * W floats, device): the partial derivatives of the
- *   SSIM map the backward filters.  workspace: sl_ssim_workspace_bytes() bytes, no initialisation needed.
+ *   SSIM map the backward filters.  workspace: sl_ssim_workspace_bytes() bytes, its first 16 bytes zero
+ *   before the first use (the kernel leaves them zero); one per concurrently running call.
  * sl_ssim_backward: dL_dimg1 = upstream * (scale_ssim * d(sum of the ssim map)/d img1
  *                                          + scale_l1 * sign(img1 - img2));
  *   `upstream`: device pointer to one float (NULL = 1).  For the loss above with means:

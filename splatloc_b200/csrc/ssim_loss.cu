@@ -10,7 +10,8 @@
 // mirror of all of them per iteration.  Here one kernel reads a 26 x 26 halo tile of both images per
 // 16 x 16 output tile into shared memory, filters {x, y, x^2, y^2, xy} separably (the window is an outer
 // product, loss_utils.py:48-58), forms the SSIM map and the three partial-derivative maps a backward needs,
-// and reduces SSIM and L1 sums deterministically; a second kernel filters the derivative maps with the
+// and reduces SSIM and L1 sums deterministically (one partial per CTA, summed in a fixed order by the last CTA to
+// finish); a second kernel filters the derivative maps with the
 // same window and writes d loss / d image.
 //
 // With  mu1 = w*x, mu2 = w*y, s11 = w*x^2, s22 = w*y^2, s12 = w*xy  (w* = window filter),
@@ -42,13 +43,16 @@ __device__ __forceinline__ float load_or_zero(const float* __restrict__ img, int
 // grid: (tiles_x, tiles_y, C); block 16 x 16
 __global__ void __launch_bounds__(SS_T * SS_T)
 ssim_forward_kernel(int W, int H, const float* __restrict__ img1, const float* __restrict__ img2, Window11 win,
-                    float* __restrict__ maps, double* __restrict__ partial)
+                    float* __restrict__ maps, double* __restrict__ partial, unsigned int* ticket, double inv_n,
+                    float* __restrict__ out)
 {
     chain_wait();
     chain_release();
     __shared__ float s_x[SS_H][SS_H + 1], s_y[SS_H][SS_H + 1];
     __shared__ float s_h[5][SS_H][SS_T + 1];
     __shared__ double s_red[SS_T * SS_T / 32][2];
+    __shared__ double s_fin[SS_T * SS_T][2];
+    __shared__ bool s_last;
     const int tx = threadIdx.x, ty = threadIdx.y, tid = ty * SS_T + tx;
     const int x0 = blockIdx.x * SS_T, y0 = blockIdx.y * SS_T, c = blockIdx.z;
     const size_t plane = (size_t)W * H;
@@ -123,25 +127,29 @@ ssim_forward_kernel(int W, int H, const float* __restrict__ img1, const float* _
         const size_t blk = ((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x;
         partial[2 * blk] = sm;
         partial[2 * blk + 1] = sl;
+        __threadfence();
+        const unsigned int n_blocks = gridDim.x * gridDim.y * gridDim.z;
+        s_last = atomicAdd(ticket, 1u) == n_blocks - 1;
     }
-}
-
-// one CTA: fixed-order sum of the per-CTA partials -> out = {mean ssim, mean |img1 - img2|}
-__global__ void __launch_bounds__(256)
-ssim_reduce_kernel(int n_partials, const double* __restrict__ partial, double inv_n, float* __restrict__ out)
-{
-    chain_wait();
-    chain_release();
-    __shared__ double s[256][2];
-    double sm = 0.0, sl = 0.0;
-    for (int i = threadIdx.x; i < n_partials; i += 256) { sm += partial[2 * i]; sl += partial[2 * i + 1]; }
-    s[threadIdx.x][0] = sm; s[threadIdx.x][1] = sl;
     __syncthreads();
-    for (int o = 128; o > 0; o >>= 1) {
-        if ((int)threadIdx.x < o) { s[threadIdx.x][0] += s[threadIdx.x + o][0]; s[threadIdx.x][1] += s[threadIdx.x + o][1]; }
+    if (!s_last) return;
+    // the last CTA to finish sums the partials in a fixed order (thread-strided, then a tree): the means
+    // do not depend on which CTA that was
+    __threadfence();
+    const int n_partials = (int)(gridDim.x * gridDim.y * gridDim.z);
+    double sm = 0.0, sl = 0.0;
+    for (int i = tid; i < n_partials; i += SS_T * SS_T) { sm += partial[2 * i]; sl += partial[2 * i + 1]; }
+    s_fin[tid][0] = sm; s_fin[tid][1] = sl;
+    __syncthreads();
+    for (int o = SS_T * SS_T / 2; o > 0; o >>= 1) {
+        if (tid < o) { s_fin[tid][0] += s_fin[tid + o][0]; s_fin[tid][1] += s_fin[tid + o][1]; }
         __syncthreads();
     }
-    if (threadIdx.x == 0) { out[0] = (float)(s[0][0] * inv_n); out[1] = (float)(s[0][1] * inv_n); }
+    if (tid == 0) {
+        out[0] = (float)(s_fin[0][0] * inv_n);
+        out[1] = (float)(s_fin[0][1] * inv_n);
+        *ticket = 0u;                                   // ready for the next call
+    }
 }
 
 // d loss / d img1 = upstream * ( scale_ssim * d(sum m)/dx + scale_l1 * sign(x - y) )
@@ -200,7 +208,7 @@ ssim_backward_kernel(int W, int H, const float* __restrict__ img1, const float* 
 
 size_t ssim_workspace_bytes(int W, int H, int C)
 {
-    return (size_t)2 * sizeof(double) * ceil_div(W, SS_T) * ceil_div(H, SS_T) * C;
+    return 16 + (size_t)2 * sizeof(double) * ceil_div(W, SS_T) * ceil_div(H, SS_T) * C;    // ticket, then the partials
 }
 
 int launch_ssim_forward(int W, int H, int C, const float* img1, const float* img2, const float* window11, float* maps,
@@ -209,11 +217,9 @@ int launch_ssim_forward(int W, int H, int C, const float* img1, const float* img
     Window11 win;
     for (int k = 0; k < 11; ++k) win.w[k] = window11[k];
     const dim3 grid(ceil_div(W, SS_T), ceil_div(H, SS_T), C), block(SS_T, SS_T);
-    double* partial = reinterpret_cast<double*>(workspace);
-    launch_chained(ssim_forward_kernel, grid, block, 0, stream, W, H, img1, img2, win, maps, partial);
-    count_launch();
-    const int n_partials = (int)(grid.x * grid.y * grid.z);
-    launch_chained(ssim_reduce_kernel, dim3(1), dim3(256), 0, stream, n_partials, (const double*)partial,
+    unsigned int* ticket = reinterpret_cast<unsigned int*>(workspace);
+    double* partial = reinterpret_cast<double*>(workspace + 16);
+    launch_chained(ssim_forward_kernel, grid, block, 0, stream, W, H, img1, img2, win, maps, partial, ticket,
                    1.0 / ((double)W * H * C), out);
     count_launch();
     return 0;

@@ -33,6 +33,19 @@ def gaussian_window(window_size: int = 11, sigma: float = 1.5) -> torch.Tensor:
 _WINDOW = (ctypes.c_float * 11)(*[float(v) for v in gaussian_window()])
 
 
+_workspaces: dict = {}
+
+
+def _workspace(dev: torch.device, nbytes: int) -> torch.Tensor:
+    """One scratch block per (device, stream), zeroed once (the kernel leaves its ticket zero): calls on one
+    stream are ordered."""
+    key = (dev.index, torch.cuda.current_stream(dev).cuda_stream)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = _workspaces[key] = torch.zeros(nbytes, dtype=torch.uint8, device=dev)
+    return ws
+
+
 def _as_f32(t: torch.Tensor, name: str) -> torch.Tensor:
     if not t.is_cuda:
         raise RuntimeError(f"{name} must be a CUDA tensor (the SSIM loss has no CPU path)")
@@ -60,7 +73,7 @@ class _L1Ssim(torch.autograd.Function):
         with _on_device(dev):
             maps = torch.empty((3, C, H, W), dtype=torch.float32, device=dev)
             out = torch.empty(2, dtype=torch.float32, device=dev)
-            ws = torch.empty(int(lib.sl_ssim_workspace_bytes(W, H, C)), dtype=torch.uint8, device=dev)
+            ws = _workspace(dev, int(lib.sl_ssim_workspace_bytes(W, H, C)))
             _capi.check(lib.sl_ssim_forward(W, H, C, a.data_ptr(), b.data_ptr(), _WINDOW, maps.data_ptr(), out.data_ptr(),
                                             ws.data_ptr(), _stream(dev)))
         ctx.save_for_backward(a, b, maps)
