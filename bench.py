@@ -1022,6 +1022,23 @@ def sub_mapping_iteration(job, args, sc):
             ms, _, _ = job.timed(it, steps, 5)
             out[prefix + mode + "_ms_per_iteration"] = round(ms / steps, 4)
 
+    # the refinement iteration replayed as ONE CUDA graph (render without read-back, loss, backward, Adam with the
+    # step count on the device): splatloc_b200.graphs.GraphedRefinementIteration
+    from splatloc_b200.graphs import GraphedRefinementIteration
+    opt = GaussianStoreOptimizer({n: raw[k].clone() for n, k in key.items()}, lrs)
+    git = GraphedRefinementIteration(opt, cams[0].H, cams[0].W, cams[0].tanfovx, cams[0].tanfovy, bg, max_pairs=2_500_000,
+                                     lambda_dssim=0.2)
+
+    def it_graph(i):
+        c = cams[i % 4]
+        git.set_view(c.viewmatrix, c.projmatrix, c.campos, gt)
+        git.replay()
+    ms, _, _ = job.timed(it_graph, steps, 5)
+    assert int(git.overflow) == 0
+    out["refinement_graphed_ms_per_iteration"] = round(ms / steps, 4)
+    out["refinement_graphed_kernels_per_replay"] = git.kernels_per_replay
+    del git, opt
+
     # the loss alone, forward + backward on a (3, H, W) image
     img = torch.rand(3, cams[0].H, cams[0].W, device=dev)
     for name, fn in (("torch_ops", torch_l1_ssim), ("fused", lambda x, y: l1_ssim_loss(x, y, 0.2))):
@@ -1033,7 +1050,8 @@ def sub_mapping_iteration(job, args, sc):
     out["note"] = ("render + loss + backward + Adam, eager; reference_shaped = render()'s PyTorch pre-processing "
                    "(gaussian_renderer/__init__.py:73-102), the loss as PyTorch ops and torch.optim.Adam around this library's "
                    "rasterizer; refinement_* = the colour-refinement iteration (train_gaussians.py:270-295) with the "
-                   "(1 - 0.2) L1 + 0.2 (1 - SSIM) loss; l1_ssim_loss_*: that loss alone, forward + backward")
+                   "(1 - 0.2) L1 + 0.2 (1 - SSIM) loss, refinement_graphed = the same iteration replayed as one CUDA graph "
+                   "(GraphedRefinementIteration); l1_ssim_loss_*: that loss alone, forward + backward")
     return out
 
 

@@ -381,6 +381,11 @@ typedef struct {
 } sl_densify_group;
 int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, double beta1, double beta2, double eps,
                  const float* marker, float marker_threshold, void* stream);
+/* The same with the step count in DEVICE memory (one int, incremented by the call before the update reads
+ * it; zero before the first step): a launch captured in a CUDA graph cannot carry a new count per replay.
+ * The bias corrections are then formed on the device, in double. */
+int sl_adam_step_counted(int P, int n_groups, const sl_adam_group* groups, int* step_counter, double beta1, double beta2,
+                         double eps, const float* marker, float marker_threshold, void* stream);
 int sl_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,
                      float* denom, float* max_radii2D, void* stream);
 size_t sl_densify_scratch_bytes(int P);

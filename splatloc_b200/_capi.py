@@ -170,6 +170,8 @@ SIGNATURES = {
     ]),
     "sl_adam_step": (C.c_int, [C.c_int, C.c_int, C.POINTER(AdamGroup), C.c_int, C.c_double, C.c_double, C.c_double,
                                _F, C.c_float, C.c_void_p]),
+    "sl_adam_step_counted": (C.c_int, [C.c_int, C.c_int, C.POINTER(AdamGroup), _F, C.c_double, C.c_double, C.c_double,
+                                       _F, C.c_float, C.c_void_p]),
     "sl_densify_stats": (C.c_int, [C.c_int, C.c_int, _F, _F, _F, _F, _F, C.c_void_p]),
     "sl_densify_scratch_bytes": (C.c_size_t, [C.c_int]),
     "sl_densify_plan": (C.c_int, [C.c_int, _F, _F, _F, C.c_int, _F, _F, C.c_float, C.c_float, C.c_float, C.c_float,

@@ -854,12 +854,13 @@ int sl_backward_render(int n_views, int P, int R, const float* background, int w
 }
 
 // ---- optimiser step and densification ---------------------------------------
-int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, double beta1, double beta2, double eps,
-                 const float* marker, float marker_threshold, void* stream_)
+static int adam_impl(const char* who, int P, int n_groups, const sl_adam_group* groups, int step, int* step_counter,
+                     double beta1, double beta2, double eps, const float* marker, float marker_threshold, void* stream_)
 {
     g_error[0] = 0;
-    if (P < 0 || n_groups < 0 || n_groups > STORE_MAX_GROUPS || step < 1 || (n_groups > 0 && groups == nullptr)) {
-        set_error("sl_adam_step: bad arguments (P=%d, groups=%d of at most %d, step=%d)", P, n_groups, STORE_MAX_GROUPS, step);
+    if (P < 0 || n_groups < 0 || n_groups > STORE_MAX_GROUPS || (step_counter == nullptr && step < 1) ||
+        (n_groups > 0 && groups == nullptr)) {
+        set_error("%s: bad arguments (P=%d, groups=%d of at most %d, step=%d)", who, P, n_groups, STORE_MAX_GROUPS, step);
         return SL_ERR_ARGUMENT;
     }
     if (P == 0 || n_groups == 0) return 0;
@@ -867,18 +868,19 @@ int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, dou
     a.n_groups = 0;
     // torch.optim.Adam forms these scalars in double and hands them to float32 tensor ops
     // (hence beta1, beta2, eps arrive as doubles: 1 - (double)0.999f is off by 1.3e-5 of itself)
-    const double bc1 = 1.0 - pow(beta1, (double)step), bc2 = 1.0 - pow(beta2, (double)step);
+    const double bc1 = step_counter ? 1.0 : 1.0 - pow(beta1, (double)step);
+    const double bc2 = step_counter ? 1.0 : 1.0 - pow(beta2, (double)step);
     for (int k = 0; k < n_groups; ++k) {
         const sl_adam_group& g = groups[k];
         if (g.width <= 0) continue;
         if (!g.param || !g.grad || !g.exp_avg || !g.exp_avg_sq) {
-            set_error("sl_adam_step: group %d has a NULL pointer", k);
+            set_error("%s: group %d has a NULL pointer", who, k);
             return SL_ERR_ARGUMENT;
         }
         AdamGroup& o = a.group[a.n_groups++];
         o.param = g.param; o.grad = g.grad; o.exp_avg = g.exp_avg; o.exp_avg_sq = g.exp_avg_sq;
         o.width = g.width;
-        o.step_size = (float)((double)g.lr / bc1);
+        o.step_size = (float)((double)g.lr / bc1);      // (the plain learning rate with a device-side count)
         o.freeze_by_marker = g.freeze_by_marker;
     }
     a.one_minus_beta1 = (float)(1.0 - beta1);
@@ -886,10 +888,31 @@ int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, dou
     a.one_minus_beta2 = (float)(1.0 - beta2);
     a.bias_correction2_sqrt = (float)sqrt(bc2);
     a.eps = (float)eps;
+    a.step_counter = step_counter;
+    a.beta1_d = beta1;
+    a.beta2_d = beta2;
     cudaStream_t stream = (cudaStream_t)stream_;
-    const int rc = launch_adam(a, P, marker, marker_threshold, stream);
+    const int rc = launch_adam(a, P, marker, marker_threshold, step_counter, stream);
     if (rc) return rc;
     return check_stage(false, stream, "adam step");
+}
+
+int sl_adam_step(int P, int n_groups, const sl_adam_group* groups, int step, double beta1, double beta2, double eps,
+                 const float* marker, float marker_threshold, void* stream_)
+{
+    return adam_impl("sl_adam_step", P, n_groups, groups, step, nullptr, beta1, beta2, eps, marker, marker_threshold, stream_);
+}
+
+int sl_adam_step_counted(int P, int n_groups, const sl_adam_group* groups, int* step_counter, double beta1, double beta2,
+                         double eps, const float* marker, float marker_threshold, void* stream_)
+{
+    if (step_counter == nullptr) {
+        g_error[0] = 0;
+        set_error("sl_adam_step_counted: step_counter is required");
+        return SL_ERR_ARGUMENT;
+    }
+    return adam_impl("sl_adam_step_counted", P, n_groups, groups, 0, step_counter, beta1, beta2, eps, marker,
+                     marker_threshold, stream_);
 }
 
 int sl_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,

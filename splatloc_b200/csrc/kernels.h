@@ -152,8 +152,15 @@ struct AdamArgs {
     AdamGroup group[STORE_MAX_GROUPS];
     int n_groups;
     float one_minus_beta1, beta2, one_minus_beta2, bias_correction2_sqrt, eps;
+    // step count kept on the device (a captured launch cannot carry a new count per replay): when
+    // step_counter != nullptr the kernel forms the bias corrections itself from *step_counter, in double as
+    // torch.optim.Adam does, and group[k].step_size holds the plain learning rate
+    const int* step_counter;
+    double beta1_d, beta2_d;
 };
-int launch_adam(const AdamArgs& args, int P, const float* marker, float marker_threshold, cudaStream_t stream);
+// `step_counter` != nullptr: incremented by one (a one-thread kernel) before the update reads it.
+int launch_adam(const AdamArgs& args, int P, const float* marker, float marker_threshold, int* step_counter,
+                cudaStream_t stream);
 
 int launch_densify_stats(int P, int n_views, const float* means2D_grad, const int* radii, float* xyz_gradient_accum,
                          float* denom, float* max_radii2D, cudaStream_t stream);

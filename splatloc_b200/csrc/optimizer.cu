@@ -25,10 +25,25 @@
 namespace sl {
 
 // ------------------------------------------------------------------ fused Adam
+__global__ void adam_count_kernel(int* step_counter) { *step_counter += 1; }
+
 __global__ void __launch_bounds__(256)
 adam_kernel(AdamArgs a, int P, const float* __restrict__ marker, float marker_threshold)
 {
     const AdamGroup g = a.group[blockIdx.y];
+    float step_size = g.step_size, bc2_sqrt = a.bias_correction2_sqrt;
+    if (a.step_counter != nullptr) {
+        // bias corrections from the device-side step count (uniform over the grid)
+        __shared__ float s_step_size, s_bc2;
+        if (threadIdx.x == 0) {
+            const double t = (double)*a.step_counter;
+            s_step_size = (float)((double)g.step_size / (1.0 - pow(a.beta1_d, t)));
+            s_bc2 = (float)sqrt(1.0 - pow(a.beta2_d, t));
+        }
+        __syncthreads();
+        step_size = s_step_size;
+        bc2_sqrt = s_bc2;
+    }
     const size_t n = (size_t)P * g.width;
     for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
         float grad = g.grad[i];
@@ -38,16 +53,18 @@ adam_kernel(AdamArgs a, int P, const float* __restrict__ marker, float marker_th
         float m = g.exp_avg[i], v = g.exp_avg_sq[i];
         m = fmaf(a.one_minus_beta1, grad - m, m);                 // exp_avg.lerp_(grad, 1 - beta1)
         v = fmaf(a.one_minus_beta2 * grad, grad, v * a.beta2);    // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
-        const float denom = sqrtf(v) / a.bias_correction2_sqrt + a.eps;
-        g.param[i] = g.param[i] - g.step_size * (m / denom);      // param.addcdiv_(exp_avg, denom, value=-step_size)
+        const float denom = sqrtf(v) / bc2_sqrt + a.eps;
+        g.param[i] = g.param[i] - step_size * (m / denom);      // param.addcdiv_(exp_avg, denom, value=-step_size)
         g.exp_avg[i] = m;
         g.exp_avg_sq[i] = v;
     }
 }
 
-int launch_adam(const AdamArgs& args, int P, const float* marker, float marker_threshold, cudaStream_t stream)
+int launch_adam(const AdamArgs& args, int P, const float* marker, float marker_threshold, int* step_counter,
+                cudaStream_t stream)
 {
     if (P <= 0 || args.n_groups <= 0) return 0;
+    if (step_counter != nullptr) { adam_count_kernel<<<1, 1, 0, stream>>>(step_counter); count_launch(); }
     int widest = 1;
     for (int k = 0; k < args.n_groups; ++k) widest = args.group[k].width > widest ? args.group[k].width : widest;
     const size_t n = (size_t)P * widest;

@@ -94,6 +94,35 @@ class GaussianStoreOptimizer:
                 _capi.check(self.lib.sl_adam_step(self.P, len(items), arr, step, self.betas[0], self.betas[1], self.eps,
                                                   None if marker is None else marker.data_ptr(), 0.005, _stream(self.dev)))
 
+    def step_counted(self, grads: dict, names: list | None = None) -> None:
+        """`step()` with the step count on the device (`self.device_step`, one int32 shared by the groups named
+        -- all groups that have a gradient by default): nothing in the call depends on a host-side number that
+        changes from step to step, so it can be captured in a CUDA graph and replayed.  The host-side counts
+        are not advanced; do not mix with `step()` on the same groups."""
+        if not hasattr(self, "device_step"):
+            self.device_step = torch.zeros(1, dtype=torch.int32, device=self.dev)
+        items = []
+        for n in (names if names is not None else list(self.params)):
+            g = grads.get(n)
+            p = self.params[n]
+            if g is None or p.numel() == 0:
+                continue
+            if g.shape != p.shape or not g.is_cuda or g.dtype != torch.float32 or not g.is_contiguous():
+                raise RuntimeError(f"gradient of {n} must be a contiguous float32 CUDA tensor of shape {tuple(p.shape)}")
+            items.append((n, g))
+        marker = self.params.get("marker") if self.primitive_reg else None
+        if marker is not None:
+            marker = marker.clone()
+        with torch.cuda.device(self.dev):
+            arr = (_capi.AdamGroup * len(items))()
+            for k, (n, g) in enumerate(items):
+                arr[k] = _capi.AdamGroup(self.params[n].data_ptr(), g.data_ptr(), self.exp_avg[n].data_ptr(),
+                                         self.exp_avg_sq[n].data_ptr(), self._width(n), self.lrs[n],
+                                         1 if (n == "xyz" and marker is not None) else 0)
+            _capi.check(self.lib.sl_adam_step_counted(self.P, len(items), arr, self.device_step.data_ptr(), self.betas[0],
+                                                      self.betas[1], self.eps, None if marker is None else marker.data_ptr(),
+                                                      0.005, _stream(self.dev)))
+
     # ------------------------------------------------------------------ add_densification_stats
     def add_densification_stats(self, means2D_grad: torch.Tensor, radii: torch.Tensor) -> None:
         """`means2D_grad` (V, P, 3) or (P, 3): the screen-space gradients of the window's views

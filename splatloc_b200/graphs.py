@@ -207,3 +207,112 @@ class GraphedViewStep:
         """The gradients of means3D, opacity, scales, rotations and colours / SH of the last replay as ONE
         flat tensor (the leading span of the step's packed block): what a multi-GPU step all-reduces."""
         return self.grad_block[:self.grad_block.trainable_numel]
+
+
+class GraphedRefinementIteration:
+    """One iteration of SplatLoc's colour-refinement loop (train_gaussians.py:270-295) -- render, the
+    (1 - lambda) L1 + lambda (1 - SSIM) loss, backward, Adam -- captured once and replayed with one launch.
+
+    Everything between the optimiser's raw parameters and their update runs inside the library: render()'s
+    pre-processing and the rasterizer (sl_forward_render without read-back, sl_backward_render), the loss and
+    its gradient (sl_ssim_forward / sl_ssim_backward), the Adam step of all groups with the step count on the
+    device (sl_adam_step_counted).  No reference counterpart: the reference's iteration is ~150 launches and
+    one host synchronisation.
+
+        it = GraphedRefinementIteration(opt, H, W, tanfovx, tanfovy, bg, max_pairs=2_000_000, lambda_dssim=0.2)
+        for view in views:
+            it.set_view(view.world_view_transform, view.full_proj_transform, view.camera_center, view.original_image)
+            it.replay()
+        ... it.loss (device scalar of the last replay), it.image (3, H, W), it.radii, it.overflow ...
+
+    `opt` is a `GaussianStoreOptimizer` with groups xyz, f_dc, opacity, scaling, rotation (and kp_score, which
+    this loss does not train); its tensors are updated in place by every replay."""
+
+    GROUPS = ("xyz", "f_dc", "opacity", "scaling", "rotation")
+
+    def __init__(self, opt, H: int, W: int, tanfovx: float, tanfovy: float, bg: torch.Tensor, max_pairs: int,
+                 lambda_dssim: float = 0.2, scale_modifier: float = 1.0, warmup: int = 2):
+        from .ssim_loss import _WINDOW
+        self.opt, self.H, self.W = opt, int(H), int(W)
+        self.tanfovx, self.tanfovy, self.bg = float(tanfovx), float(tanfovy), bg
+        self.max_pairs, self.lam, self.scale_modifier = int(max_pairs), float(lambda_dssim), float(scale_modifier)
+        self._window = _WINDOW
+        dev = opt.params["xyz"].device
+        for n in self.GROUPS:
+            if n not in opt.params:
+                raise ValueError(f"the optimiser has no group {n}")
+        self.viewmatrix = torch.zeros(1, 4, 4, device=dev)
+        self.projmatrix = torch.zeros(1, 4, 4, device=dev)
+        self.campos = torch.zeros(1, 3, device=dev)
+        self.gt_image = torch.zeros(3, self.H, self.W, device=dev)
+        self.loss = self.image = self.radii = self.overflow = None
+        lib = _capi.load()
+        with torch.cuda.device(dev):
+            self._ws = torch.zeros(int(lib.sl_ssim_workspace_bytes(self.W, self.H, 3)), dtype=torch.uint8, device=dev)
+            if not hasattr(opt, "device_step"):
+                opt.device_step = torch.zeros(1, dtype=torch.int32, device=dev)
+            # warm-up runs would move the parameters: they are put back before the capture
+            saved = {n: (opt.params[n].detach().clone(), opt.exp_avg[n].clone(), opt.exp_avg_sq[n].clone()) for n in self.GROUPS}
+            step0 = opt.device_step.clone()
+            s = torch.cuda.Stream()
+            s.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(s):
+                for _ in range(max(1, warmup)):
+                    self._iteration()
+            torch.cuda.current_stream().wait_stream(s)
+            torch.cuda.synchronize()
+            n0 = lib.sl_launch_count()
+            self.graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(self.graph):
+                self._iteration()
+            self.kernels_per_replay = int(lib.sl_launch_count() - n0)
+            with torch.no_grad():
+                for n, (p, m, v) in saved.items():
+                    opt.params[n].copy_(p)
+                    opt.exp_avg[n].copy_(m)
+                    opt.exp_avg_sq[n].copy_(v)
+                opt.device_step.copy_(step0)
+            torch.cuda.synchronize()
+
+    def _iteration(self):
+        lib, o = _capi.load(), self.opt
+        p = {n: o.params[n].detach() for n in o.params}
+        kp = p.get("kp_score", _EMPTY)
+        dev = self.gt_image.device
+        fw = _C.render_forward(self.bg, p["xyz"], p["f_dc"], kp, p["opacity"], p["scaling"], p["rotation"], self.scale_modifier,
+                               None, self.viewmatrix, self.projmatrix, self.tanfovx, self.tanfovy, self.H, self.W, self.campos,
+                               False, self.max_pairs)
+        R, color, depth, alpha, radii, geom, binning, img, status = fw
+        C, n = int(color.shape[1]), float(3 * self.H * self.W)
+        image = color[0, :3]
+        maps = torch.empty((3, 3, self.H, self.W), device=dev)
+        out = torch.empty(2, device=dev)
+        g_color = torch.zeros_like(color)             # the key-point channel, depth and alpha are not in this loss
+        g_rgb = g_color[0, :3]
+        stream = torch.cuda.current_stream(dev).cuda_stream
+        _capi.check(lib.sl_ssim_forward(self.W, self.H, 3, image.data_ptr(), self.gt_image.data_ptr(), self._window,
+                                        maps.data_ptr(), out.data_ptr(), self._ws.data_ptr(), stream))
+        _capi.check(lib.sl_ssim_backward(self.W, self.H, 3, image.data_ptr(), self.gt_image.data_ptr(), self._window,
+                                         maps.data_ptr(), None, -self.lam / n, (1.0 - self.lam) / n, g_rgb.data_ptr(), stream))
+        bw = _C.render_backward(self.bg, p["xyz"], radii, p["f_dc"], kp, p["opacity"], p["scaling"], p["rotation"],
+                                self.scale_modifier, self.viewmatrix, self.projmatrix, self.tanfovx, self.tanfovy, g_color,
+                                torch.zeros_like(depth), torch.zeros_like(alpha), self.campos, geom, R, binning, img, alpha)
+        (_, g_means2D, g_xyz, g_fdc, _, g_opac, g_scale, g_rot) = bw
+        grads = {"xyz": g_xyz.view(o.params["xyz"].shape), "f_dc": g_fdc.view(o.params["f_dc"].shape),
+                 "opacity": g_opac.view(o.params["opacity"].shape), "scaling": g_scale.view(o.params["scaling"].shape),
+                 "rotation": g_rot.view(o.params["rotation"].shape)}
+        o.step_counted({k: v.contiguous() for k, v in grads.items()}, names=list(self.GROUPS))
+        self.loss = (1.0 - self.lam) * out[1] + self.lam * (1.0 - out[0])
+        self.image, self.radii, self.overflow, self.means2D_grad = image, radii[0], status, g_means2D[0]
+        self._keep = (fw, bw, maps, out, g_color)
+
+    def set_view(self, viewmatrix, projmatrix, campos, gt_image) -> None:
+        """Copy a camera (reference convention: transposed world-to-view, full projection, centre) and its
+        ground-truth image (3, H, W) into the static inputs; host or device tensors."""
+        self.viewmatrix[0].copy_(viewmatrix, non_blocking=True)
+        self.projmatrix[0].copy_(projmatrix, non_blocking=True)
+        self.campos[0].copy_(campos, non_blocking=True)
+        self.gt_image.copy_(gt_image, non_blocking=True)
+
+    def replay(self) -> None:
+        self.graph.replay()
