@@ -223,58 +223,82 @@ blend_backward_kernel(const uint2* __restrict__ ranges, const uint32_t* __restri
 
     // Pixel phase over the `cnt` records parked in the warp's buffer; `top_pos` is the list position
     // of the chunk's entry 0 (entries run towards the front of the list).
-    auto pixel_phase = [&](int cnt, int top_pos, bool final) {
-        for (int k = 0;; ++k) {
-            bool flush = final && rows > 0;      // after the last record: whatever rows are left
-            if (k < cnt) {
-            const uint32_t ra = rec_a + (uint32_t)k * (uint32_t)sizeof(PairRecord);
-            const int pos = top_pos - (int)lds_u8(lane_a + k);
-            const float4 xyd = lds128(ra);
-            const float4 co = lds128(ra + 16);
-            const float dx = __fsub_rn(xyd.x, pixf_x);
-            const float dy = __fsub_rn(xyd.y, pixf_y);
-            const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
-            const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
-            const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
-            const float power = __fmaf_rn(s, -0.5f, -t3);
-            const float G = exp_like_reference(power);
-            const float alpha = fminf(0.99f, __fmul_rn(co.w, G));
-            const bool blend = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
-            if (!__any_sync(FULL, blend)) continue;
+    // alpha of the k-th parked record for this lane's pixel, exactly as the forward evaluated it
+    auto evaluate = [&](int k, int top_pos, float4& xyd, float4& co, float& G, float& alpha, bool& blend) {
+        const uint32_t ra = rec_a + (uint32_t)k * (uint32_t)sizeof(PairRecord);
+        const int pos = top_pos - (int)lds_u8(lane_a + k);
+        xyd = lds128(ra);
+        co = lds128(ra + 16);
+        const float dx = __fsub_rn(xyd.x, pixf_x);
+        const float dy = __fsub_rn(xyd.y, pixf_y);
+        const float t1 = __fmul_rn(__fmul_rn(dy, co.z), dy);
+        const float t3 = __fmul_rn(__fmul_rn(dx, co.y), dy);
+        const float s = __fmaf_rn(dx, __fmul_rn(dx, co.x), t1);
+        const float power = __fmaf_rn(s, -0.5f, -t3);
+        G = exp_like_reference(power);
+        alpha = fminf(0.99f, __fmul_rn(co.w, G));
+        blend = (pos < last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+    };
+    // the pixel's recurrences for one record some pixel of the patch blends; fills one row
+    auto apply = [&](int k, const float4& xyd, const float4& co, float G, float alpha, bool blend) {
+        const uint32_t ra = rec_a + (uint32_t)k * (uint32_t)sizeof(PairRecord);
+        float w = 0.f, a = 0.f;
+        if (blend) {
+            // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha); 1 - alpha is in
+            // [0.01, 1], so MUFU.RCP plus one Newton step is within an ulp of the reference's division
+            const float om = 1.f - alpha;
+            float inv;
+            asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(om));
+            inv = __fmaf_rn(__fmaf_rn(-om, inv, 1.f), inv, inv);
+            T = T * inv;
+            w = alpha * T;
+            // d = dL/dpix . (colour, depth, 1) of this Gaussian; channels >= 3 are masked out
+            const float4 f = lds128(ra + 32);
+            float d = fmaf(xyd.z, dL_dpixel_depth, dL_dpixel_alpha);
+            d = fmaf(f.x, dL_dpixel[0], d);
+            d = fmaf(f.y, dL_dpixel[1], d);
+            d = fmaf(f.z, dL_dpixel[2], d);
+            const float dL_dalpha = fmaf(T, d, -(behind * inv));
+            behind = fmaf(w, d, behind);
+            a = G * dL_dalpha;
+        }
+        s_w[warp][rows * BWD_STRIDE + lane] = w;
+        s_a[warp][rows * BWD_STRIDE + lane] = a;
+        if (lane == 0) {
+            s_grec[warp][rows][0] = make_float4(xyd.x, xyd.y, co.x, co.y);
+            s_grec[warp][rows][1] = make_float4(co.z, co.w, xyd.w, 0.f);
+        }
+        if (++rows == BWD_ROWS) {
+            gaussian_phase(rows);
+            rows = 0;
+        }
+    };
 
-            float w = 0.f, a = 0.f;
-            if (blend) {
-                // one reciprocal serves T / (1 - alpha) and T_final / (1 - alpha); 1 - alpha is in
-                // [0.01, 1], so MUFU.RCP plus one Newton step is within an ulp of the reference's division
-                const float om = 1.f - alpha;
-                float inv;
-                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(inv) : "f"(om));
-                inv = __fmaf_rn(__fmaf_rn(-om, inv, 1.f), inv, inv);
-                T = T * inv;
-                w = alpha * T;
-                // d = dL/dpix . (colour, depth, 1) of this Gaussian; channels >= 3 are masked out
-                const float4 f = lds128(ra + 32);
-                float d = fmaf(xyd.z, dL_dpixel_depth, dL_dpixel_alpha);
-                d = fmaf(f.x, dL_dpixel[0], d);
-                d = fmaf(f.y, dL_dpixel[1], d);
-                d = fmaf(f.z, dL_dpixel[2], d);
-                const float dL_dalpha = fmaf(T, d, -(behind * inv));
-                behind = fmaf(w, d, behind);
-                a = G * dL_dalpha;
-            }
-            s_w[warp][rows * BWD_STRIDE + lane] = w;
-            s_a[warp][rows * BWD_STRIDE + lane] = a;
-            if (lane == 0) {
-                s_grec[warp][rows][0] = make_float4(xyd.x, xyd.y, co.x, co.y);
-                s_grec[warp][rows][1] = make_float4(co.z, co.w, xyd.w, 0.f);
-            }
-            flush = (++rows == BWD_ROWS);
-            }
-            if (flush) {
-                gaussian_phase(rows);
-                rows = 0;
-            }
-            if (k >= cnt) break;
+    // Pixel phase over the `cnt` records parked in the warp's buffer; `top_pos` is the list position
+    // of the chunk's entry 0 (entries run towards the front of the list).  Two records are evaluated
+    // together (their alphas do not depend on each other), then applied in list order.
+    auto pixel_phase = [&](int cnt, int top_pos, bool final) {
+        int k = 0;
+        for (; k + 1 < cnt; k += 2) {
+            float4 xa, ca, xb, cb;
+            float Ga, aa, Gb, ab;
+            bool ba, bb;
+            evaluate(k, top_pos, xa, ca, Ga, aa, ba);
+            evaluate(k + 1, top_pos, xb, cb, Gb, ab, bb);
+            const bool any_a = __any_sync(FULL, ba), any_b = __any_sync(FULL, bb);
+            if (any_a) apply(k, xa, ca, Ga, aa, ba);
+            if (any_b) apply(k + 1, xb, cb, Gb, ab, bb);
+        }
+        if (k < cnt) {
+            float4 xa, ca;
+            float Ga, aa;
+            bool ba;
+            evaluate(k, top_pos, xa, ca, Ga, aa, ba);
+            if (__any_sync(FULL, ba)) apply(k, xa, ca, Ga, aa, ba);
+        }
+        if (final && rows > 0) {         // after the last record: whatever rows are left
+            gaussian_phase(rows);
+            rows = 0;
         }
     };
 
